@@ -1,0 +1,207 @@
+"""CPU: pin the oracle restatement against golden vectors produced by the
+reference itself (oracle/make_golden.py).  No GPU, no /root/reference."""
+import numpy as np
+import pytest
+
+from oracle import cpm_link as o
+from tests.conftest import golden
+
+
+# ---- G1 PRBS (reference tests/test_glfsr.py pins only periodicity; goldens pin values)
+def test_masks_all_degrees():
+    g = golden("g1_pn.npz")
+    ours = np.array([o.pn_mask(d) for d in range(2, 65)], dtype=np.uint64)
+    assert np.array_equal(ours, g["masks"])
+    assert o.pn_mask(9) == 0x110 and o.pn_mask(15) == 0x6000 and o.pn_mask(23) == 0x420000
+
+
+@pytest.mark.parametrize("bad", [0, 1, 65, 100, -3])
+def test_mask_keyerror(bad):
+    with pytest.raises(KeyError):
+        o.pn_mask(bad)
+
+
+@pytest.mark.parametrize("deg", [9, 15])
+def test_pn_full_period(deg):
+    g = golden("g1_pn.npz")
+    seq = o.pn_sequence(deg)
+    assert np.array_equal(np.packbits(seq), g[f"pn{deg}"])
+
+
+@pytest.mark.parametrize("deg", [2, 3, 5, 7, 12, 16, 31, 32, 33, 63, 64])
+def test_pn_prefix(deg):
+    g = golden("g1_pn.npz")
+    bits, _ = o.lfsr_bits(o.pn_mask(deg), (1 << deg) - 1, 256)
+    assert np.array_equal(np.packbits(bits), g[f"pn{deg}_first256"])
+
+
+def test_pn23_prefix():
+    g = golden("g1_pn.npz")
+    bits, _ = o.lfsr_bits(o.pn_mask(23), (1 << 23) - 1, 65536)
+    assert np.array_equal(np.packbits(bits), g["pn23_first65536"])
+
+
+@pytest.mark.parametrize("order", range(2, 15))
+def test_pn_periodicity(order):
+    """Mirror of reference tests/test_glfsr.py:6-25 (orders trimmed for CPU time)."""
+    mask, st = o.pn_mask(order), (1 << order) - 1
+    a, st = o.lfsr_bits(mask, st, 2**order - 1)
+    b, st = o.lfsr_bits(mask, st, 2**order - 1)
+    assert np.array_equal(a, b)
+
+
+# ---- G2 encoders / mappers
+@pytest.mark.parametrize("name", list(o.TRELLISES))
+def test_encoders(name, pn15_stream):
+    g = golden("g2_encode.npz")
+    assert np.array_equal(o.fsm_encode(o.TRELLISES[name], pn15_stream), g[name])
+
+
+def test_mappers_and_identities(pn15_stream):
+    g = golden("g2_encode.npz")
+    assert np.array_equal(o.map_pcmfm(pn15_stream), g["PCMFMSymbolMapper"])
+    assert np.array_equal(o.map_multih(pn15_stream), g["MultiHSymbolMapper"])
+    assert np.array_equal(o.soqpsk_precoder(pn15_stream), g["SOQPSKPrecoder"])
+    assert np.array_equal(g["SimpleTrellis2"], g["PCMFMSymbolMapper"])
+    assert np.array_equal(g["SimpleTrellis4"], g["MultiHSymbolMapper"])
+    assert np.array_equal(-2 * g["SOQPSKPrecoder"], g["SOQPSKTrellis4x2"])
+    assert np.array_equal(g["SOQPSKTrellis8x1"], g["SOQPSKTrellis4x2"])
+    b = pn15_stream
+    d = b.copy()
+    for i in range(2, d.size):
+        d[i] ^= d[i - 2]
+    assert np.array_equal(o.fsm_encode(o.TRELLISES["SOQPSKTrellis4x2"], d), g["SOQPSKTrellis4x2DiffEncoded"])
+
+
+def test_encoder_streaming(pn15_stream):
+    g = golden("g2_encode.npz")
+    cols = o.TRELLISES["SOQPSKTrellis4x2DiffEncoded"]
+    a, i, st = o.fsm_encode(cols, pn15_stream[:1001], return_state=True)
+    b = o.fsm_encode(cols, pn15_stream[1001:3000], i0=i, state0=st)
+    assert np.array_equal(np.concatenate((a, b)), g["stream_split_1001"])
+
+
+def test_encoder_errors():
+    with pytest.raises(ValueError):
+        o.fsm_encode(o.TRELLISES["SimpleTrellis4"], np.zeros(3, dtype=np.uint8))
+    with pytest.raises(ValueError):
+        o.map_multih(np.zeros(5, dtype=np.uint8))
+
+
+# ---- G3 pulses
+@pytest.mark.parametrize("sps", [8, 10])
+def test_pulses(sps):
+    g = golden("g3_pulses.npz")
+    cases = {
+        "tg": o.pulse_soqpsk_tg(sps), "a": o.pulse_soqpsk_a(sps), "b": o.pulse_soqpsk_b(sps),
+        "mil": o.pulse_soqpsk_mil(sps), "pcmfm4": o.pulse_pcmfm(sps, 4), "pcmfm6": o.pulse_pcmfm(sps, 6),
+        "multih": o.pulse_multih(sps),
+    }
+    for k, v in cases.items():
+        ref = g[f"{k}_{sps}"]
+        assert v.shape == ref.shape, k
+        np.testing.assert_allclose(v, ref, rtol=0, atol=1e-14, err_msg=k)
+        assert abs(v.sum() - sps / 2) < 1e-12
+    for lab, f in (("tg", o.pulse_soqpsk_tg), ("mil", o.pulse_soqpsk_mil)):
+        r = o.rho_pulses(f(sps), 0.25, sps, 2)
+        np.testing.assert_allclose(r[0], g[f"rho0_{lab}_{sps}"], rtol=0, atol=1e-14)
+        np.testing.assert_allclose(r[1], g[f"rho1_{lab}_{sps}"], rtol=0, atol=1e-14)
+    if sps == 8:
+        assert [cases[k].size for k in ("tg", "a", "b", "mil", "pcmfm4", "pcmfm6", "multih")] == [65, 65, 129, 9, 24, 24, 25]
+
+
+# ---- G4 modulators
+_MOD = {
+    "pcmfm": ("SimpleTrellis2", 0.7, lambda s: o.pulse_pcmfm(s, 4)),
+    "pcmfm6": ("SimpleTrellis2", 0.7, lambda s: o.pulse_pcmfm(s, 6)),
+    "tg": ("SOQPSKTrellis4x2DiffEncoded", 0.25, o.pulse_soqpsk_tg),
+    "mil": ("SOQPSKTrellis4x2DiffEncoded", 0.25, o.pulse_soqpsk_mil),
+    "a": ("SOQPSKTrellis4x2", 0.25, o.pulse_soqpsk_a),
+    "b": ("SOQPSKTrellis4x2", 0.25, o.pulse_soqpsk_b),
+    "multih": ("SimpleTrellis4", np.array([4, 5]) / 16, o.pulse_multih),
+}
+
+
+@pytest.mark.parametrize("sps", [8, 10])
+@pytest.mark.parametrize("lab", list(_MOD))
+def test_modulators(lab, sps):
+    g = golden("g4_modulated.npz")
+    tre, h, pf = _MOD[lab]
+    sy = o.fsm_encode(o.TRELLISES[tre], g["bits"])
+    ref = g[f"{lab}_{sps}"]
+    t, s = o.cpm_modulate(sy, h, pf(sps), sps)
+    assert s.shape == ref.shape
+    assert np.max(np.abs(s - ref)) < 1e-12
+    s2 = o.cpm_modulate_closed_form(sy, h, pf(sps), sps)
+    assert np.max(np.abs(s2 - ref)) < 1e-10
+    if lab == "tg" and sps == 8:
+        np.testing.assert_allclose(t, g["time_tg_8"], rtol=0, atol=0)
+
+
+# ---- G5-G8 config 1 chain
+def test_config1_chain():
+    g = golden("g5_config1.npz")
+    bits = g["bits"]
+    pulse = o.pulse_soqpsk_tg(8)
+    for det in ("PT", "PAM"):
+        r = o.soqpsk_link_frame(bits, pulse, 8, float(g["sigma"]), noise=g["noise"], detector=det,
+                                fast=False, return_all=True)
+        assert np.array_equal(r["symbols"], g["symbols"])
+        assert np.max(np.abs(r["signal"] - g["tx"])) < 1e-12
+        assert r["z"].shape == g[f"{det}_z"].shape == (4095, 3)
+        assert np.max(np.abs(r["z"] - g[f"{det}_z"])) < 1e-10
+        assert np.array_equal(r["dec_bits"], g[f"{det}_dec_bits"])
+        assert np.array_equal(r["dec_syms"], g[f"{det}_dec_syms"])
+        assert (r["bit_errors"], r["sym_errors"], r["compared"]) == (
+            int(g[f"{det}_bit_errors"]), int(g[f"{det}_sym_errors"]), int(g[f"{det}_compared"]))
+    assert int(g["PT_bit_errors"]) == 66 and int(g["PAM_bit_errors"]) == 32 and int(g["PAM_compared"]) == 4093
+
+
+def test_fast_detector_equals_stateful():
+    g = golden("g5_config1.npz")
+    for det in ("PT", "PAM"):
+        z = g[f"{det}_z"]
+        b1, s1 = o.detect_soqpsk(z[:1500], 2, True)
+        b2, s2 = o.detect_soqpsk_fast(z[:1500], True)
+        assert np.array_equal(b1, b2) and np.array_equal(s1, s2)
+        assert np.array_equal(b2, g[f"{det}_dec_bits"][:1500])
+    zz = np.stack([g["PT_z"], g["PAM_z"]])
+    bb, ss = o.detect_soqpsk_fast(zz, True)
+    assert np.array_equal(bb[0], g["PT_dec_bits"]) and np.array_equal(bb[1], g["PAM_dec_bits"])
+    assert np.array_equal(ss[0], g["PT_dec_syms"]) and np.array_equal(ss[1], g["PAM_dec_syms"])
+
+
+@pytest.mark.parametrize("diff", [True, False])
+@pytest.mark.parametrize("length", [2, 4])
+def test_variants(diff, length):
+    g = golden("g7_variants.npz")
+    tag = f"d{int(diff)}_l{length}"
+    sig = float(np.sqrt(8 / (2 * 10 ** 0.8)))
+    for det in ("PT", "PAM"):
+        r = o.soqpsk_link_frame(g["bits"], o.pulse_soqpsk_tg(8), 8, sig, noise=g[f"noise_{tag}"],
+                                detector=det, length=length, diff=diff, fast=True, return_all=True)
+        assert np.array_equal(r["dec_bits"], g[f"{det}_bits_{tag}"])
+        assert np.array_equal(r["dec_syms"], g[f"{det}_syms_{tag}"])
+        assert [r["bit_errors"], r["sym_errors"], r["compared"]] == list(g[f"{det}_counts_{tag}"])
+
+
+def test_example_replay(pn15_stream):
+    """The shipped example: sps 10, sigma sqrt(2)/2, MIL then TG from one PCG64(1)
+    (soqpsk_detection.py:26,38-41,66-70,183-187).  Counts: G8."""
+    g = golden("g8_example.npz")
+    rng = np.random.Generator(np.random.PCG64(seed=1))
+    sps, sigma = 10, np.sqrt(2) / 2
+    for lab, pf, offs in (("MIL", o.pulse_soqpsk_mil, {"PT": -1, "PAM": -3}),
+                          ("TG", o.pulse_soqpsk_tg, {"PT": -1, "PAM": 0})):
+        T = (pn15_stream.size + 1) * sps
+        noise = o.complex_awgn(sigma, T, rng)
+        crc = np.array([noise.real.sum(), noise.imag.sum()])
+        if not np.allclose(crc, g[f"noise_crc_{lab}"], rtol=0, atol=1e-6):
+            pytest.skip("numpy PCG64 normal stream differs from the golden generator's numpy")
+        for det in ("PT", "PAM"):
+            r = o.soqpsk_link_frame(pn15_stream, pf(sps), sps, sigma, noise=noise, detector=det,
+                                    timing_offset=offs[det], fast=True, return_all=True)
+            assert [r["bit_errors"], r["sym_errors"], r["compared"]] == list(g[f"{lab}_{det}_counts"]), (lab, det)
+            assert np.array_equal(np.packbits(r["dec_bits"]), g[f"{lab}_{det}_bits"])
+    assert list(g["TG_PT_counts"])[::2] == [14, 32765] and list(g["TG_PAM_counts"])[::2] == [11, 32765]
+    assert list(g["MIL_PT_counts"])[::2] == [61, 32765] and list(g["MIL_PAM_counts"])[::2] == [0, 32765]
