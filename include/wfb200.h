@@ -1,0 +1,175 @@
+/* wfb200.h -- C ABI of libwfb200.so, the B200 (sm_100a) hot path of the CPM
+ * Monte-Carlo link simulator.
+ *
+ * Boundary rules:
+ *   - every bulk pointer named d_* is DEVICE memory owned by the caller; the
+ *     library never allocates, frees or keeps it.  Small tables (pulses, taps,
+ *     mod indices) are HOST pointers, copied into kernel parameter space.
+ *   - every compute entry point is asynchronous on `stream` (a cudaStream_t
+ *     passed as void*; NULL = legacy default stream) and re-entrant.
+ *   - return value: 0 = ok, negative = wf_status; wf_last_error_string() gives
+ *     the text for the calling thread.  There is no CPU fallback: on a machine
+ *     without an sm_100 device the compute calls return WF_ERR_DEVICE.
+ *
+ * Each entry point names the reference interface it replaces (paths relative
+ * to the reference repository mcdiarmid/waveforms).
+ */
+#ifndef WFB200_H
+#define WFB200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define WF_ABI_VERSION 1
+
+#if defined(__GNUC__)
+#define WF_API __attribute__((visibility("default")))
+#else
+#define WF_API
+#endif
+
+enum wf_status {
+  WF_OK = 0,
+  WF_ERR_ARG = -1,     /* bad argument (text says which) */
+  WF_ERR_DEVICE = -2,  /* no usable sm_100 CUDA device */
+  WF_ERR_CUDA = -3,    /* CUDA runtime error (text = cudaGetErrorString) */
+  WF_ERR_UNSUPPORTED = -4
+};
+
+/* element type of baseband / matched-filter / metric arrays */
+enum wf_dtype { WF_F32 = 0 /* complex64 */, WF_F64 = 1 /* complex128 */ };
+
+/* closed-form bit->symbol encoders (waveforms/cpm/trellis/model.py:179-293,
+ * cpm/{soqpsk,pcmfm,multih}/precoder.py) */
+enum wf_encoder {
+  WF_ENC_SOQPSK_DIFF = 0,    /* TrellisEncoder(SOQPSKTrellis4x2DiffEncoded)            */
+  WF_ENC_SOQPSK = 1,         /* TrellisEncoder(SOQPSKTrellis4x2) == SOQPSKTrellis8x1   */
+  WF_ENC_BINARY = 2,         /* SimpleTrellis2 == PCMFMSymbolMapper: 2b-1              */
+  WF_ENC_QUATERNARY = 3,     /* SimpleTrellis4 == MultiHSymbolMapper: 2(2b0+b1)-3      */
+  WF_ENC_SOQPSK_TERNARY = 4  /* SOQPSKPrecoder: {-1,0,+1} = -(SOQPSKTrellis4x2)/2      */
+};
+
+/* ---- library / device ---------------------------------------------------- */
+WF_API int wf_abi_version(void);
+WF_API const char* wf_last_error_string(void);
+/* 0 when the current CUDA device is compute capability 10.x, else WF_ERR_DEVICE */
+WF_API int wf_device_check(void);
+
+/* ---- A1  PRBS: waveforms/glfsr/glfsr.py:6-19, glfsr/pn.py:6-107 --------- */
+/* generate_mask(degree) (pn.py:75-90); returns 0 when 1 < degree < 65 fails
+ * (the Python shim raises the reference's KeyError). Host only. */
+WF_API uint64_t wf_lfsr_mask(int degree);
+/* state after `steps` applications of GLFSR.next_bit (glfsr.py:15-19) by
+ * GF(2) jump-ahead. Host only. */
+WF_API uint64_t wf_lfsr_jump(uint64_t mask, int degree, uint64_t state, uint64_t steps);
+
+/* B frames of N bits from one Galois LFSR stream plus their symbols.
+ * Frame b starts `d_bit_offsets[b]` steps after `init_state` when
+ * d_bit_offsets != NULL, else (first_frame + b) * N steps (reduced mod 2^degree-1
+ * when the state is non-zero and the polynomial maximal -- caller's choice via
+ * `period`; period == 0 means "do not reduce").
+ * Outputs (any may be NULL): d_bits uint8[B][N] (0/1, the reference layout),
+ * d_packed uint32[B][ld_words] (bit i of a frame = word i/32, bit i%32),
+ * d_syms int8[B][S] with S = N (N/2 for WF_ENC_QUATERNARY).
+ * d_enc_state int32[B][2] = (i, state) of TrellisEncoder carried in/out
+ * (encoder.py:11-12,44-46); NULL = fresh encoder per frame.
+ * Replaces PNSequence/GLFSR.next_bit + TrellisEncoder.encode / the mappers. */
+WF_API int wf_prbs_encode(uint64_t mask, int degree, uint64_t init_state, uint64_t period,
+                   const uint64_t* d_bit_offsets, uint64_t first_frame,
+                   int64_t B, int64_t N, int encoder,
+                   int32_t* d_enc_state,
+                   uint8_t* d_bits, uint32_t* d_packed, int64_t ld_words,
+                   int8_t* d_syms, void* stream);
+
+/* Same encoders on caller-supplied bits d_bits_in uint8[B][N] (0/1).
+ * Replaces TrellisEncoder.encode (encoder.py:17-48) and the mapper __call__s. */
+WF_API int wf_bits_encode(const uint8_t* d_bits_in, int64_t B, int64_t N, int encoder,
+                   int32_t* d_enc_state,
+                   uint32_t* d_packed, int64_t ld_words, int8_t* d_syms, void* stream);
+
+/* Arbitrary Trellis object, table driven (one frame per thread).
+ * next_state / out_symbol are HOST tables [columns][states][1<<bits_per_symbol]
+ * built from forward_map (model.py:127-137; last branch wins on duplicates);
+ * entries < 0 in next_state mark a missing branch (-> WF_ERR_ARG is NOT raised
+ * on device; the symbol written is 0 and the state is kept). */
+WF_API int wf_trellis_encode(const uint8_t* d_bits_in, int64_t B, int64_t N,
+                      const int8_t* next_state, const int8_t* out_symbol,
+                      int columns, int states, int bits_per_symbol,
+                      int32_t* d_enc_state, int8_t* d_syms, void* stream);
+
+/* ---- A6/A7  modulator and AWGN: cpm/modulate.py:28-101, noise.py:8-32 ---- */
+/* cpm_modulate(symbols, mod_index, pulse_filter, sps) for B frames.
+ * d_syms int8[B][S]; mod_index double[n_h] (cycled per symbol, modulate.py:91-92);
+ * pulse double[K]; output d_out complex[B][ld_out] (ld_out >= T=(S+1)*sps, in
+ * complex elements), dtype selects complex64 / complex128.
+ * phase[n] = 2pi/sps * cumsum(convolve(upsampled, pulse, "same"))[n] + initial_phase;
+ * the output is exp(j(phase + derotate)) (derotate = -pi/4 reproduces
+ * examples/soqpsk_detection.py:85; 0 = plain cpm_modulate).
+ * When d_sigma != NULL complex AWGN is added in the same pass (see wf_awgn_add). */
+WF_API int wf_cpm_modulate(const int8_t* d_syms, int64_t B, int64_t S,
+                    const double* mod_index, int n_h,
+                    const double* pulse, int K, int sps,
+                    double initial_phase, double derotate,
+                    int dtype, void* d_out, int64_t ld_out,
+                    const float* d_sigma, const int32_t* d_point,
+                    uint64_t seed, uint64_t first_frame, void* stream);
+
+/* generate_complex_awgn(sigma, size) added in place: d_sig[b][n] += sigma[b] *
+ * (N(0,1) + j N(0,1)).  Philox4x32-10, key = seed, counter = (n/2, global frame
+ * first_frame+b, point d_point[b] (0 if NULL), 0): two complex samples per
+ * counter, so results do not depend on batching or sharding.
+ * d_sigma float[B] (sigma per real component, as in noise.py). */
+WF_API int wf_awgn_add(void* d_sig, int dtype, int64_t B, int64_t T, int64_t ld,
+                const float* d_sigma, const int32_t* d_point,
+                uint64_t seed, uint64_t first_frame, void* stream);
+
+/* raw N(0,1) pairs, for statistical tests: d_out float2[B][T] */
+WF_API int wf_awgn_fill(float* d_out, int64_t B, int64_t T, const float* d_sigma,
+                 const int32_t* d_point, uint64_t seed, uint64_t first_frame, void* stream);
+
+/* ---- A8/A9  decimated matched-filter bank:
+ *      examples/soqpsk_detection.py:134-173 (np.convolve(rx, taps, "same") then
+ *      the driver's 1-in-sps column pick, :189-196) ------------------------- */
+/* y_f[i] = sum_t rx[n_i + center - t] * taps[f][t],  n_i = first_instant + i*sps,
+ * rx outside [0,T) = 0;  z_r[i] = sum_f combine[r][f] * y_f[i] (combine NULL ->
+ * z = y, n_out = n_filt).  taps_im NULL -> real taps.  All tables HOST double.
+ * d_rx complex[B][ld_rx]; d_out complex[B][ld_out][n_out] (ld_out >= n_calls).
+ * center = (n_taps-1)/2 reproduces "same". */
+WF_API int wf_mf_bank(const void* d_rx, int dtype, int64_t B, int64_t T, int64_t ld_rx,
+               const double* taps_re, const double* taps_im, int n_filt, int n_taps,
+               int center, const double* combine_re, const double* combine_im, int n_out,
+               int sps, int64_t first_instant, int64_t n_calls,
+               void* d_out, int64_t ld_out, void* stream);
+
+/* ---- A10/A13  SOQPSK trellis detector + error count:
+ *      viterbi/algorithm.py:19-101 driven as examples/soqpsk_detection.py:177-209 */
+/* d_z complex[B][ld_z][3] = one matched-filter 3-vector (alpha=-2,0,+2) per
+ * detector call.  Runs n_calls calls of SOQPSKTrellisDetector(length,
+ * differantial_encoding=diff).iteration per frame and keeps element [0] of each.
+ * Optional outputs: d_dec_bits uint8[B][n_calls], d_dec_syms int8[B][n_calls].
+ * Optional error count (soqpsk_detection.py:200-209): decisions [length:] are
+ * compared with d_tx_packed (bits, wf_prbs_encode layout) and d_tx_syms
+ * int8[B][S]; n_cmp = min(S, n_calls-length) per frame; adds to
+ * d_counters int64[n_points][3] = (bit errors, symbol errors, compared) at row
+ * d_point[b] (row 0 if NULL). */
+WF_API int wf_viterbi_soqpsk(const void* d_z, int dtype, int64_t B, int64_t n_calls, int64_t ld_z,
+                      int diff, int length,
+                      uint8_t* d_dec_bits, int8_t* d_dec_syms,
+                      const uint32_t* d_tx_packed, int64_t ld_words,
+                      const int8_t* d_tx_syms, int64_t S,
+                      const int32_t* d_point, int64_t* d_counters, void* stream);
+
+/* stand-alone error count of unpacked decisions (soqpsk_detection.py:200-209):
+ * drops the first `skip` decisions of each frame, compares n_cmp of them. */
+WF_API int wf_bert(const uint8_t* d_dec_bits, const int8_t* d_dec_syms, int64_t ld_dec,
+            const uint8_t* d_tx_bits, const int8_t* d_tx_syms, int64_t ld_tx,
+            int64_t B, int64_t skip, int64_t n_cmp,
+            const int32_t* d_point, int64_t* d_counters, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* WFB200_H */

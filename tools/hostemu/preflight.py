@@ -1,0 +1,298 @@
+"""DEVELOPMENT TOOL ONLY: run the kernel sources on host threads (build_emu.py) and
+compare with the oracle, before spending GPU minutes.  Not a test of the product
+library and never imported by it.
+
+    python tools/hostemu/build_emu.py && python tools/hostemu/preflight.py [names...]
+"""
+import ctypes as C
+import os
+import sys
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+sys.path.insert(0, ROOT)
+from oracle import cpm_link as o  # noqa: E402
+from waveforms_b200 import _ffi  # noqa: E402
+
+L = _ffi.bind(C.CDLL(os.environ.get("WFEMU_LIB", "/tmp/wfemu/libwfb200_emu.so")))
+G = lambda n: np.load(os.path.join(ROOT, "tests", "golden", n))  # noqa: E731
+
+
+def ptr(a):
+    return None if a is None else a.ctypes.data_as(C.c_void_p)
+
+
+def ok(rc):
+    assert rc == 0, (rc, L.wf_last_error_string())
+
+
+def darr(v):
+    v = np.ascontiguousarray(np.atleast_1d(v), dtype=np.float64)
+    return v, v.ctypes.data_as(C.c_void_p)
+
+
+def t_lfsr():
+    for deg in (2, 9, 15, 23, 33, 64):
+        mask = o.pn_mask(deg)
+        assert L.wf_lfsr_mask(deg) == mask
+        st0 = (1 << deg) - 1
+        for k in (0, 1, 31, 1000, 12345):
+            _, st = o.lfsr_bits(mask, st0, k)
+            assert L.wf_lfsr_jump(mask, deg, st0, k) == st, (deg, k)
+    assert L.wf_lfsr_mask(1) == 0 and L.wf_lfsr_mask(65) == 0
+
+
+def run_prbs(deg, B, N, enc, first=0, state=None, period=True):
+    mask, st0 = o.pn_mask(deg), (1 << deg) - 1
+    S = N // 2 if enc == 3 else N
+    ldw = (N + 31) // 32
+    bits = np.full((B, N), 7, np.uint8)
+    packed = np.zeros((B, ldw), np.uint32)
+    syms = np.full((B, S), 99, np.int8)
+    ok(L.wf_prbs_encode(mask, deg, st0, (1 << deg) - 1 if period else 0, None, first, B, N, enc,
+                        ptr(state), ptr(bits), ptr(packed), ldw, ptr(syms), None))
+    return bits, packed, syms
+
+
+ENC = {0: "SOQPSKTrellis4x2DiffEncoded", 1: "SOQPSKTrellis4x2", 2: "SimpleTrellis2", 3: "SimpleTrellis4"}
+
+
+def t_prbs():
+    for deg, B, N, first in ((15, 5, 4096, 0), (15, 3, 1000, 7), (9, 2, 70, 3), (23, 2, 2080, 1), (33, 2, 96, 5)):
+        for enc in (0, 1, 2, 3, 4):
+            bits, packed, syms = run_prbs(deg, B, N, enc, first)
+            period = (1 << deg) - 1
+            for b in range(B):
+                if deg <= 15:
+                    ref = o.pn_frame_bits(deg, first + b, N)
+                else:
+                    st = L.wf_lfsr_jump(o.pn_mask(deg), deg, period, ((first + b) * N) % period)
+                    ref, _ = o.lfsr_bits(o.pn_mask(deg), st, N)
+                assert np.array_equal(bits[b], ref), (deg, N, enc, b)
+                pk = np.packbits(ref, bitorder="little")
+                pk = np.concatenate((pk, np.zeros((-pk.size) % 4, np.uint8))).view(np.uint32)
+                assert np.array_equal(packed[b], pk), (deg, N, enc, b)
+                if enc == 4:
+                    rs = o.soqpsk_precoder(ref)
+                else:
+                    rs = o.fsm_encode(o.TRELLISES[ENC[enc]], ref)
+                assert np.array_equal(syms[b], rs), (deg, N, enc, b, np.flatnonzero(syms[b] != rs)[:10])
+    # streaming encoder state: two calls == one call
+    g = G("g2_encode.npz")
+    stream = np.unpackbits(G("g1_pn.npz")["pn15"])
+    for n1, n2 in ((1001, 1999), (64, 33), (1, 1)):
+        st = np.zeros((1, 2), np.int32)
+        a = np.zeros((1, n1), np.int8)
+        b = np.zeros((1, n2), np.int8)
+        bi = np.ascontiguousarray(stream[:n1][None])
+        ok(L.wf_bits_encode(ptr(bi), 1, n1, 0, ptr(st), None, 0, ptr(a), None))
+        bi2 = np.ascontiguousarray(stream[n1:n1 + n2][None])
+        ok(L.wf_bits_encode(ptr(bi2), 1, n2, 0, ptr(st), None, 0, ptr(b), None))
+        ref = g["SOQPSKTrellis4x2DiffEncoded"][:n1 + n2]
+        got = np.concatenate((a[0], b[0]))
+        assert np.array_equal(got, ref), (n1, n2, np.flatnonzero(got != ref)[:10])
+        assert st[0, 0] == n1 + n2
+    # generic table-driven trellis
+    for name, cols in o.TRELLISES.items():
+        card = o.trellis_bits_per_symbol(cols)
+        ns = max(max(b[2], b[3]) for c in cols for b in c) + 1
+        nxt = np.full((len(cols), ns, 1 << card), -1, np.int8)
+        out = np.zeros((len(cols), ns, 1 << card), np.int8)
+        for ci, col in enumerate(cols):
+            for (inp, ou, s, e) in col:
+                nxt[ci, s, inp], out[ci, s, inp] = e, ou
+        bi = np.ascontiguousarray(stream[:2048][None])
+        sy = np.zeros((1, 2048 // card), np.int8)
+        ok(L.wf_trellis_encode(ptr(bi), 1, 2048, ptr(nxt), ptr(out), len(cols), ns, card, None, ptr(sy), None))
+        assert np.array_equal(sy[0], g[name][:2048 // card]), name
+
+
+_MOD = {
+    "tg": ("SOQPSKTrellis4x2DiffEncoded", [0.25], o.pulse_soqpsk_tg),
+    "pcmfm": ("SimpleTrellis2", [0.7], lambda s: o.pulse_pcmfm(s, 4)),
+    "multih": ("SimpleTrellis4", [4 / 16, 5 / 16], o.pulse_multih),
+    "mil": ("SOQPSKTrellis4x2DiffEncoded", [0.25], o.pulse_soqpsk_mil),
+    "b": ("SOQPSKTrellis4x2", [0.25], o.pulse_soqpsk_b),
+}
+
+
+def modulate(syms, h, pulse, sps, dtype, derot=0.0, sigma=None, seed=0, first=0):
+    B, S = syms.shape
+    T = (S + 1) * sps
+    ld = T + (T & 1)
+    out = np.zeros((B, ld), np.complex64 if dtype == 0 else np.complex128)
+    hv, hp = darr(h)
+    pv, pp = darr(pulse)
+    ok(L.wf_cpm_modulate(ptr(syms), B, S, hp, hv.size, pp, pv.size, sps, np.pi / 4, derot, dtype, ptr(out), ld,
+                         ptr(sigma), None, seed, first, None))
+    return out[:, :T]
+
+
+def t_mod():
+    g = G("g4_modulated.npz")
+    for lab, (tre, h, pf) in _MOD.items():
+        for sps in (8, 10):
+            sy = o.fsm_encode(o.TRELLISES[tre], g["bits"])
+            ref = g[f"{lab}_{sps}"]
+            for dtype, tol in ((0, 1e-5), (1, 1e-10)):
+                s = modulate(sy[None], h, pf(sps), sps, dtype)[0]
+                err = np.max(np.abs(s - ref))
+                print(f"  mod {lab} sps={sps} dtype={dtype} max err {err:.2e}")
+                assert err < tol, (lab, sps, dtype, err)
+    # several chunks + batch
+    bits = np.unpackbits(G("g1_pn.npz")["pn15"])[:2 * 2600].reshape(2, 2600)
+    sy = np.stack([o.fsm_encode(o.TRELLISES["SOQPSKTrellis4x2DiffEncoded"], b) for b in bits])
+    for dtype, tol in ((0, 1e-5), (1, 1e-10)):
+        s = modulate(sy, [0.25], o.pulse_soqpsk_tg(8), 8, dtype)
+        for b in range(2):
+            ref = o.cpm_modulate_closed_form(sy[b], 0.25, o.pulse_soqpsk_tg(8), 8)
+            err = np.max(np.abs(s[b] - ref))
+            print(f"  mod long frame {b} dtype={dtype} max err {err:.2e}")
+            assert err < tol
+
+
+def mf(rx, taps, comb, sps, n_calls, dtype, first=0):
+    B, T = rx.shape
+    ld = T
+    n_filt, n_taps = taps.shape
+    n_out = comb.shape[0] if comb is not None else n_filt
+    ldo = n_calls + (n_calls & 1)
+    out = np.zeros((B, ldo, n_out), np.complex64 if dtype == 0 else np.complex128)
+    rx = np.ascontiguousarray(rx.astype(out.dtype))
+    tr, trp = darr(taps.real.ravel())
+    ti, tip = darr(taps.imag.ravel())
+    if not np.iscomplexobj(taps):
+        tip = None
+    cr = ci = crp = cip = None
+    if comb is not None:
+        cr, crp = darr(comb.real.ravel())
+        ci, cip = darr(comb.imag.ravel())
+    ok(L.wf_mf_bank(ptr(rx), dtype, B, T, ld, trp, tip, n_filt, n_taps, (n_taps - 1) // 2, crp, cip, n_out, sps, first,
+                    n_calls, ptr(out), ldo, None))
+    return out[:, :n_calls]
+
+
+def pam_tables(pulse, h, sps):
+    rho = o.rho_pulses(pulse, h, sps, 2)
+    d = max(r.size for r in rho)
+    taps = np.stack([np.concatenate((r, np.zeros(d - r.size))) for r in rho])
+    comb = np.conj(o.PSEUDO_SYMBOLS).T  # [3][2]
+    return taps, comb
+
+
+def t_mf():
+    g = G("g5_config1.npz")
+    pulse = o.pulse_soqpsk_tg(8)
+    rx = g["tx"] * np.exp(-1j * np.pi / 4) + g["noise"]
+    n_calls = 4095
+    for dtype, tol in ((1, 1e-9), (0, 2e-4)):
+        z = mf(rx[None], *pam_tables(pulse, 0.25, 8), 8, n_calls, dtype)[0]
+        err = np.max(np.abs(z - g["PAM_z"]))
+        print(f"  PAM bank dtype={dtype} max err {err:.2e}")
+        assert err < tol
+        z = mf(rx[None], o.pt_taps(pulse, 0.25, 8), None, 8, n_calls, dtype)[0]
+        err = np.max(np.abs(z - g["PT_z"]))
+        print(f"  PT bank dtype={dtype} max err {err:.2e}")
+        assert err < tol
+    # generic shape (sps 8, 5 complex filters of 13 taps, first instant 3)
+    rng = np.random.default_rng(0)
+    taps = rng.normal(size=(5, 13)) + 1j * rng.normal(size=(5, 13))
+    rr = rng.normal(size=(2, 1000)) + 1j * rng.normal(size=(2, 1000))
+    z = mf(rr, taps, None, 8, 100, 1, first=3)
+    for b in range(2):
+        full = np.stack([np.convolve(rr[b], t, "same") for t in taps])
+        ref = full[:, 3 + 8 * np.arange(100)].T
+        assert np.max(np.abs(z[b] - ref)) < 1e-9
+
+
+def viterbi(z, dtype, diff=1, length=2, tx_bits=None, tx_syms=None):
+    B, n_calls, _ = z.shape
+    zz = np.ascontiguousarray(z.astype(np.complex64 if dtype == 0 else np.complex128))
+    db = np.zeros((B, n_calls), np.uint8)
+    ds = np.zeros((B, n_calls), np.int8)
+    cnt = np.zeros((1, 3), np.int64)
+    packed = None
+    ldw = 0
+    S = 0
+    if tx_bits is not None:
+        S = tx_bits.shape[1]
+        pk = np.packbits(tx_bits, axis=1, bitorder="little")
+        pk = np.concatenate((pk, np.zeros((B, (-pk.shape[1]) % 4), np.uint8)), axis=1)
+        packed = np.ascontiguousarray(pk).view(np.uint32)
+        ldw = packed.shape[1]
+    ok(L.wf_viterbi_soqpsk(ptr(zz), dtype, B, n_calls, n_calls, diff, length, ptr(db), ptr(ds), ptr(packed), ldw,
+                           ptr(tx_syms), S, None, ptr(cnt), None))
+    return db, ds, cnt
+
+
+def t_vit():
+    g = G("g5_config1.npz")
+    for det in ("PT", "PAM"):
+        z = g[f"{det}_z"]
+        for dtype in (1, 0):
+            db, ds, cnt = viterbi(z[None], dtype, tx_bits=g["bits"][None], tx_syms=np.ascontiguousarray(g["symbols"][None]))
+            nb = int(np.sum(db[0] != g[f"{det}_dec_bits"]))
+            print(f"  viterbi {det} dtype={dtype}: {nb} decision mismatches; counters {cnt[0]}")
+            if dtype == 1:
+                assert nb == 0
+                assert np.array_equal(ds[0], g[f"{det}_dec_syms"])
+                assert list(cnt[0]) == [int(g[f"{det}_bit_errors"]), int(g[f"{det}_sym_errors"]), int(g[f"{det}_compared"])]
+            else:
+                assert nb <= 2
+    # other window lengths / non-differential from the G7 variants: regenerate z with the oracle
+    g7 = G("g7_variants.npz")
+    pulse = o.pulse_soqpsk_tg(8)
+    sig = float(np.sqrt(8 / (2 * 10 ** 0.8)))
+    for diff in (True, False):
+        for length in (2, 4):
+            tag = f"d{int(diff)}_l{length}"
+            r = o.soqpsk_link_frame(g7["bits"], pulse, 8, sig, noise=g7[f"noise_{tag}"], detector="PAM", length=length,
+                                    diff=diff, return_all=True)
+            db, ds, cnt = viterbi(r["z"][None], 1, int(diff), length, tx_bits=g7["bits"][None],
+                                  tx_syms=np.ascontiguousarray(r["symbols"][None]))
+            assert np.array_equal(db[0], g7[f"PAM_bits_{tag}"]), tag
+            assert np.array_equal(ds[0], g7[f"PAM_syms_{tag}"]), tag
+            assert list(cnt[0]) == list(g7[f"PAM_counts_{tag}"]), (tag, cnt)
+    # odd / long windows against the stateful oracle
+    z = g["PAM_z"][:300]
+    for length in (1, 3, 6, 16):
+        rb, rs = o.detect_soqpsk(z, length, True)
+        db, ds, _ = viterbi(z[None], 1, 1, length)
+        assert np.array_equal(db[0], rb) and np.array_equal(ds[0], rs), length
+
+
+def t_noise():
+    B, T = 4, 20000
+    out = np.zeros((B, T, 2), np.float32)
+    sig = np.array([1.0, 2.0, 0.5, 1.0], np.float32)
+    ok(L.wf_awgn_fill(ptr(out), B, T, ptr(sig), None, 1234, 0, None))
+    for b in range(B):
+        x = out[b].ravel() / sig[b]
+        print(f"  noise frame {b}: mean {x.mean():+.4f} var {x.var():.4f} kurt {np.mean(x**4):.3f}")
+        assert abs(x.mean()) < 0.03 and abs(x.var() - 1) < 0.03 and abs(np.mean(x ** 4) - 3) < 0.15
+    # sharding independence: frames 2..3 generated alone with first_frame=2
+    out2 = np.zeros((2, T, 2), np.float32)
+    ok(L.wf_awgn_fill(ptr(out2), 2, T, ptr(sig[2:].copy()), None, 1234, 2, None))
+    assert np.array_equal(out2, out[2:])
+    # fused modulate+noise == modulate then add
+    sy = o.fsm_encode(o.TRELLISES["SOQPSKTrellis4x2DiffEncoded"], G("g4_modulated.npz")["bits"])[None]
+    s1 = modulate(sy, [0.25], o.pulse_soqpsk_tg(8), 8, 0, derot=-np.pi / 4)
+    T1 = s1.shape[1]
+    sg = np.array([0.7], np.float32)
+    buf = np.ascontiguousarray(s1.copy())
+    ok(L.wf_awgn_add(ptr(buf), 0, 1, T1, T1, ptr(sg), None, 99, 5, None))
+    s2 = modulate(sy, [0.25], o.pulse_soqpsk_tg(8), 8, 0, derot=-np.pi / 4, sigma=sg, seed=99, first=5)
+    assert np.max(np.abs(buf - s2)) < 1e-6, np.max(np.abs(buf - s2))
+
+
+TESTS = {"lfsr": t_lfsr, "prbs": t_prbs, "mod": t_mod, "mf": t_mf, "vit": t_vit, "noise": t_noise}
+
+if __name__ == "__main__":
+    names = sys.argv[1:] or list(TESTS)
+    for n in names:
+        t0 = time.time()
+        print(f"[{n}]")
+        TESTS[n]()
+        print(f"[{n}] ok in {time.time() - t0:.1f}s")

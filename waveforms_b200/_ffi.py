@@ -1,0 +1,90 @@
+"""ctypes binding of the C ABI in include/wfb200.h (one prototype per entry point).
+
+``lib()`` loads waveforms_b200/_lib/libwfb200.so, building it with nvcc first when it
+is missing.  There is no CPU implementation behind these calls: when the library
+cannot be built or loaded the import fails loudly, and on a machine without an
+sm_100 device every compute call returns WF_ERR_DEVICE, surfaced as RuntimeError.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+import threading
+
+WF_F32, WF_F64 = 0, 1
+ENC_SOQPSK_DIFF, ENC_SOQPSK, ENC_BINARY, ENC_QUATERNARY, ENC_SOQPSK_TERNARY = range(5)
+
+_vp, _i32, _i64, _u64, _dbl = C.c_void_p, C.c_int, C.c_int64, C.c_uint64, C.c_double
+
+# name -> (restype, argtypes); order and meaning exactly as in include/wfb200.h
+PROTOTYPES = {
+    "wf_abi_version": (_i32, []),
+    "wf_last_error_string": (C.c_char_p, []),
+    "wf_device_check": (_i32, []),
+    "wf_lfsr_mask": (_u64, [_i32]),
+    "wf_lfsr_jump": (_u64, [_u64, _i32, _u64, _u64]),
+    "wf_prbs_encode": (_i32, [_u64, _i32, _u64, _u64, _vp, _u64, _i64, _i64, _i32, _vp, _vp, _vp, _i64, _vp, _vp]),
+    "wf_bits_encode": (_i32, [_vp, _i64, _i64, _i32, _vp, _vp, _i64, _vp, _vp]),
+    "wf_trellis_encode": (_i32, [_vp, _i64, _i64, _vp, _vp, _i32, _i32, _i32, _vp, _vp, _vp]),
+    "wf_cpm_modulate": (_i32, [_vp, _i64, _i64, _vp, _i32, _vp, _i32, _i32, _dbl, _dbl, _i32, _vp, _i64,
+                               _vp, _vp, _u64, _u64, _vp]),
+    "wf_awgn_add": (_i32, [_vp, _i32, _i64, _i64, _i64, _vp, _vp, _u64, _u64, _vp]),
+    "wf_awgn_fill": (_i32, [_vp, _i64, _i64, _vp, _vp, _u64, _u64, _vp]),
+    "wf_mf_bank": (_i32, [_vp, _i32, _i64, _i64, _i64, _vp, _vp, _i32, _i32, _i32, _vp, _vp, _i32, _i32, _i64, _i64,
+                          _vp, _i64, _vp]),
+    "wf_viterbi_soqpsk": (_i32, [_vp, _i32, _i64, _i64, _i64, _i32, _i32, _vp, _vp, _vp, _i64, _vp, _i64, _vp, _vp, _vp]),
+    "wf_bert": (_i32, [_vp, _vp, _i64, _vp, _vp, _i64, _i64, _i64, _i64, _vp, _vp, _vp]),
+}
+
+
+def bind(cdll: C.CDLL) -> C.CDLL:
+    """Attach the prototypes to a loaded library; AttributeError if a symbol is missing."""
+    for name, (res, args) in PROTOTYPES.items():
+        fn = getattr(cdll, name)
+        fn.restype = res
+        fn.argtypes = args
+    return cdll
+
+
+_lock = threading.Lock()
+_lib = None
+
+
+def lib_path() -> str:
+    return os.path.join(os.path.dirname(os.path.abspath(__file__)), "_lib", "libwfb200.so")
+
+
+def lib() -> C.CDLL:
+    global _lib
+    if _lib is None:
+        with _lock:
+            if _lib is None:
+                path = lib_path()
+                if not os.path.exists(path):
+                    from . import build as _build
+
+                    _build.build()
+                _lib = bind(C.CDLL(path))
+                if _lib.wf_abi_version() != 1:
+                    raise RuntimeError("libwfb200 ABI version mismatch")
+    return _lib
+
+
+class WfError(RuntimeError):
+    pass
+
+
+def check(rc: int) -> None:
+    """Raise for a negative wf_status.  WF_ERR_ARG -> ValueError, others -> WfError."""
+    if rc == 0:
+        return
+    msg = lib().wf_last_error_string().decode("utf-8", "replace")
+    if rc == -1:
+        raise ValueError(msg)
+    raise WfError(f"libwfb200 error {rc}: {msg}")
+
+
+def dbl_array(values):
+    """Host double[] argument for the small tables (pulses, taps, mod indices)."""
+    vals = [float(v) for v in values]
+    return (C.c_double * len(vals))(*vals)

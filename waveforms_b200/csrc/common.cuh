@@ -1,0 +1,102 @@
+// common.cuh -- shared host/device helpers of libwfb200 (sm_100a only).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <stdarg.h>
+#include "../../include/wfb200.h"
+
+namespace wf {
+
+// ---- per-thread error text -------------------------------------------------
+char* err_buf();
+int fail(int code, const char* fmt, ...);
+int cuda_fail(cudaError_t e, const char* where);
+
+#define WF_REQUIRE(cond, ...)                                  \
+  do {                                                         \
+    if (!(cond)) return ::wf::fail(WF_ERR_ARG, __VA_ARGS__);   \
+  } while (0)
+
+#define WF_LAUNCH_CHECK(where)                                 \
+  do {                                                         \
+    cudaError_t e__ = cudaGetLastError();                      \
+    if (e__ != cudaSuccess) return ::wf::cuda_fail(e__, where);\
+  } while (0)
+
+int require_device();  // WF_OK or WF_ERR_DEVICE (cached per device)
+int sm_count();
+
+static inline cudaStream_t as_stream(void* s) { return reinterpret_cast<cudaStream_t>(s); }
+
+// ---- Philox4x32-10 (Salmon et al., SC'11), counter-based ---------------------
+struct u32x4 { uint32_t x, y, z, w; };
+
+__host__ __device__ __forceinline__ uint32_t mulhi32(uint32_t a, uint32_t b) {
+#ifdef __CUDA_ARCH__
+  return __umulhi(a, b);
+#else
+  return (uint32_t)(((uint64_t)a * b) >> 32);
+#endif
+}
+
+__host__ __device__ __forceinline__ u32x4 philox4x32_10(u32x4 c, uint32_t k0, uint32_t k1) {
+  const uint32_t M0 = 0xD2511F53u, M1 = 0xCD9E8D57u;
+  const uint32_t W0 = 0x9E3779B9u, W1 = 0xBB67AE85u;
+#pragma unroll
+  for (int r = 0; r < 10; ++r) {
+    uint32_t hi0 = mulhi32(M0, c.x), lo0 = M0 * c.x;
+    uint32_t hi1 = mulhi32(M1, c.z), lo1 = M1 * c.z;
+    u32x4 n;
+    n.x = hi1 ^ c.y ^ k0;
+    n.y = lo1;
+    n.z = hi0 ^ c.w ^ k1;
+    n.w = lo0;
+    c = n;
+    k0 += W0;
+    k1 += W1;
+  }
+  return c;
+}
+
+// Counter layout shared by every noise kernel: results depend only on
+// (seed, point, global frame, sample pair) -- never on batching or sharding.
+__host__ __device__ __forceinline__ u32x4 noise_counter(uint64_t pair, uint64_t frame, uint32_t point) {
+  u32x4 c;
+  c.x = (uint32_t)pair;
+  c.y = (uint32_t)frame;
+  c.z = (uint32_t)(frame >> 32) ^ ((uint32_t)(pair >> 32) << 16);
+  c.w = point;
+  return c;
+}
+
+#ifdef __CUDACC__
+__device__ __forceinline__ float fast_sqrt(float x) {
+#ifdef WF_HOSTEMU
+  return sqrtf(x);
+#else
+  float r;
+  asm("sqrt.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
+  return r;
+#endif
+}
+
+// Box-Muller on two 32-bit uniforms -> one complex N(0,1)+jN(0,1) sample.
+// Uniforms are built from mantissa bits (no I2F on the XU pipe, which already
+// carries LG2/SQRT/SIN/COS).  u1's top 23 bits give x in (0,1); when they are all
+// zero (p = 2^-23) the low 9 bits refine the tail, so radii reach
+// sqrt(2 ln 2^33) = 6.76 sigma instead of clipping at 5.65.
+__device__ __forceinline__ float2 box_muller(uint32_t u1, uint32_t u2) {
+  float x = __uint_as_float(0x3F800000u | (u1 >> 9)) - 1.0f + 5.9604644775390625e-08f;  // (m + 0.5) 2^-23
+  if ((u1 >> 9) == 0u) x = ((float)(u1 & 0x1FFu) + 0.5f) * 2.3283064365386963e-10f;     // (u1 + 0.5) 2^-32
+  // r^2 = -2 ln x = -2 ln2 log2 x
+  float r = fast_sqrt(-1.3862943611198906f * __log2f(x));
+  // angle uniform in [-pi, pi): (f - 1.5) * 2 pi with f in [1,2), plus half a step
+  float ang = fmaf(__uint_as_float(0x3F800000u | (u2 >> 9)), 6.283185307179586f, -9.42477796f);
+  float s, c;
+  __sincosf(ang, &s, &c);
+  return make_float2(r * c, r * s);
+}
+#endif
+
+}  // namespace wf

@@ -1,0 +1,254 @@
+// mfbank.cu -- A8/A9 decimated matched-filter bank.
+//
+// The reference computes np.convolve(rx, taps, "same") at EVERY sample for each
+// filter and the driver loop then uses one column in sps
+// (examples/soqpsk_detection.py:134-173, :189-196).  Here only the used columns
+// are computed: for detector call i at sample n_i = first_instant + i*sps
+//     y_f[i] = sum_t rx[n_i + center - t] * taps[f][t]        (rx = 0 outside [0,T))
+//     z_r[i] = sum_f combine[r][f] * y_f[i]
+// One block = one frame x (R*128) consecutive calls.  The rx tile is staged in
+// shared memory TRANSPOSED as [n mod sps][q mod R][q / R] (q = n / sps) so that the
+// 32 lanes of a warp -- which own consecutive groups of R calls -- read
+// consecutive 8-byte words: conflict free.  Each thread keeps R calls in registers
+// so every staged sample is read once per R*(taps/sps) uses; taps are kernel
+// parameters, i.e. constant-bank operands of the FFMAs in the unrolled loop.
+// Results are staged back through shared memory and stored coalesced.
+#include "common.cuh"
+#include <string.h>
+
+namespace wf {
+
+constexpr int kMfThreads = 128;
+constexpr int kMfMaxTapEntries = 448;  // n_filt * n_taps
+constexpr int kMfMaxComb = 16;         // n_out * n_filt
+
+template <typename T> struct Cplx;
+template <> struct Cplx<float> { using type = float2; };
+template <> struct Cplx<double> { using type = double2; };
+
+template <typename T>
+struct MfParams {
+  const void* rx;
+  void* out;
+  int64_t B, Tn, ld_rx, ld_out, first_instant, n_calls;
+  int n_filt, n_taps, center, n_out, sps, cplx_taps, has_comb;
+  int qs;  // row stride of the transposed tile, in complex elements
+  T tap_re[kMfMaxTapEntries];
+  T tap_im[kMfMaxTapEntries];
+  T comb_re[kMfMaxComb];
+  T comb_im[kMfMaxComb];
+};
+
+// NT/NF/SPS > 0: compile-time shape (fully unrolled, constant-bank taps).
+// NT == 0: run-time shape (API-parity path for arbitrary banks).
+template <typename T, int SPS, int NF, int NT, bool CPLX, int R>
+__global__ void __launch_bounds__(kMfThreads)
+mf_bank_kernel(const __grid_constant__ MfParams<T> p) {
+  using C = typename Cplx<T>::type;
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  C* tile = reinterpret_cast<C*>(smem_raw);
+
+  constexpr bool CT = NT > 0;
+  const int sps = CT ? SPS : p.sps;
+  const int nt = CT ? NT : p.n_taps;
+  const int nf = CT ? NF : p.n_filt;
+  const int n_out = p.n_out;
+  const int qs = p.qs;
+  const int tid = threadIdx.x;
+  constexpr int SYM = R * kMfThreads;
+
+  const int64_t n_tiles = (p.n_calls + SYM - 1) / SYM;
+  const int64_t frame = (int64_t)blockIdx.x / n_tiles;  // consecutive blocks share a frame (halo hits L2)
+  const int64_t i0 = ((int64_t)blockIdx.x - frame * n_tiles) * SYM;
+  const int n_sym = (int)min((int64_t)SYM, p.n_calls - i0);
+  const C* rx = reinterpret_cast<const C*>(p.rx) + frame * p.ld_rx;
+  const int64_t n_lo = p.first_instant + i0 * sps + p.center - (nt - 1);
+  const int n_samp = (SYM - 1) * sps + nt;
+
+  // ---- stage the rx tile, transposed ------------------------------------------
+  for (int m = tid; m < n_samp; m += kMfThreads) {
+    const int64_t n = n_lo + m;
+    C v;
+    v.x = 0; v.y = 0;
+    if (n >= 0 && n < p.Tn) v = rx[n];
+    const int r = m % sps, q = m / sps;
+    tile[(r * R + (q % R)) * qs + q / R] = v;
+  }
+  __syncthreads();
+
+  // ---- R calls per thread ----------------------------------------------------------
+  constexpr int NFM = CT ? NF : 8;
+  T yr[R][NFM], yi[R][NFM];
+#pragma unroll
+  for (int e = 0; e < R; ++e)
+#pragma unroll
+    for (int f = 0; f < NFM; ++f) { yr[e][f] = 0; yi[e][f] = 0; }
+
+  if constexpr (CT) {
+    constexpr int NV = (R - 1) * SPS + NT;  // distinct samples this thread touches
+#pragma unroll
+    for (int v = 0; v < NV; ++v) {
+      const int r = v % SPS, c = v / SPS;
+      const C x = tile[(r * R + (c % R)) * qs + tid + c / R];
+#pragma unroll
+      for (int e = 0; e < R; ++e) {
+        const int u = v - e * SPS;
+        if (u >= 0 && u < NT) {
+          const int tt = NT - 1 - u;
+#pragma unroll
+          for (int f = 0; f < NF; ++f) {
+            const T tr = p.tap_re[f * NT + tt];
+            if (CPLX) {
+              const T ti = p.tap_im[f * NT + tt];
+              yr[e][f] = fma(x.x, tr, yr[e][f]); yr[e][f] = fma(-x.y, ti, yr[e][f]);
+              yi[e][f] = fma(x.x, ti, yi[e][f]); yi[e][f] = fma(x.y, tr, yi[e][f]);
+            } else {
+              yr[e][f] = fma(x.x, tr, yr[e][f]);
+              yi[e][f] = fma(x.y, tr, yi[e][f]);
+            }
+          }
+        }
+      }
+    }
+  } else {
+    const int nv = (R - 1) * sps + nt;
+    for (int v = 0; v < nv; ++v) {
+      const int r = v % sps, c = v / sps;
+      const C x = tile[(r * R + (c % R)) * qs + tid + c / R];
+#pragma unroll
+      for (int e = 0; e < R; ++e) {
+        const int u = v - e * sps;
+        if (u >= 0 && u < nt) {
+          const int tt = nt - 1 - u;
+          for (int f = 0; f < nf; ++f) {
+            const T tr = p.tap_re[f * nt + tt];
+            const T ti = p.cplx_taps ? p.tap_im[f * nt + tt] : (T)0;
+            yr[e][f] = fma(x.x, tr, yr[e][f]); yr[e][f] = fma(-x.y, ti, yr[e][f]);
+            yi[e][f] = fma(x.x, ti, yi[e][f]); yi[e][f] = fma(x.y, tr, yi[e][f]);
+          }
+        }
+      }
+    }
+  }
+  __syncthreads();  // every thread is done reading the rx tile; reuse it for the output
+
+  // ---- combine + stage the output tile [SYM][n_out] ----------------------------------
+#pragma unroll
+  for (int e = 0; e < R; ++e) {
+    const int s = R * tid + e;
+    if (p.has_comb) {
+      for (int r = 0; r < n_out; ++r) {
+        T zr = 0, zi = 0;
+#pragma unroll
+        for (int f = 0; f < NFM; ++f) {
+          if (f < nf) {
+            const T cr = p.comb_re[r * nf + f], ci = p.comb_im[r * nf + f];
+            zr = fma(cr, yr[e][f], zr); zr = fma(-ci, yi[e][f], zr);
+            zi = fma(cr, yi[e][f], zi); zi = fma(ci, yr[e][f], zi);
+          }
+        }
+        C z; z.x = zr; z.y = zi;
+        tile[s * n_out + r] = z;
+      }
+    } else {
+#pragma unroll
+      for (int f = 0; f < NFM; ++f) {
+        if (f < nf) { C z; z.x = yr[e][f]; z.y = yi[e][f]; tile[s * n_out + f] = z; }
+      }
+    }
+  }
+  __syncthreads();
+  C* out = reinterpret_cast<C*>(p.out) + (frame * p.ld_out + i0) * n_out;
+  const int n_el = n_sym * n_out;
+  for (int k = tid; k < n_el; k += kMfThreads) out[k] = tile[k];
+}
+
+template <typename T>
+static size_t mf_smem_bytes(int sps, int nt, int R, int n_out, int& qs) {
+  const int SYM = R * kMfThreads;
+  const int qmax = ((SYM - 1) * sps + nt - 1) / sps;  // largest q
+  qs = qmax / R + 2;
+  // 2*qs*R == 4 (mod 32) words keeps the transposing stores conflict free for sps = 8 (float)
+  for (int guard = 0; guard < 16 && (qs * R) % 16 != 2; ++guard) ++qs;
+  size_t in_bytes = (size_t)sps * R * qs * 2 * sizeof(T);
+  size_t out_bytes = (size_t)SYM * n_out * 2 * sizeof(T);
+  return in_bytes > out_bytes ? in_bytes : out_bytes;
+}
+
+template <typename T>
+static int launch_mf(const void* d_rx, int64_t B, int64_t Tn, int64_t ld_rx, const double* taps_re,
+                     const double* taps_im, int n_filt, int n_taps, int center, const double* comb_re,
+                     const double* comb_im, int n_out, int sps, int64_t first_instant, int64_t n_calls,
+                     void* d_out, int64_t ld_out, cudaStream_t stream) {
+  MfParams<T> p;
+  memset(&p, 0, sizeof(p));
+  p.rx = d_rx; p.out = d_out; p.B = B; p.Tn = Tn; p.ld_rx = ld_rx; p.ld_out = ld_out;
+  p.first_instant = first_instant; p.n_calls = n_calls;
+  p.n_filt = n_filt; p.n_taps = n_taps; p.center = center; p.n_out = n_out; p.sps = sps;
+  p.cplx_taps = taps_im != nullptr; p.has_comb = comb_re != nullptr;
+  for (int i = 0; i < n_filt * n_taps; ++i) {
+    p.tap_re[i] = (T)taps_re[i];
+    p.tap_im[i] = taps_im ? (T)taps_im[i] : (T)0;
+  }
+  if (comb_re)
+    for (int i = 0; i < n_out * n_filt; ++i) {
+      p.comb_re[i] = (T)comb_re[i];
+      p.comb_im[i] = comb_im ? (T)comb_im[i] : (T)0;
+    }
+
+#define WF_MF_CASE(SPS_, NF_, NT_, CPLX_, R_)                                                         \
+  do {                                                                                                \
+    int qs;                                                                                           \
+    size_t sm = mf_smem_bytes<T>(sps, n_taps, R_, n_out, qs);                                         \
+    p.qs = qs;                                                                                        \
+    auto kfn = mf_bank_kernel<T, SPS_, NF_, NT_, CPLX_, R_>;                                          \
+    if (sm > 48 * 1024) {                                                                             \
+      cudaError_t e = cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm);\
+      if (e != cudaSuccess) return cuda_fail(e, "cudaFuncSetAttribute(mf_bank_kernel)");              \
+    }                                                                                                 \
+    const int SYM = R_ * kMfThreads;                                                                  \
+    dim3 grid((unsigned)(((n_calls + SYM - 1) / SYM) * B));                                           \
+    kfn<<<grid, kMfThreads, sm, stream>>>(p);                                                         \
+  } while (0)
+
+  const bool real_taps = taps_im == nullptr;
+  if (sps == 8 && n_filt == 2 && n_taps == 73 && real_taps) WF_MF_CASE(8, 2, 73, false, 2);       // PAM bank, TG
+  else if (sps == 8 && n_filt == 3 && n_taps == 9 && !real_taps) WF_MF_CASE(8, 3, 9, true, 2);   // PT bank
+  else if (sps == 10 && n_filt == 2 && n_taps == 91 && real_taps) WF_MF_CASE(10, 2, 91, false, 2);
+  else if (sps == 10 && n_filt == 3 && n_taps == 11 && !real_taps) WF_MF_CASE(10, 3, 11, true, 2);
+  else WF_MF_CASE(0, 0, 0, true, 1);
+#undef WF_MF_CASE
+  WF_LAUNCH_CHECK("mf_bank_kernel");
+  return WF_OK;
+}
+
+}  // namespace wf
+
+extern "C" {
+
+int wf_mf_bank(const void* d_rx, int dtype, int64_t B, int64_t T, int64_t ld_rx, const double* taps_re,
+               const double* taps_im, int n_filt, int n_taps, int center, const double* combine_re,
+               const double* combine_im, int n_out, int sps, int64_t first_instant, int64_t n_calls,
+               void* d_out, int64_t ld_out, void* stream) {
+  using namespace wf;
+  WF_REQUIRE(B >= 0 && T >= 0 && n_calls >= 0, "negative shape");
+  WF_REQUIRE(dtype == WF_F32 || dtype == WF_F64, "dtype must be WF_F32 or WF_F64");
+  WF_REQUIRE(taps_re && n_filt >= 1 && n_filt <= 8 && n_taps >= 1, "bad filter bank shape (1..8 filters)");
+  WF_REQUIRE(n_filt * n_taps <= kMfMaxTapEntries, "filter bank has %d taps in total (max %d)", n_filt * n_taps, kMfMaxTapEntries);
+  WF_REQUIRE(sps >= 1 && sps <= 64, "sps=%d outside 1..64", sps);
+  WF_REQUIRE(ld_rx >= T && ld_out >= n_calls, "leading dimension too small");
+  if (combine_re) WF_REQUIRE(n_out >= 1 && n_out * n_filt <= kMfMaxComb, "combine matrix too large");
+  else WF_REQUIRE(n_out == n_filt, "n_out must equal n_filt without a combine matrix");
+  WF_REQUIRE(B * ((n_calls + 127) / 128) <= 0x7FFFFFFF, "batch too large for one launch; split the call");
+  int rc;
+  if ((rc = require_device())) return rc;
+  if (B == 0 || n_calls == 0) return WF_OK;
+  WF_REQUIRE(d_rx && d_out, "NULL device pointer");
+  if (dtype == WF_F32)
+    return launch_mf<float>(d_rx, B, T, ld_rx, taps_re, taps_im, n_filt, n_taps, center, combine_re, combine_im, n_out,
+                            sps, first_instant, n_calls, d_out, ld_out, as_stream(stream));
+  return launch_mf<double>(d_rx, B, T, ld_rx, taps_re, taps_im, n_filt, n_taps, center, combine_re, combine_im, n_out,
+                           sps, first_instant, n_calls, d_out, ld_out, as_stream(stream));
+}
+
+}  // extern "C"

@@ -1,0 +1,380 @@
+// modulate.cu -- A6 CPM modulator (cpm/modulate.py:57-101) with optional fused
+// A7 AWGN (noise.py:8-32), plus the stand-alone AWGN kernels.
+//
+// The reference up-samples h*alpha, convolves with the frequency pulse ("same"),
+// accumulates sample by sample and takes exp(j phase).  Here the accumulation is
+// closed-form: with Q the cumulative pulse, off=(K-1)//2,
+//   revs[n] = sum_k w_k ( Q[clip(n+off+1-(k+1)sps, 0, K)] - Q[clip(off-(k+1)sps, 0, K)] ),  w_k = alpha_k h_k.
+// Symbols whose pulse is complete contribute w_k Q[K]: that part is an exact
+// 64-bit fixed-point prefix sum in turns (wraps mod 1 turn, order independent,
+// no drift over long frames); only the J = ceil((K-1)/sps) newest symbols need
+// Q-table terms per sample.  One block per frame walks the frame in chunks of
+// 1024 symbols; threads own sample PAIRS so every store is one 128-bit word and
+// a warp store covers 512 contiguous bytes.
+#include "common.cuh"
+#include <math.h>
+#include <string.h>
+
+namespace wf {
+
+constexpr int kModThreads = 256;
+constexpr int kChunkSyms = 1024;
+constexpr int kRing = 2048;       // power of two >= chunk + look-back + look-ahead
+constexpr int kQMax = 768;        // padded Q table entries
+constexpr int kScanPer = 2;       // symbols per thread per scan step (512 per step)
+constexpr int kMaxH = 8;
+
+template <typename T> struct ModTraits;
+template <> struct ModTraits<float> {
+  using Fix = uint32_t;  // top 32 bits of the 64-bit turn fraction
+  using Vec2 = float2;
+  __device__ static __forceinline__ Fix narrow(uint64_t f) { return (uint32_t)(f >> 32); }
+  __device__ static __forceinline__ float turns(Fix f) { return (float)(int32_t)f * 2.3283064365386963e-10f; }
+  __device__ static __forceinline__ void unit(float t, float& c, float& s) {
+    t -= (t + 12582912.f) - 12582912.f;  // t - rint(t), |t| < 2^22
+    __sincosf(t * 6.283185307179586f, &s, &c);
+  }
+};
+template <> struct ModTraits<double> {
+  using Fix = uint64_t;
+  using Vec2 = double2;
+  __device__ static __forceinline__ Fix narrow(uint64_t f) { return f; }
+  __device__ static __forceinline__ double turns(Fix f) { return (double)(int64_t)f * 5.421010862427522e-20; }
+  __device__ static __forceinline__ void unit(double t, double& c, double& s) {
+    t -= rint(t);
+    sincospi(2.0 * t, &s, &c);
+  }
+};
+
+template <typename T>
+struct ModParams {
+  const int8_t* syms;
+  void* out;
+  const float* sigma;
+  const int32_t* point;
+  int64_t B, S, Tn, ld_out;
+  uint64_t seed, first_frame;
+  int n_h, K, sps, off, J;
+  T phase0_turns;
+  T inv_sps;
+  T hw[kMaxH];
+  uint64_t hfix[kMaxH];
+  T q[kQMax];  // Q[0..K], padded with Q[K]
+};
+
+// SPS > 0: compile-time samples/symbol; JT > 0: compile-time J with the thread's
+// Q coefficients hoisted into registers (needs (2*threads) % SPS == 0, off even).
+template <typename T, int SPS, int JT, bool NOISE>
+__global__ void __launch_bounds__(kModThreads)
+cpm_modulate_kernel(const __grid_constant__ ModParams<T> p) {
+  constexpr int SPSD = SPS > 0 ? SPS : 1;  // dead-code divisor when SPS is a run-time value
+  using Tr = ModTraits<T>;
+  using Fix = typename Tr::Fix;
+  using Vec2 = typename Tr::Vec2;
+  __shared__ T w_s[kRing];
+  __shared__ Fix f_s[kRing];
+  __shared__ uint64_t warp_tot[kModThreads / 32];
+  __shared__ T c0_s;
+
+  const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+  const int64_t frame = blockIdx.x;
+  const int sps = SPS > 0 ? SPS : p.sps;
+  const int J = JT > 0 ? JT : p.J;
+  const int off = p.off;
+  const int64_t S = p.S, Tn = p.Tn;
+  const int8_t* sy = p.syms + frame * S;
+  Vec2* out = reinterpret_cast<Vec2*>(p.out) + frame * p.ld_out;
+  const bool vec_ok = ((p.ld_out & 1) == 0) && ((reinterpret_cast<uintptr_t>(p.out) & (2 * sizeof(Vec2) - 1)) == 0);
+
+  // zero the ring (covers symbols k < 0 and F[m <= 0])
+  for (int i = tid; i < kRing; i += kModThreads) { w_s[i] = (T)0; f_s[i] = 0; }
+  if (tid == 0) {
+    // frame-start truncation of "same" convolution: sum_k w_k Q[clip(off-(k+1)sps,0,K)]
+    T c0 = 0;
+    for (int64_t k = 0; k < S && (k + 1) * sps < off; ++k) {
+      int idx = off - (int)(k + 1) * sps;
+      if (idx > p.K) idx = p.K;
+      c0 += (T)sy[k] * p.hw[k % p.n_h] * p.q[idx];
+    }
+    c0_s = c0;
+  }
+
+  float sig = 0.f;
+  uint32_t pt = 0;
+  uint64_t gframe = 0;
+  if (NOISE) {
+    sig = p.sigma[frame];
+    pt = p.point ? (uint32_t)p.point[frame] : 0u;
+    gframe = p.first_frame + (uint64_t)frame;
+  }
+
+  // hoisted Q coefficients (fast path): rho of this thread's even sample is fixed
+  T qa[JT > 0 ? JT : 1], qb[JT > 0 ? JT : 1];
+  if (JT > 0) {
+    const int rho = (2 * tid + off) % SPSD;  // even sample; odd sample is rho + 1 (same symbol since rho even < SPS-1)
+#pragma unroll
+    for (int j = 0; j < JT; ++j) { qa[j] = p.q[rho + 1 + j * SPSD]; qb[j] = p.q[rho + 2 + j * SPSD]; }
+  }
+
+  uint64_t carry = 0;           // F[scanned]
+  int64_t scanned = 0;          // symbols [0, scanned) are in the ring
+  const int ahead = off / sps + 2;
+  __syncthreads();
+  const T c0 = c0_s;
+
+  for (int64_t cs = 0; cs * sps < Tn; cs += kChunkSyms) {
+    // ---- (a) extend the scan to symbol cs + chunk + ahead ----------------------
+    const int64_t want = cs + kChunkSyms + ahead;
+    while (scanned < want) {  // uniform across the block
+      // each thread takes kScanPer consecutive symbols; the ring then holds
+      // [cs - J, cs + 1536): never more than kRing entries (J + ahead <= 512)
+      const int64_t k0 = scanned + kScanPer * (int64_t)tid;
+      uint64_t inc[kScanPer];
+      T wv[kScanPer];
+      uint64_t run = 0;
+#pragma unroll
+      for (int i = 0; i < kScanPer; ++i) {
+        const int64_t k = k0 + i;
+        int a = (k < S) ? (int)sy[k] : 0;
+        int hi = (int)(k % p.n_h);
+        wv[i] = (T)a * p.hw[hi];
+        run += (uint64_t)((int64_t)a) * p.hfix[hi];
+        inc[i] = run;
+      }
+      // block-wide exclusive scan of `run`
+      uint64_t incl = run;
+#pragma unroll
+      for (int s = 1; s < 32; s <<= 1) {
+        uint64_t t = __shfl_up_sync(0xFFFFFFFFu, incl, s);
+        if (lane >= s) incl += t;
+      }
+      if (lane == 31) warp_tot[wid] = incl;
+      __syncthreads();
+      uint64_t base = carry;
+      for (int i = 0; i < wid; ++i) base += warp_tot[i];
+      uint64_t total = 0;
+      for (int i = 0; i < kModThreads / 32; ++i) total += warp_tot[i];
+      base += incl - run;
+#pragma unroll
+      for (int i = 0; i < kScanPer; ++i) {
+        const int64_t k = k0 + i;
+        w_s[k & (kRing - 1)] = wv[i];
+        f_s[(k + 1) & (kRing - 1)] = Tr::narrow(base + inc[i]);  // F[k+1]
+      }
+      carry += total;
+      scanned += kScanPer * kModThreads;
+      __syncthreads();
+    }
+
+    // ---- (b) samples of symbols-intervals [cs, cs + chunk) --------------------
+    const int64_t n_base = cs * sps;
+    const int npairs = kChunkSyms * sps / 2;
+    for (int q = tid; q < npairs; q += kModThreads) {
+      const int64_t n = n_base + 2 * (int64_t)q;
+      if (n >= Tn) break;
+      T ph[2];
+      if (JT > 0) {
+        const int64_t a = n + off;
+        const int64_t khi = a / SPSD - 1;
+        T acc0 = 0, acc1 = 0;
+#pragma unroll
+        for (int j = 0; j < JT; ++j) {
+          const T w = w_s[(khi - j) & (kRing - 1)];
+          acc0 = fma(w, qa[j], acc0);
+          acc1 = fma(w, qb[j], acc1);
+        }
+        const T old = Tr::turns(f_s[(khi - JT + 1) & (kRing - 1)]) + p.phase0_turns;
+        ph[0] = fma(acc0 - c0, p.inv_sps, old);
+        ph[1] = fma(acc1 - c0, p.inv_sps, old);
+      } else {
+#pragma unroll
+        for (int e = 0; e < 2; ++e) {
+          const int64_t a = n + e + off;
+          const int64_t khi = a / sps - 1;
+          const int rho = (int)(a - (khi + 1) * sps);
+          T acc = 0;
+          for (int j = 0; j < J; ++j) acc = fma(w_s[(khi - j) & (kRing - 1)], p.q[rho + 1 + j * sps], acc);
+          const T old = Tr::turns(f_s[(khi - J + 1) & (kRing - 1)]) + p.phase0_turns;
+          ph[e] = fma(acc - c0, p.inv_sps, old);
+        }
+      }
+      T c[2], s[2];
+      Tr::unit(ph[0], c[0], s[0]);
+      Tr::unit(ph[1], c[1], s[1]);
+      if (NOISE) {
+        u32x4 r = philox4x32_10(noise_counter((uint64_t)(n >> 1), gframe, pt), (uint32_t)p.seed, (uint32_t)(p.seed >> 32));
+        float2 g0 = box_muller(r.x, r.y), g1 = box_muller(r.z, r.w);
+        c[0] += (T)(sig * g0.x); s[0] += (T)(sig * g0.y);
+        c[1] += (T)(sig * g1.x); s[1] += (T)(sig * g1.y);
+      }
+      if (vec_ok && n + 1 < Tn) {
+        if (sizeof(T) == 4) {
+          *reinterpret_cast<float4*>(out + n) = make_float4((float)c[0], (float)s[0], (float)c[1], (float)s[1]);
+        } else {
+          double2* o = reinterpret_cast<double2*>(out + n);
+          o[0] = make_double2((double)c[0], (double)s[0]);
+          o[1] = make_double2((double)c[1], (double)s[1]);
+        }
+      } else {
+        Vec2 v0; v0.x = c[0]; v0.y = s[0];
+        out[n] = v0;
+        if (n + 1 < Tn) { Vec2 v1; v1.x = c[1]; v1.y = s[1]; out[n + 1] = v1; }
+      }
+    }
+    // next chunk's scan starts with a __syncthreads-protected phase; ring slots it
+    // overwrites are older than anything chunk `cs` reads (kRing >= 2*chunk).
+  }
+}
+
+// ---------------------------------------------------------------------------
+// Stand-alone AWGN: in-place add / fill.  One thread per sample pair, grid-stride.
+// ---------------------------------------------------------------------------
+template <typename T, bool ADD>
+__global__ void __launch_bounds__(256)
+awgn_kernel(T* __restrict__ sig, int64_t B, int64_t Tn, int64_t ld, const float* __restrict__ sigma,
+            const int32_t* __restrict__ point, uint64_t seed, uint64_t first_frame) {
+  const int64_t pairs_per_frame = (Tn + 1) >> 1;
+  const int64_t total = B * pairs_per_frame;
+  const bool vec_ok = ((ld & 1) == 0) && ((reinterpret_cast<uintptr_t>(sig) & (4 * sizeof(T) - 1)) == 0);
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+    const int64_t b = i / pairs_per_frame;
+    const int64_t pr = i - b * pairs_per_frame;
+    const int64_t n = pr << 1;
+    const float sg = sigma ? sigma[b] : 1.0f;
+    const uint32_t pt = point ? (uint32_t)point[b] : 0u;
+    u32x4 r = philox4x32_10(noise_counter((uint64_t)pr, first_frame + (uint64_t)b, pt), (uint32_t)seed, (uint32_t)(seed >> 32));
+    float2 g0 = box_muller(r.x, r.y), g1 = box_muller(r.z, r.w);
+    T* row = sig + 2 * (b * ld + n);
+    if (vec_ok && n + 1 < Tn && sizeof(T) == 4) {
+      float4* q = reinterpret_cast<float4*>(row);
+      float4 v = ADD ? *q : make_float4(0.f, 0.f, 0.f, 0.f);
+      v.x += sg * g0.x; v.y += sg * g0.y; v.z += sg * g1.x; v.w += sg * g1.y;
+      *q = v;
+    } else {
+      row[0] = (ADD ? row[0] : (T)0) + (T)(sg * g0.x);
+      row[1] = (ADD ? row[1] : (T)0) + (T)(sg * g0.y);
+      if (n + 1 < Tn) {
+        row[2] = (ADD ? row[2] : (T)0) + (T)(sg * g1.x);
+        row[3] = (ADD ? row[3] : (T)0) + (T)(sg * g1.y);
+      }
+    }
+  }
+}
+
+template <typename T>
+static int launch_modulate(const int8_t* d_syms, int64_t B, int64_t S, const double* mod_index, int n_h,
+                           const double* pulse, int K, int sps, double initial_phase, double derotate,
+                           void* d_out, int64_t ld_out, const float* d_sigma, const int32_t* d_point,
+                           uint64_t seed, uint64_t first_frame, cudaStream_t stream) {
+  ModParams<T> p;
+  memset(&p, 0, sizeof(p));
+  p.syms = d_syms; p.out = d_out; p.sigma = d_sigma; p.point = d_point;
+  p.B = B; p.S = S; p.Tn = (S + 1) * sps; p.ld_out = ld_out;
+  p.seed = seed; p.first_frame = first_frame;
+  p.n_h = n_h; p.K = K; p.sps = sps; p.off = (K - 1) / 2;
+  p.J = (K - 1 + sps - 1) / sps;
+  if (p.J < 1) p.J = 1;
+  WF_REQUIRE(p.J * sps + 1 <= kQMax, "pulse too long: K=%d at sps=%d needs %d table entries (max %d)", K, sps, p.J * sps + 1, kQMax);
+  WF_REQUIRE(p.J + p.off / sps + 2 <= 512, "pulse look-back too long for the symbol ring");
+  // cumulative pulse in long double, then narrowed once
+  long double acc = 0;
+  p.q[0] = (T)0;
+  for (int i = 0; i < K; ++i) { acc += (long double)pulse[i]; p.q[i + 1] = (T)acc; }
+  const long double qK = acc;
+  for (int i = K + 1; i < kQMax; ++i) p.q[i] = (T)qK;
+  for (int i = 0; i < n_h; ++i) {
+    p.hw[i] = (T)mod_index[i];
+    long double turns = (long double)mod_index[i] * qK / (long double)sps;  // per unit alpha
+    turns -= floorl(turns);                                                  // [0,1)
+    long double scaled = turns * 18446744073709551616.0L;                    // 2^64
+    uint64_t fx = (scaled >= 18446744073709551615.0L) ? 0ull : (uint64_t)(scaled + 0.5L);
+    p.hfix[i] = fx;
+  }
+  const double two_pi = 6.283185307179586476925286766559;
+  double ph0 = (initial_phase + derotate) / two_pi;
+  p.phase0_turns = (T)(ph0 - floor(ph0 + 0.5));
+  p.inv_sps = (T)(1.0 / (double)sps);
+  const bool noise = d_sigma != nullptr;
+  const dim3 grid((unsigned)B), block(kModThreads);
+  const bool fast8 = (sps == 8) && (p.off % 2 == 0);
+#define WF_MOD_LAUNCH(SPS_, JT_)                                                            \
+  do {                                                                                      \
+    if (noise) cpm_modulate_kernel<T, SPS_, JT_, true><<<grid, block, 0, stream>>>(p);     \
+    else cpm_modulate_kernel<T, SPS_, JT_, false><<<grid, block, 0, stream>>>(p);          \
+  } while (0)
+  if (fast8 && p.J == 8) WF_MOD_LAUNCH(8, 8);
+  else if (fast8 && p.J == 3) WF_MOD_LAUNCH(8, 3);
+  else if (fast8 && p.J == 1) WF_MOD_LAUNCH(8, 1);
+  else if (sps == 8) WF_MOD_LAUNCH(8, 0);
+  else if (sps == 10) WF_MOD_LAUNCH(10, 0);
+  else WF_MOD_LAUNCH(0, 0);
+#undef WF_MOD_LAUNCH
+  WF_LAUNCH_CHECK("cpm_modulate_kernel");
+  return WF_OK;
+}
+
+}  // namespace wf
+
+extern "C" {
+
+int wf_cpm_modulate(const int8_t* d_syms, int64_t B, int64_t S, const double* mod_index, int n_h,
+                    const double* pulse, int K, int sps, double initial_phase, double derotate,
+                    int dtype, void* d_out, int64_t ld_out, const float* d_sigma, const int32_t* d_point,
+                    uint64_t seed, uint64_t first_frame, void* stream) {
+  using namespace wf;
+  WF_REQUIRE(B >= 0 && S >= 0, "negative batch or symbol count");
+  WF_REQUIRE(sps >= 1 && sps <= 64, "sps=%d outside 1..64", sps);
+  WF_REQUIRE(K >= 1 && pulse, "empty pulse filter");
+  WF_REQUIRE(n_h >= 1 && n_h <= kMaxH && mod_index, "n_h=%d outside 1..%d", n_h, kMaxH);
+  WF_REQUIRE(dtype == WF_F32 || dtype == WF_F64, "dtype must be WF_F32 or WF_F64");
+  WF_REQUIRE(ld_out >= (S + 1) * sps, "ld_out smaller than (S+1)*sps");
+  WF_REQUIRE(B <= 0x7FFFFFFF, "batch too large for one launch");
+  int rc;
+  if ((rc = require_device())) return rc;
+  if (B == 0) return WF_OK;
+  WF_REQUIRE(d_syms || S == 0, "d_syms is NULL");
+  WF_REQUIRE(d_out, "d_out is NULL");
+  if (dtype == WF_F32)
+    return launch_modulate<float>(d_syms, B, S, mod_index, n_h, pulse, K, sps, initial_phase, derotate, d_out, ld_out,
+                                  d_sigma, d_point, seed, first_frame, as_stream(stream));
+  return launch_modulate<double>(d_syms, B, S, mod_index, n_h, pulse, K, sps, initial_phase, derotate, d_out, ld_out,
+                                 d_sigma, d_point, seed, first_frame, as_stream(stream));
+}
+
+static int awgn_common(void* d_sig, int dtype, int64_t B, int64_t T, int64_t ld, const float* d_sigma,
+                       const int32_t* d_point, uint64_t seed, uint64_t first_frame, void* stream, bool add) {
+  using namespace wf;
+  WF_REQUIRE(B >= 0 && T >= 0 && ld >= T, "bad AWGN shape");
+  WF_REQUIRE(dtype == WF_F32 || dtype == WF_F64, "dtype must be WF_F32 or WF_F64");
+  int rc;
+  if ((rc = require_device())) return rc;
+  if (B == 0 || T == 0) return WF_OK;
+  WF_REQUIRE(d_sig, "signal pointer is NULL");
+  const int64_t total = B * ((T + 1) / 2);
+  int64_t blocks = (total + 255) / 256;
+  const int64_t cap = (int64_t)sm_count() * 16;
+  if (blocks > cap) blocks = cap;
+  cudaStream_t st = as_stream(stream);
+  if (dtype == WF_F32) {
+    if (add) awgn_kernel<float, true><<<(unsigned)blocks, 256, 0, st>>>((float*)d_sig, B, T, ld, d_sigma, d_point, seed, first_frame);
+    else awgn_kernel<float, false><<<(unsigned)blocks, 256, 0, st>>>((float*)d_sig, B, T, ld, d_sigma, d_point, seed, first_frame);
+  } else {
+    if (add) awgn_kernel<double, true><<<(unsigned)blocks, 256, 0, st>>>((double*)d_sig, B, T, ld, d_sigma, d_point, seed, first_frame);
+    else awgn_kernel<double, false><<<(unsigned)blocks, 256, 0, st>>>((double*)d_sig, B, T, ld, d_sigma, d_point, seed, first_frame);
+  }
+  WF_LAUNCH_CHECK("awgn_kernel");
+  return WF_OK;
+}
+
+int wf_awgn_add(void* d_sig, int dtype, int64_t B, int64_t T, int64_t ld, const float* d_sigma,
+                const int32_t* d_point, uint64_t seed, uint64_t first_frame, void* stream) {
+  WF_REQUIRE(d_sigma, "d_sigma is NULL");
+  return awgn_common(d_sig, dtype, B, T, ld, d_sigma, d_point, seed, first_frame, stream, true);
+}
+
+int wf_awgn_fill(float* d_out, int64_t B, int64_t T, const float* d_sigma, const int32_t* d_point,
+                 uint64_t seed, uint64_t first_frame, void* stream) {
+  return awgn_common(d_out, WF_F32, B, T, T, d_sigma, d_point, seed, first_frame, stream, false);
+}
+
+}  // extern "C"
