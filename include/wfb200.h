@@ -117,6 +117,16 @@ WF_API int wf_cpm_modulate(const int8_t* d_syms, int64_t B, int64_t S,
                     const float* d_sigma, const int32_t* d_point,
                     uint64_t seed, uint64_t first_frame, void* stream);
 
+/* frequency_modulate(freq_pulses, sps, initial_phase) (cpm/modulate.py:28-54) for B rows
+ * of arbitrary per-sample frequency pulses d_freq double[B][ld_in]:
+ * out[n] = exp(j(((sum_{m<=n} f[m]) mod sps) * 2pi/sps + initial_phase)). */
+WF_API int wf_frequency_modulate(const double* d_freq, int64_t B, int64_t T, int64_t ld_in, int sps,
+                                 double initial_phase, int dtype, void* d_out, int64_t ld_out, void* stream);
+
+/* phase_modulate(phase, sensitivity) (cpm/modulate.py:12-25): exp(j * sensitivity * phase[i]) */
+WF_API int wf_phase_modulate(const double* d_phase, int64_t n, double sensitivity, int dtype, void* d_out,
+                             void* stream);
+
 /* generate_complex_awgn(sigma, size) added in place: d_sig[b][n] += sigma[b] *
  * (N(0,1) + j N(0,1)).  Philox4x32-10, key = seed, counter = (n/2, global frame
  * first_frame+b, point d_point[b] (0 if NULL), 0): two complex samples per
@@ -154,13 +164,16 @@ WF_API int wf_mf_bank(const void* d_rx, int dtype, int64_t B, int64_t T, int64_t
  * compared with d_tx_packed (bits, wf_prbs_encode layout) and d_tx_syms
  * int8[B][S]; n_cmp = min(S, n_calls-length) per frame; adds to
  * d_counters int64[n_points][3] = (bit errors, symbol errors, compared) at row
- * d_point[b] (row 0 if NULL). */
+ * d_point[b] (row 0 if NULL).
+ * d_state (NULL = fresh detector per frame): real[B][5 + 8*length] of the z element
+ * type = (call parity, metrics[:,0], bi_history) carried in and out, so a stream can
+ * be detected in chunks exactly like repeated .iteration() calls (algorithm.py:25-42,100). */
 WF_API int wf_viterbi_soqpsk(const void* d_z, int dtype, int64_t B, int64_t n_calls, int64_t ld_z,
                       int diff, int length,
                       uint8_t* d_dec_bits, int8_t* d_dec_syms,
                       const uint32_t* d_tx_packed, int64_t ld_words,
                       const int8_t* d_tx_syms, int64_t S,
-                      const int32_t* d_point, int64_t* d_counters, void* stream);
+                      const int32_t* d_point, int64_t* d_counters, void* d_state, void* stream);
 
 /* stand-alone error count of unpacked decisions (soqpsk_detection.py:200-209):
  * drops the first `skip` decisions of each frame, compares n_cmp of them. */

@@ -110,9 +110,21 @@ def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--out", default=os.path.join(os.path.dirname(__file__), "..", "tests", "golden"))
     ap.add_argument("--skip-example", action="store_true")
+    ap.add_argument("--only-trellis", action="store_true", help="write only g9_trellis.npz")
     a = ap.parse_args()
     os.makedirs(a.out, exist_ok=True)
     sv = lambda name, **kw: np.savez_compressed(os.path.join(a.out, name), **kw)  # noqa: E731
+
+    # G9: the reference's trellis tables, branch order included (model.py:179-293)
+    g9 = {}
+    for name in ("SOQPSKTrellis8x1", "SOQPSKTrellis4x2", "SOQPSKTrellis4x2DiffEncoded", "SimpleTrellis2", "SimpleTrellis4"):
+        t = getattr(tm, name)
+        g9[name] = np.array([[(b.inp, b.out, b.start, b.end) for b in col] for col in t.branches], dtype=np.int64)
+        g9[name + "_shape"] = np.array([t.columns, t.states, t.branches_per_column, t.input_cardinality,
+                                        t.output_cardinality])
+    sv("g9_trellis.npz", **g9)
+    if a.only_trellis:
+        return
 
     # G1: PN bits + masks
     g1 = {"masks": np.array([generate_mask(d) for d in range(2, 65)], dtype=np.uint64)}

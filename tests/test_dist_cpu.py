@@ -1,0 +1,73 @@
+"""CPU, world_size 2, gloo: the multi-GPU path of LinkSimulator.sweep -- contiguous frame
+shards per rank, then a SUM all-reduce of the counter table -- with the per-rank kernel
+chain replaced by a deterministic stand-in (no GPU here).  The union over ranks must be
+identical to a single-rank run, for even and uneven splits."""
+import os
+import socket
+
+import numpy as np
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+from waveforms_b200 import linksim
+
+
+def _fake_run(self, ebn0_db, n_frames, first_frame=0):
+    """Counters that depend on every (point, frame) pair individually, like the real chain."""
+    eb = np.atleast_1d(np.asarray(ebn0_db, dtype=np.float64))
+    out = np.zeros((eb.size, 3), dtype=np.int64)
+    for p in range(eb.size):
+        f = np.arange(first_frame, first_frame + n_frames, dtype=np.int64)
+        out[p, 0] = int(np.sum((f * 2654435761 + p * 40503) % 97))
+        out[p, 1] = int(np.sum((f * 40503 + p) % 89))
+        out[p, 2] = n_frames * 4093
+    return out
+
+
+def _worker(rank, world, port, n_frames, q):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    linksim.LinkSimulator.run = _fake_run
+    sim = object.__new__(linksim.LinkSimulator)
+    sim.device = "cpu"
+    got = sim.sweep([0.0, 6.0, 12.0], n_frames, first_frame=5)
+    q.put((rank, got))
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+def _free_port():
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        return s.getsockname()[1]
+
+
+def _run_world(n_frames, world=2):
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_worker, args=(r, world, port, n_frames, q)) for r in range(world)]
+    for p in procs:
+        p.start()
+    res = dict(q.get(timeout=120) for _ in range(world))
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    return res
+
+
+def test_sweep_two_ranks_equals_one_rank():
+    for n_frames in (64, 7, 1):
+        want = _fake_run(None, [0.0, 6.0, 12.0], n_frames, 5)
+        res = _run_world(n_frames)
+        assert np.array_equal(res[0], want) and np.array_equal(res[1], want), n_frames
+
+
+def test_sweep_without_process_group_is_run():
+    linksim_run = linksim.LinkSimulator.run
+    try:
+        linksim.LinkSimulator.run = _fake_run
+        sim = object.__new__(linksim.LinkSimulator)
+        assert np.array_equal(sim.sweep([3.0], 10, 2), _fake_run(None, [3.0], 10, 2))
+    finally:
+        linksim.LinkSimulator.run = linksim_run

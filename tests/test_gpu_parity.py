@@ -1,0 +1,383 @@
+"""GPU parity tests: the CUDA path (through the Python mirror of the reference API,
+i.e. through the C ABI of libwfb200.so) against the oracle and the golden vectors the
+reference produced.  Integer work is bit-exact; float tolerances are written at each
+assert.  Run on the B200 box: python -m pytest tests -m gpu."""
+import numpy as np
+import pytest
+import torch
+
+from oracle import cpm_link as o
+from tests.conftest import golden
+
+pytestmark = pytest.mark.gpu
+
+if torch.cuda.is_available():
+    import waveforms_b200 as wf  # noqa: F401
+    from waveforms_b200 import _ffi, bert, mfbank
+    from waveforms_b200.cpm import modulate as wmod
+    from waveforms_b200.cpm.multih import MultiHSymbolMapper, freq_pulse_multih_irig
+    from waveforms_b200.cpm.pcmfm import PCMFMSymbolMapper, freq_pulse_pcmfm
+    from waveforms_b200.cpm.soqpsk import (SOQPSKPrecoder, freq_pulse_soqpsk_a, freq_pulse_soqpsk_b,
+                                          freq_pulse_soqpsk_mil, freq_pulse_soqpsk_tg)
+    from waveforms_b200.cpm.trellis import model as tm
+    from waveforms_b200.cpm.trellis.encoder import TrellisEncoder
+    from waveforms_b200.glfsr import GLFSR, PNSequence
+    from waveforms_b200.linksim import LinkConfig, LinkSimulator
+    from waveforms_b200.noise import PhiloxRNG, add_awgn, generate_complex_awgn
+    from waveforms_b200.viterbi import SOQPSKTrellisDetector
+
+DEV = "cuda:0"
+
+
+def cu(a, dtype=None):
+    t = torch.from_numpy(np.ascontiguousarray(a))
+    if dtype is not None:
+        t = t.to(dtype)
+    return t.to(DEV)
+
+
+def test_library_is_native_and_loaded():
+    lib = _ffi.lib()
+    assert lib.wf_abi_version() == 1
+    assert lib.wf_device_check() == 0, lib.wf_last_error_string()
+    with open("/proc/self/maps") as f:
+        assert "libwfb200.so" in f.read()
+
+
+# ------------------------------------------------------------------ A1 PRBS
+@pytest.mark.parametrize("deg", [9, 15])
+def test_pn_full_period(deg):
+    g = golden("g1_pn.npz")
+    seq = PNSequence(deg).generate_sequence()
+    assert isinstance(seq, list) and len(seq) == 2 ** deg - 1
+    assert np.array_equal(np.packbits(np.array(seq, dtype=np.uint8)), g[f"pn{deg}"])
+
+
+@pytest.mark.parametrize("deg", [2, 3, 5, 7, 12, 16, 31, 32, 33, 63, 64])
+def test_pn_prefix_all_widths(deg):
+    g = golden("g1_pn.npz")
+    bits = PNSequence(deg).next_bits(256).cpu().numpy()
+    assert np.array_equal(np.packbits(bits), g[f"pn{deg}_first256"])
+
+
+def test_pn23_prefix_and_next_bit():
+    g = golden("g1_pn.npz")
+    p = PNSequence(23)
+    bits = p.next_bits(65536).cpu().numpy()
+    assert np.array_equal(np.packbits(bits), g["pn23_first65536"])
+    # next_bit() continues the same stream and keeps .state exact
+    q = PNSequence(23)
+    first = [q.next_bit() for _ in range(100)]
+    assert first == list(np.unpackbits(g["pn23_first65536"])[:100])
+    _, st = o.lfsr_bits(o.pn_mask(23), (1 << 23) - 1, 100)
+    assert q.state == st
+    r = GLFSR(o.pn_mask(9), 0x1FF)
+    assert [r.next_bit() for _ in range(40)] == list(o.pn_sequence(9)[:40])
+
+
+@pytest.mark.parametrize("order", range(2, 23))
+def test_pn_periodicity(order):
+    """Mirror of the reference's only test, tests/test_glfsr.py:6-25."""
+    pn = PNSequence(order)
+    a = pn.generate_sequence()
+    b = pn.generate_sequence()
+    assert a == b
+
+
+def test_pn_frames_jump_ahead():
+    """Frame f = stream bits [f*N, (f+1)*N) mod period, for far-away frames too."""
+    pn = PNSequence(15)
+    for first, B, N in ((0, 7, 4096), (123456789, 5, 1000), (2 ** 40 + 3, 3, 333)):
+        fr = pn.frames(first, B, N).cpu().numpy()
+        for b in range(B):
+            assert np.array_equal(fr[b], o.pn_frame_bits(15, first + b, N)), (first, b)
+        pk = pn.frames(first, B, N, packed=True).cpu().numpy().view(np.uint32)
+        ref = np.packbits(fr, axis=1, bitorder="little")
+        ref = np.concatenate((ref, np.zeros((B, (-ref.shape[1]) % 4), np.uint8)), axis=1).view(np.uint32)
+        assert np.array_equal(pk, ref)
+
+
+# ------------------------------------------------------------------ A2-A4 encoders
+@pytest.mark.parametrize("name", ["SOQPSKTrellis8x1", "SOQPSKTrellis4x2", "SOQPSKTrellis4x2DiffEncoded",
+                                  "SimpleTrellis2", "SimpleTrellis4"])
+def test_trellis_encoders(name, pn15_stream):
+    g = golden("g2_encode.npz")
+    enc = TrellisEncoder(getattr(tm, name))
+    out = enc(cu(pn15_stream)).cpu().numpy()
+    assert out.dtype == np.int8 and np.array_equal(out, g[name])
+
+
+def test_mappers_precoder_and_streaming(pn15_stream):
+    g = golden("g2_encode.npz")
+    b = cu(pn15_stream)
+    assert np.array_equal(PCMFMSymbolMapper()(b).cpu().numpy(), g["PCMFMSymbolMapper"])
+    assert np.array_equal(MultiHSymbolMapper()(b).cpu().numpy(), g["MultiHSymbolMapper"])
+    assert np.array_equal(SOQPSKPrecoder()(b).cpu().numpy(), g["SOQPSKPrecoder"])
+    enc = TrellisEncoder(tm.SOQPSKTrellis4x2DiffEncoded)
+    two = torch.cat((enc(b[:1001]), enc(b[1001:3000]))).cpu().numpy()
+    assert np.array_equal(two, g["stream_split_1001"])
+    pre = SOQPSKPrecoder()
+    parts = torch.cat((pre(b[:501]), pre(b[501:1500]), pre(b[1500:1503]))).cpu().numpy()
+    assert np.array_equal(parts, g["SOQPSKPrecoder"][:1503])
+
+
+def test_encoder_batch_ragged_and_errors(pn15_stream):
+    cols = o.TRELLISES["SOQPSKTrellis4x2DiffEncoded"]
+    for n in (1, 2, 31, 33, 1000):
+        frames = np.stack([pn15_stream[k * 1000:k * 1000 + n] for k in range(5)])
+        out = TrellisEncoder(tm.SOQPSKTrellis4x2DiffEncoded)(cu(frames)).cpu().numpy()
+        for k in range(5):
+            assert np.array_equal(out[k], o.fsm_encode(cols, frames[k])), (n, k)
+    with pytest.raises(ValueError, match="multiple of FSM cardinality"):
+        TrellisEncoder(tm.SimpleTrellis4)(cu(np.zeros(3, np.uint8)))
+    with pytest.raises(ValueError, match="Odd length"):
+        MultiHSymbolMapper()(cu(np.zeros(5, np.uint8)))
+    with pytest.raises(TypeError):
+        TrellisEncoder(tm.SimpleTrellis2)(torch.zeros(8, dtype=torch.uint8))  # CPU tensor: no fallback
+    with pytest.raises(KeyError):
+        PNSequence(65)
+
+
+# ------------------------------------------------------------------ A6 modulators
+_MOD = {
+    "pcmfm": ("SimpleTrellis2", 0.7, lambda s: freq_pulse_pcmfm(s, 4)),
+    "pcmfm6": ("SimpleTrellis2", 0.7, lambda s: freq_pulse_pcmfm(s, 6)),
+    "tg": ("SOQPSKTrellis4x2DiffEncoded", 0.25, lambda s: freq_pulse_soqpsk_tg(s)),
+    "mil": ("SOQPSKTrellis4x2DiffEncoded", 0.25, lambda s: freq_pulse_soqpsk_mil(s)),
+    "a": ("SOQPSKTrellis4x2", 0.25, lambda s: freq_pulse_soqpsk_a(s)),
+    "b": ("SOQPSKTrellis4x2", 0.25, lambda s: freq_pulse_soqpsk_b(s)),
+    "multih": ("SimpleTrellis4", np.array([4, 5]) / 16, lambda s: freq_pulse_multih_irig(s)),
+}
+
+
+@pytest.mark.parametrize("sps", [8, 10])
+@pytest.mark.parametrize("lab", list(_MOD))
+def test_modulators_vs_reference(lab, sps):
+    """north_star: modulated baseband within 1e-5 of the reference's float64 (|s| = 1, so
+    absolute = relative); the float64 instantiation agrees to 1e-10."""
+    g = golden("g4_modulated.npz")
+    tre, h, pf = _MOD[lab]
+    sy = cu(o.fsm_encode(o.TRELLISES[tre], g["bits"]))
+    ref = g[f"{lab}_{sps}"]
+    t, s = wmod.cpm_modulate(sy, h, pf(sps), sps)
+    assert s.dtype == torch.complex64 and s.shape == ref.shape
+    assert np.max(np.abs(s.cpu().numpy() - ref)) < 1e-5
+    _, s64 = wmod.cpm_modulate(sy, h, pf(sps), sps, dtype=torch.complex128)
+    assert np.max(np.abs(s64.cpu().numpy() - ref)) < 1e-10
+    if lab == "tg" and sps == 8:
+        np.testing.assert_allclose(t.cpu().numpy(), g["time_tg_8"], rtol=0, atol=0)
+
+
+def test_modulator_long_frames_batch():
+    """Several 1024-symbol chunks per frame, batch axis, no drift of the fixed-point phase."""
+    bits = np.unpackbits(golden("g1_pn.npz")["pn15"])
+    frames = np.stack([np.roll(bits, -k * 4099)[:20000] for k in range(3)])
+    sy = np.stack([o.fsm_encode(o.TRELLISES["SOQPSKTrellis4x2DiffEncoded"], f) for f in frames])
+    pulse = freq_pulse_soqpsk_tg(8)
+    _, s = wmod.cpm_modulate(cu(sy), 0.25, pulse, 8)
+    for k in range(3):
+        ref = o.cpm_modulate_closed_form(sy[k], 0.25, pulse, 8)
+        assert np.max(np.abs(s[k].cpu().numpy() - ref)) < 1e-5
+
+
+def test_frequency_and_phase_modulate():
+    rng = np.random.default_rng(3)
+    f = rng.normal(size=3000) * 0.3
+    out = wmod.frequency_modulate(cu(f), 8, 0.4).cpu().numpy()
+    revs, ph = 0.0, np.zeros(3000)
+    for i in range(3000):
+        revs = (revs + f[i]) % 8
+        ph[i] = revs * 2 * np.pi / 8 + 0.4
+    assert np.max(np.abs(out - np.exp(1j * ph))) < 1e-11
+    pm = wmod.phase_modulate(cu(f), 1.7).cpu().numpy()
+    assert np.max(np.abs(pm - np.exp(1j * 1.7 * f))) < 1e-12
+
+
+# ------------------------------------------------------------------ A7 noise
+def test_awgn_statistics_and_sharding_independence():
+    rng = PhiloxRNG(seed=1234)
+    x = generate_complex_awgn(0.5, 1 << 20, rng)
+    v = torch.view_as_real(x).cpu().numpy().astype(np.float64) / 0.5
+    assert x.dtype == torch.complex64 and x.shape == (1 << 20,)
+    n = v.size
+    assert abs(v.mean()) < 5 / np.sqrt(n)
+    assert abs(v.var() - 1) < 5 * np.sqrt(2 / n)
+    assert abs(np.mean(v ** 4) - 3) < 5 * np.sqrt(96 / n)
+    assert abs(np.mean(v[:, 0] * v[:, 1])) < 5 / np.sqrt(n / 2)       # re/im uncorrelated
+    assert abs(np.mean(v[:-1, 0] * v[1:, 0])) < 5 / np.sqrt(n / 2)    # white
+    # tail: P(|x| > 4) = 6.33e-5 per real component
+    tail = np.mean(np.abs(v) > 4.0)
+    assert 0.7 * 6.33e-5 < tail < 1.3 * 6.33e-5
+    # frames (seed, frame id) reproduce regardless of batching
+    a = generate_complex_awgn(1.0, 4096, PhiloxRNG(7, first_frame=0), batch=8)
+    b = generate_complex_awgn(1.0, 4096, PhiloxRNG(7, first_frame=5), batch=3)
+    assert torch.equal(a[5:], b)
+    assert not torch.equal(a[0], a[1])
+
+
+def test_fused_noise_equals_separate_add():
+    g = golden("g4_modulated.npz")
+    sy = cu(o.fsm_encode(o.TRELLISES["SOQPSKTrellis4x2DiffEncoded"], g["bits"]))[None].repeat(4, 1)
+    pulse = freq_pulse_soqpsk_tg(8)
+    sig = torch.tensor([0.3, 0.7, 1.0, 2.0], dtype=torch.float32, device=DEV)
+    pt = torch.tensor([0, 1, 2, 3], dtype=torch.int32, device=DEV)
+    clean = wmod.modulate_frames(sy, [0.25], pulse, 8, derotate=-np.pi / 4).contiguous()
+    sep = add_awgn(clean.clone(), sig, PhiloxRNG(99), point=pt, first_frame=5)
+    fused = wmod.modulate_frames(sy, [0.25], pulse, 8, derotate=-np.pi / 4, sigma=sig, point=pt, seed=99, first_frame=5)
+    assert torch.max(torch.abs(sep - fused)).item() < 1e-6
+    noise = (sep - clean)
+    assert abs(torch.view_as_real(noise[3]).std().item() / 2.0 - 1) < 0.05
+
+
+# ------------------------------------------------------------------ A8/A9 banks, A10 detector, A13 count
+def _rx_config1():
+    g = golden("g5_config1.npz")
+    return g, g["tx"] * np.exp(-1j * np.pi / 4) + g["noise"]
+
+
+@pytest.mark.parametrize("det", ["PT", "PAM"])
+def test_banks_vs_reference(det):
+    g, rx = _rx_config1()
+    pulse = freq_pulse_soqpsk_tg(8)
+    bank = mfbank.pt_bank if det == "PT" else mfbank.pam_bank
+    z64 = bank(cu(rx), pulse, 0.25, 8).cpu().numpy()
+    assert z64.shape == (4095, 3)
+    assert np.max(np.abs(z64 - g[f"{det}_z"])) < 1e-9
+    z32 = bank(cu(rx, torch.complex64), pulse, 0.25, 8).cpu().numpy()
+    # float32 accumulation of <= 73 taps on |rx| ~ 1.7: 1e-4 absolute on outputs of magnitude ~ 8
+    assert np.max(np.abs(z32 - g[f"{det}_z"])) < 1e-4
+
+
+def test_generic_bank_shape():
+    rng = np.random.default_rng(0)
+    taps = rng.normal(size=(5, 13)) + 1j * rng.normal(size=(5, 13))
+    rr = rng.normal(size=(2, 1000)) + 1j * rng.normal(size=(2, 1000))
+    z = mfbank.filter_bank(cu(rr), taps, sps=8, first_instant=3, n_calls=100).cpu().numpy()
+    for b in range(2):
+        full = np.stack([np.convolve(rr[b], t, "same") for t in taps])
+        assert np.max(np.abs(z[b] - full[:, 3 + 8 * np.arange(100)].T)) < 1e-9
+
+
+@pytest.mark.parametrize("det", ["PT", "PAM"])
+def test_detector_bit_exact_on_reference_noise(det):
+    """north_star: bit-exact Viterbi decisions when fed the reference's own noise samples.
+    float64 instantiation: every one of the 4095 decisions and the counts of G8."""
+    g, rx = _rx_config1()
+    pulse = freq_pulse_soqpsk_tg(8)
+    bank = mfbank.pt_bank if det == "PT" else mfbank.pam_bank
+    z = bank(cu(rx)[None], pulse, 0.25, 8)
+    tx_bits = cu(g["bits"])[None]
+    tx_syms = cu(g["symbols"])[None]
+    pk = np.packbits(g["bits"], bitorder="little").view(np.uint32).view(np.int32)
+    counters = torch.zeros((1, 3), dtype=torch.int64, device=DEV)
+    db, ds = SOQPSKTrellisDetector().detect(z, tx_packed=cu(pk)[None], tx_symbols=tx_syms, counters=counters)
+    assert np.array_equal(db[0].cpu().numpy(), g[f"{det}_dec_bits"])
+    assert np.array_equal(ds[0].cpu().numpy(), g[f"{det}_dec_syms"])
+    want = [int(g[f"{det}_bit_errors"]), int(g[f"{det}_sym_errors"]), int(g[f"{det}_compared"])]
+    assert counters[0].tolist() == want
+    assert bert.count_errors(db, tx_bits, 2, dec_symbols=ds, ref_symbols=tx_syms) == tuple(want)
+    # float32 throughput path, same input: decisions may differ only where the float64 ACS
+    # margin is below float32 resolution; on this frame there is no such place
+    z32 = bank(cu(rx, torch.complex64)[None], pulse, 0.25, 8)
+    db32, _ = SOQPSKTrellisDetector().detect(z32)
+    assert int((db32[0].cpu().numpy() != g[f"{det}_dec_bits"]).sum()) <= 1
+
+
+@pytest.mark.parametrize("diff", [True, False])
+@pytest.mark.parametrize("length", [2, 4])
+def test_detector_variants(diff, length):
+    g = golden("g7_variants.npz")
+    tag = f"d{int(diff)}_l{length}"
+    pulse = freq_pulse_soqpsk_tg(8)
+    sig = float(np.sqrt(8 / (2 * 10 ** 0.8)))
+    for det, bank in (("PT", mfbank.pt_bank), ("PAM", mfbank.pam_bank)):
+        r = o.soqpsk_link_frame(g["bits"], pulse, 8, sig, noise=g[f"noise_{tag}"], detector=det, length=length,
+                                diff=diff, return_all=True)
+        z = bank(cu(r["rx"])[None], pulse, 0.25, 8, length=length)
+        db, ds = SOQPSKTrellisDetector(length, differantial_encoding=diff).detect(z)
+        assert np.array_equal(db[0].cpu().numpy(), g[f"{det}_bits_{tag}"])
+        assert np.array_equal(ds[0].cpu().numpy(), g[f"{det}_syms_{tag}"])
+
+
+def test_detector_streaming_and_odd_windows():
+    g = golden("g5_config1.npz")
+    z = g["PAM_z"][:301]
+    for length in (1, 2, 3, 6, 16):
+        rb, rs = o.detect_soqpsk(z, length, True)
+        det = SOQPSKTrellisDetector(length)
+        parts = [det.iterate(cu(z[a:b])) for a, b in ((0, 101), (101, 102), (102, 301))]
+        assert np.array_equal(torch.cat([p[0] for p in parts]).cpu().numpy(), rb), length
+        assert np.array_equal(torch.cat([p[1] for p in parts]).cpu().numpy(), rs), length
+    det = SOQPSKTrellisDetector()
+    rb, rs = o.detect_soqpsk(z[:20], 2, True)
+    for c in range(20):
+        b, s = det.iteration(cu(z[c]))
+        assert b[0].item() == rb[c] and s[0].item() == rs[c]
+
+
+def test_example_replay_counts(pn15_stream):
+    """The shipped example (sps 10, sigma sqrt(2)/2, MIL then TG from one PCG64(1)): the CUDA
+    chain fed the same noise reproduces G8's error counts (TG PT 14 / PAM 11 of 32765, ...)."""
+    g = golden("g8_example.npz")
+    rng = np.random.Generator(np.random.PCG64(seed=1))
+    sps, sigma = 10, np.sqrt(2) / 2
+    bits = cu(pn15_stream)
+    syms = TrellisEncoder(tm.SOQPSKTrellis4x2DiffEncoded)(bits)
+    pk = cu(np.packbits(pn15_stream, bitorder="little").view(np.uint32).view(np.int32))[None]
+    for lab, pf, offs in (("MIL", freq_pulse_soqpsk_mil, {"PT": -1, "PAM": -3}),
+                          ("TG", freq_pulse_soqpsk_tg, {"PT": -1, "PAM": 0})):
+        T = (pn15_stream.size + 1) * sps
+        noise = o.complex_awgn(sigma, T, rng)
+        crc = np.array([noise.real.sum(), noise.imag.sum()])
+        if not np.allclose(crc, g[f"noise_crc_{lab}"], rtol=0, atol=1e-6):
+            pytest.skip("numpy PCG64 normal stream differs from the golden generator's numpy")
+        _, s = wmod.cpm_modulate(syms, 0.25, pf(sps), sps, dtype=torch.complex128)
+        rx = (s * np.exp(-1j * np.pi / 4) + cu(noise))[None]
+        for det, bank in (("PT", mfbank.pt_bank), ("PAM", mfbank.pam_bank)):
+            z = bank(rx, pf(sps), 0.25, sps, timing_offset=offs[det])
+            counters = torch.zeros((1, 3), dtype=torch.int64, device=DEV)
+            db, _ = SOQPSKTrellisDetector().detect(z, tx_packed=pk, tx_symbols=syms[None], counters=counters)
+            assert counters[0].tolist() == list(g[f"{lab}_{det}_counts"]), (lab, det)
+            assert np.array_equal(np.packbits(db[0].cpu().numpy()), g[f"{lab}_{det}_bits"])
+
+
+# ------------------------------------------------------------------ whole chain, full size
+def test_link_noiseless_round_trip_full_batch():
+    """Size-independent property at BASELINE size (N=4096, sps=8): with sigma = 0 every frame
+    decodes without error, for both banks."""
+    for det in ("PAM", "PT"):
+        sim = LinkSimulator(LinkConfig(detector=det), device=DEV, max_batch=2048)
+        counters = torch.zeros((1, 3), dtype=torch.int64, device=DEV)
+        sim.run_batch(1000, torch.zeros(2048, dtype=torch.float32, device=DEV), None, counters)
+        be, se, n = counters[0].tolist()
+        assert (be, n) == (0, 2048 * 4093), det
+
+
+def test_link_matches_oracle_chain_with_philox_noise():
+    """Same Philox noise through the CUDA chain and through the float64 oracle chain."""
+    cfg = LinkConfig(n_bits=1024, detector="PAM")
+    sim = LinkSimulator(cfg, device=DEV, max_batch=8)
+    sigma = float(o.sigma_from_ebn0_db(4.0, 8))
+    sg = torch.full((8,), sigma, dtype=torch.float32, device=DEV)
+    counters = torch.zeros((1, 3), dtype=torch.int64, device=DEV)
+    sim.run_batch(40, sg, None, counters)
+    noise = generate_complex_awgn(sg, sim.n_samples, PhiloxRNG(cfg.seed, first_frame=40), batch=8).cpu().numpy()
+    tot = np.zeros(3, dtype=np.int64)
+    for b in range(8):
+        bits = o.pn_frame_bits(15, 40 + b, 1024)
+        tot += np.array(o.soqpsk_link_frame(bits, o.pulse_soqpsk_tg(8), 8, sigma, noise=noise[b].astype(np.complex128),
+                                            detector="PAM"))
+    got = counters[0].tolist()
+    assert got[2] == tot[2]
+    assert abs(got[0] - tot[0]) <= 2 and abs(got[1] - tot[1]) <= 2  # float32 front end vs float64 oracle
+
+
+def test_link_batching_independence_and_e2e_host_call():
+    cfg = LinkConfig(n_bits=512)
+    a = LinkSimulator(cfg, device=DEV, max_batch=64).run([3.0, 6.0], 64)
+    b = LinkSimulator(cfg, device=DEV, max_batch=10).run([3.0, 6.0], 64)
+    assert isinstance(a, np.ndarray) and a.shape == (2, 3) and np.array_equal(a, b)
+    assert a[0, 0] > a[1, 0] > 0 and a[0, 2] == 64 * 509
+    first = LinkSimulator(cfg, device=DEV, max_batch=64).run([3.0, 6.0], 32)
+    second = LinkSimulator(cfg, device=DEV, max_batch=64).run([3.0, 6.0], 32, first_frame=32)
+    assert np.array_equal(first + second, a)  # frame sharding (multi-GPU) adds up exactly

@@ -223,7 +223,7 @@ def viterbi(z, dtype, diff=1, length=2, tx_bits=None, tx_syms=None):
         packed = np.ascontiguousarray(pk).view(np.uint32)
         ldw = packed.shape[1]
     ok(L.wf_viterbi_soqpsk(ptr(zz), dtype, B, n_calls, n_calls, diff, length, ptr(db), ptr(ds), ptr(packed), ldw,
-                           ptr(tx_syms), S, None, ptr(cnt), None))
+                           ptr(tx_syms), S, None, ptr(cnt), None, None))
     return db, ds, cnt
 
 
@@ -287,7 +287,37 @@ def t_noise():
     assert np.max(np.abs(buf - s2)) < 1e-6, np.max(np.abs(buf - s2))
 
 
-TESTS = {"lfsr": t_lfsr, "prbs": t_prbs, "mod": t_mod, "mf": t_mf, "vit": t_vit, "noise": t_noise}
+def t_stream():
+    g = G("g5_config1.npz")
+    z = np.ascontiguousarray(g["PAM_z"][:301].astype(np.complex128))
+    for length in (2, 3, 4):
+        rb, rs = o.detect_soqpsk(z, length, True)
+        st = np.zeros((1, 5 + 8 * length), np.float64)
+        got = []
+        for a, b in ((0, 101), (101, 102), (102, 301)):
+            zz = np.ascontiguousarray(z[a:b][None])
+            db = np.zeros((1, b - a), np.uint8)
+            ok(L.wf_viterbi_soqpsk(ptr(zz), 1, 1, b - a, b - a, 1, length, ptr(db), None, None, 0, None, 0, None, None,
+                                   ptr(st), None))
+            got.append(db[0])
+        assert np.array_equal(np.concatenate(got), rb), length
+    # frequency_modulate / phase_modulate against the oracle's sequential accumulator
+    rng = np.random.default_rng(3)
+    f = rng.normal(size=(2, 3000)) * 0.3
+    out = np.zeros((2, 3000), np.complex128)
+    ok(L.wf_frequency_modulate(ptr(f), 2, 3000, 3000, 8, 0.4, 1, ptr(out), 3000, None))
+    for b in range(2):
+        revs, ph = 0.0, np.zeros(3000)
+        for i in range(3000):
+            revs = (revs + f[b, i]) % 8
+            ph[i] = revs * 2 * np.pi / 8 + 0.4
+        assert np.max(np.abs(out[b] - np.exp(1j * ph))) < 1e-11
+    out32 = np.zeros(3000, np.complex64)
+    ok(L.wf_phase_modulate(ptr(f[0].copy()), 3000, 1.7, 0, ptr(out32), None))
+    assert np.max(np.abs(out32 - np.exp(1j * 1.7 * f[0]))) < 1e-6
+
+
+TESTS = {"lfsr": t_lfsr, "prbs": t_prbs, "mod": t_mod, "mf": t_mf, "vit": t_vit, "noise": t_noise, "stream": t_stream}
 
 if __name__ == "__main__":
     names = sys.argv[1:] or list(TESTS)

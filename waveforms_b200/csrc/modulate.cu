@@ -261,6 +261,71 @@ awgn_kernel(T* __restrict__ sig, int64_t B, int64_t Tn, int64_t ld, const float*
   }
 }
 
+
+// ---------------------------------------------------------------------------
+// frequency_modulate (cpm/modulate.py:28-54) for arbitrary per-sample frequency
+// pulses: phase[n] = ((sum_{m<=n} f[m]) mod sps) * 2pi/sps + initial_phase, and
+// phase_modulate (:12-25): exp(j * sensitivity * phase).  One block per frame,
+// float64 block scan in chunks of 1024 samples.
+// ---------------------------------------------------------------------------
+template <typename TO>
+__global__ void __launch_bounds__(256)
+frequency_modulate_kernel(const double* __restrict__ f, int64_t Tn, int64_t ld_in, int sps, double initial_phase,
+                          TO* __restrict__ out, int64_t ld_out) {
+  __shared__ double warp_tot[8];
+  const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+  const double* row = f + (int64_t)blockIdx.x * ld_in;
+  TO* orow = out + 2 * (int64_t)blockIdx.x * ld_out;
+  double carry = 0.0;
+  const double k = 6.283185307179586476925286766559 / (double)sps;
+  for (int64_t base = 0; base < Tn; base += 1024) {
+    double v[4], run = 0.0;
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      const int64_t n = base + 4 * tid + i;
+      run += (n < Tn) ? row[n] : 0.0;
+      v[i] = run;
+    }
+    double incl = run;
+#pragma unroll
+    for (int s = 1; s < 32; s <<= 1) {
+      double t = __shfl_up_sync(0xFFFFFFFFu, incl, s);
+      if (lane >= s) incl += t;
+    }
+    if (lane == 31) warp_tot[wid] = incl;
+    __syncthreads();
+    double before = carry, total = 0.0;
+    for (int i = 0; i < 8; ++i) { if (i < wid) before += warp_tot[i]; total += warp_tot[i]; }
+    before += incl - run;
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      const int64_t n = base + 4 * tid + i;
+      if (n < Tn) {
+        double revs = before + v[i];
+        revs -= floor(revs / sps) * sps;  // Python's % : result in [0, sps)
+        double sn, cs;
+        sincos(revs * k + initial_phase, &sn, &cs);
+        orow[2 * n] = (TO)cs;
+        orow[2 * n + 1] = (TO)sn;
+      }
+    }
+    carry += total;
+    carry -= floor(carry / sps) * sps;
+    __syncthreads();
+  }
+}
+
+template <typename TO>
+__global__ void __launch_bounds__(256)
+phase_modulate_kernel(const double* __restrict__ ph, int64_t n, double sensitivity, TO* __restrict__ out) {
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+    double sn, cs;
+    sincos(sensitivity * ph[i], &sn, &cs);
+    out[2 * i] = (TO)cs;
+    out[2 * i + 1] = (TO)sn;
+  }
+}
+
 template <typename T>
 static int launch_modulate(const int8_t* d_syms, int64_t B, int64_t S, const double* mod_index, int n_h,
                            const double* pulse, int K, int sps, double initial_phase, double derotate,
@@ -375,6 +440,43 @@ int wf_awgn_add(void* d_sig, int dtype, int64_t B, int64_t T, int64_t ld, const 
 int wf_awgn_fill(float* d_out, int64_t B, int64_t T, const float* d_sigma, const int32_t* d_point,
                  uint64_t seed, uint64_t first_frame, void* stream) {
   return awgn_common(d_out, WF_F32, B, T, T, d_sigma, d_point, seed, first_frame, stream, false);
+}
+
+int wf_frequency_modulate(const double* d_freq, int64_t B, int64_t T, int64_t ld_in, int sps, double initial_phase,
+                          int dtype, void* d_out, int64_t ld_out, void* stream) {
+  using namespace wf;
+  WF_REQUIRE(B >= 0 && T >= 0 && ld_in >= T && ld_out >= T, "bad frequency_modulate shape");
+  WF_REQUIRE(sps >= 1, "sps must be positive");
+  WF_REQUIRE(dtype == WF_F32 || dtype == WF_F64, "dtype must be WF_F32 or WF_F64");
+  int rc;
+  if ((rc = require_device())) return rc;
+  if (B == 0 || T == 0) return WF_OK;
+  WF_REQUIRE(d_freq && d_out, "NULL device pointer");
+  if (dtype == WF_F32)
+    frequency_modulate_kernel<float><<<(unsigned)B, 256, 0, as_stream(stream)>>>(d_freq, T, ld_in, sps, initial_phase, (float*)d_out, ld_out);
+  else
+    frequency_modulate_kernel<double><<<(unsigned)B, 256, 0, as_stream(stream)>>>(d_freq, T, ld_in, sps, initial_phase, (double*)d_out, ld_out);
+  WF_LAUNCH_CHECK("frequency_modulate_kernel");
+  return WF_OK;
+}
+
+int wf_phase_modulate(const double* d_phase, int64_t n, double sensitivity, int dtype, void* d_out, void* stream) {
+  using namespace wf;
+  WF_REQUIRE(n >= 0, "negative size");
+  WF_REQUIRE(dtype == WF_F32 || dtype == WF_F64, "dtype must be WF_F32 or WF_F64");
+  int rc;
+  if ((rc = require_device())) return rc;
+  if (n == 0) return WF_OK;
+  WF_REQUIRE(d_phase && d_out, "NULL device pointer");
+  int64_t blocks = (n + 255) / 256;
+  const int64_t cap = (int64_t)sm_count() * 16;
+  if (blocks > cap) blocks = cap;
+  if (dtype == WF_F32)
+    phase_modulate_kernel<float><<<(unsigned)blocks, 256, 0, as_stream(stream)>>>(d_phase, n, sensitivity, (float*)d_out);
+  else
+    phase_modulate_kernel<double><<<(unsigned)blocks, 256, 0, as_stream(stream)>>>(d_phase, n, sensitivity, (double*)d_out);
+  WF_LAUNCH_CHECK("phase_modulate_kernel");
+  return WF_OK;
 }
 
 }  // extern "C"

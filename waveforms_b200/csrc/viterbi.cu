@@ -53,6 +53,7 @@ struct VitParams {
   const int8_t* tx_syms;
   const int32_t* point;
   unsigned long long* counters;
+  void* state;  // T[B][1 + 4 + 8*length]: call parity, carried metrics, increment history (streaming)
   int64_t B, n_calls, ld_z, ld_words, S;
   int length;
 };
@@ -254,6 +255,14 @@ viterbi_soqpsk_any_kernel(const __grid_constant__ VitParams<T> p) {
   for (int j = 0; j < kVitMaxLen; ++j)
     for (int b = 0; b < 8; ++b) inc[j][b] = 0;
   T carry[4] = {0, 0, 0, 0};
+  int64_t ibase = 0;
+  T* st_io = (active && p.state) ? reinterpret_cast<T*>(p.state) + frame * (5 + 8 * L) : nullptr;
+  if (st_io) {
+    ibase = (int64_t)st_io[0];
+    for (int s = 0; s < 4; ++s) carry[s] = st_io[1 + s];
+    for (int j = 0; j < L; ++j)
+      for (int b = 0; b < 8; ++b) inc[j][b] = st_io[5 + 8 * j + b];
+  }
   ErrCount ec;
   const C* row = tile + threadIdx.x * PITCH;
 
@@ -263,7 +272,8 @@ viterbi_soqpsk_any_kernel(const __grid_constant__ VitParams<T> p) {
     __syncthreads();
     if (!active) continue;
     for (int u = 0; u < kVitChunk && c0 + u < n_calls; ++u) {
-      const int64_t i = c0 + u;
+      const int64_t il = c0 + u;       // call index inside this launch
+      const int64_t i = il + ibase;    // detector's running call counter (parity is what matters)
       T zr[3], zi[3];
       for (int r = 0; r < 3; ++r) { const C v = row[u * 3 + r]; zr[r] = v.x; zi[r] = v.y; }
       // roll the history left, append this call's increments (column i % 2)
@@ -310,10 +320,16 @@ viterbi_soqpsk_any_kernel(const __grid_constant__ VitParams<T> p) {
       const int nb = tr_newbit(c0p, st);
       const int bit = tr_inp(c0p, pstart, nb, DIFF);
       const int sym = tr_out(c0p, pstart, nb);
-      if (ob) ob[i] = (uint8_t)bit;
-      if (os) os[i] = (int8_t)sym;
-      ec.add(i - L, n_cmp, (uint32_t)bit, sym, txw, txs);
+      if (ob) ob[il] = (uint8_t)bit;
+      if (os) os[il] = (int8_t)sym;
+      ec.add(il - L, n_cmp, (uint32_t)bit, sym, txw, txs);
     }
+  }
+  if (st_io) {
+    st_io[0] = (T)((ibase + n_calls) & 1);
+    for (int s = 0; s < 4; ++s) st_io[1 + s] = carry[s];
+    for (int j = 0; j < L; ++j)
+      for (int b = 0; b < 8; ++b) st_io[5 + 8 * j + b] = inc[j][b];
   }
   if (p.counters) flush_counters(ec, n_cmp, active, (active && p.point) ? p.point[frame] : 0, p.counters);
 }
@@ -321,7 +337,7 @@ viterbi_soqpsk_any_kernel(const __grid_constant__ VitParams<T> p) {
 template <typename T>
 static int launch_viterbi(const VitParams<T>& p, int diff, cudaStream_t stream) {
   const unsigned grid = (unsigned)((p.B + kVitThreads - 1) / kVitThreads);
-  if (p.length == 2) {
+  if (p.length == 2 && !p.state) {
     if (diff) viterbi_soqpsk_l2_kernel<T, true><<<grid, kVitThreads, 0, stream>>>(p);
     else viterbi_soqpsk_l2_kernel<T, false><<<grid, kVitThreads, 0, stream>>>(p);
   } else {
@@ -338,7 +354,8 @@ extern "C" {
 
 int wf_viterbi_soqpsk(const void* d_z, int dtype, int64_t B, int64_t n_calls, int64_t ld_z, int diff, int length,
                       uint8_t* d_dec_bits, int8_t* d_dec_syms, const uint32_t* d_tx_packed, int64_t ld_words,
-                      const int8_t* d_tx_syms, int64_t S, const int32_t* d_point, int64_t* d_counters, void* stream) {
+                      const int8_t* d_tx_syms, int64_t S, const int32_t* d_point, int64_t* d_counters, void* d_state,
+                      void* stream) {
   using namespace wf;
   WF_REQUIRE(B >= 0 && n_calls >= 0, "negative shape");
   WF_REQUIRE(dtype == WF_F32 || dtype == WF_F64, "dtype must be WF_F32 or WF_F64");
@@ -355,14 +372,14 @@ int wf_viterbi_soqpsk(const void* d_z, int dtype, int64_t B, int64_t n_calls, in
     memset(&p, 0, sizeof(p));
     p.z = d_z; p.dec_bits = d_dec_bits; p.dec_syms = d_dec_syms; p.tx_packed = d_tx_packed; p.tx_syms = d_tx_syms;
     p.point = d_point; p.counters = reinterpret_cast<unsigned long long*>(d_counters);
-    p.B = B; p.n_calls = n_calls; p.ld_z = ld_z; p.ld_words = ld_words; p.S = S; p.length = length;
+    p.B = B; p.n_calls = n_calls; p.ld_z = ld_z; p.ld_words = ld_words; p.S = S; p.length = length; p.state = d_state;
     return launch_viterbi<float>(p, diff, as_stream(stream));
   }
   VitParams<double> p;
   memset(&p, 0, sizeof(p));
   p.z = d_z; p.dec_bits = d_dec_bits; p.dec_syms = d_dec_syms; p.tx_packed = d_tx_packed; p.tx_syms = d_tx_syms;
   p.point = d_point; p.counters = reinterpret_cast<unsigned long long*>(d_counters);
-  p.B = B; p.n_calls = n_calls; p.ld_z = ld_z; p.ld_words = ld_words; p.S = S; p.length = length;
+  p.B = B; p.n_calls = n_calls; p.ld_z = ld_z; p.ld_words = ld_words; p.S = S; p.length = length; p.state = d_state;
   return launch_viterbi<double>(p, diff, as_stream(stream));
 }
 

@@ -1,0 +1,217 @@
+"""Batched Monte-Carlo link simulation: the headless, batched equivalent of
+examples/soqpsk_detection.py:35-216 (bits -> precode -> CPM modulate -> AWGN ->
+matched-filter bank -> trellis detection -> error count), one kernel per stage over a
+whole batch of frames, counters left on the device.
+
+    PRBS+precode (wf_prbs_encode) -> modulate+AWGN (wf_cpm_modulate, fused Philox noise)
+        -> decimated PAM/PT bank (wf_mf_bank) -> Viterbi + error count (wf_viterbi_soqpsk)
+
+Frames are independent, so multi-GPU runs shard frames across ranks (one process per
+GPU) and all-reduce only the int64 counters (``LinkSimulator.sweep``).  Frame f of
+every Eb/N0 point carries PN bits [f*N, (f+1)*N) of the periodic PN stream and noise
+keyed by (seed, point, f): results are identical for any batch size, chunking or
+number of GPUs.
+"""
+from __future__ import annotations
+
+import math
+from dataclasses import dataclass, field
+
+import numpy as np
+import torch
+
+from . import _dev, _ffi
+from . import mfbank as _mf
+from .cpm.multih import MULTIH_IRIG_DENOM, MULTIH_IRIG_NUMER, freq_pulse_multih_irig
+from .cpm.pcmfm import PCMFM_DENOM, PCMFM_NUMER, freq_pulse_pcmfm
+from .cpm.soqpsk import (SOQPSK_DENOM, SOQPSK_NUMER, freq_pulse_soqpsk_a, freq_pulse_soqpsk_b, freq_pulse_soqpsk_mil,
+                         freq_pulse_soqpsk_tg)
+from .glfsr.pn import generate_mask
+from .noise import sigma_from_ebn0_db
+
+# (encoder id, mod indices, pulse designer, bits per symbol) -- examples/irig_comparison.py:50-72
+WAVEFORMS = {
+    "soqpsk-tg": (_ffi.ENC_SOQPSK_DIFF, [SOQPSK_NUMER / SOQPSK_DENOM], freq_pulse_soqpsk_tg, 1),
+    "soqpsk-mil": (_ffi.ENC_SOQPSK_DIFF, [SOQPSK_NUMER / SOQPSK_DENOM], freq_pulse_soqpsk_mil, 1),
+    "soqpsk-a": (_ffi.ENC_SOQPSK_DIFF, [SOQPSK_NUMER / SOQPSK_DENOM], freq_pulse_soqpsk_a, 1),
+    "soqpsk-b": (_ffi.ENC_SOQPSK_DIFF, [SOQPSK_NUMER / SOQPSK_DENOM], freq_pulse_soqpsk_b, 1),
+    "pcmfm": (_ffi.ENC_BINARY, [PCMFM_NUMER / PCMFM_DENOM], freq_pulse_pcmfm, 1),
+    "multih": (_ffi.ENC_QUATERNARY, list(MULTIH_IRIG_NUMER / MULTIH_IRIG_DENOM), freq_pulse_multih_irig, 2),
+}
+
+
+@dataclass
+class LinkConfig:
+    waveform: str = "soqpsk-tg"
+    n_bits: int = 4096          # bits per frame
+    sps: int = 8
+    detector: str = "PAM"       # "PAM" or "PT" (examples/soqpsk_detection.py:177)
+    timing_offset: int = 0      # soqpsk_detection.py:184-187 sign convention: (n + offset) % sps == 0
+    length: int = 2             # detector window
+    differential: bool = True
+    pn_degree: int = 15
+    seed: int = 1
+    dtype: torch.dtype = torch.complex64
+    extra: dict = field(default_factory=dict)
+
+
+class LinkSimulator:
+    """Owns the work buffers for up to ``max_batch`` frames and runs the four-kernel chain."""
+
+    def __init__(self, cfg: LinkConfig | None = None, device=None, max_batch: int = 4096) -> None:
+        self.cfg = cfg = cfg or LinkConfig()
+        self.device = torch.device(device) if device is not None else _dev.default_device()
+        if cfg.waveform not in WAVEFORMS:
+            raise KeyError(f"unknown waveform {cfg.waveform!r}; choose from {sorted(WAVEFORMS)}")
+        enc, h, pulse_fn, bps = WAVEFORMS[cfg.waveform]
+        if not cfg.waveform.startswith("soqpsk"):
+            raise NotImplementedError("LinkSimulator detects SOQPSK waveforms; use cpm.modulate for the others")
+        self.encoder = enc if cfg.differential else _ffi.ENC_SOQPSK
+        self.h = _dev.host_f64(h)
+        self.bits_per_symbol = bps
+        self.pulse = _dev.host_f64(pulse_fn(cfg.sps))
+        self.mask = generate_mask(cfg.pn_degree)
+        self.period = (1 << cfg.pn_degree) - 1
+        self.n_sym = cfg.n_bits // bps
+        self.n_samples = (self.n_sym + 1) * cfg.sps
+        self.first_instant, self.n_calls = _mf.symbol_instants(self.n_samples, cfg.sps, cfg.timing_offset, cfg.length)
+        self.n_compared = max(0, min(self.n_sym, self.n_calls - cfg.length))
+        if cfg.detector.upper() == "PAM":
+            taps, comb = _mf.pam_taps(self.pulse, float(self.h[0]), cfg.sps)
+        elif cfg.detector.upper() == "PT":
+            taps, comb = _mf.pt_taps(self.pulse, float(self.h[0]), cfg.sps), None
+        else:
+            raise ValueError("detector must be 'PAM' or 'PT'")
+        self._taps = np.asarray(taps)
+        self._tap_re = _dev.host_f64(self._taps.real.ravel())
+        self._tap_im = _dev.host_f64(self._taps.imag.ravel()) if np.iscomplexobj(self._taps) else None
+        self._comb_re = None if comb is None else _dev.host_f64(np.asarray(comb).real.ravel())
+        self._comb_im = None if comb is None else _dev.host_f64(np.asarray(comb).imag.ravel())
+        self._n_out = 3
+        self.max_batch = 0
+        self._alloc(int(max_batch))
+        self.launches = 0  # kernels launched so far (4 per run_batch)
+
+    # ------------------------------------------------------------------ buffers
+    def _alloc(self, max_batch: int) -> None:
+        cfg, dev = self.cfg, self.device
+        self.max_batch = max_batch
+        self.ld_words = (cfg.n_bits + 31) // 32
+        self.ld_rx = (self.n_samples + 1) & ~1
+        self.ld_z = (self.n_calls + 3) & ~3
+        self.packed = torch.zeros((max_batch, self.ld_words), dtype=torch.int32, device=dev)
+        self.syms = torch.empty((max_batch, self.n_sym), dtype=torch.int8, device=dev)
+        self.rx = torch.empty((max_batch, self.ld_rx), dtype=cfg.dtype, device=dev)
+        self.z = torch.empty((max_batch, self.ld_z, 3), dtype=cfg.dtype, device=dev)
+
+    def workspace_bytes(self) -> int:
+        return sum(t.numel() * t.element_size() for t in (self.packed, self.syms, self.rx, self.z))
+
+    # ------------------------------------------------------------------ one batch
+    def run_batch(self, first_frame: int, sigma: torch.Tensor, point: torch.Tensor | None, counters: torch.Tensor,
+                  events: list | None = None) -> None:
+        """Frames first_frame .. first_frame+B-1 (B = len(sigma) <= max_batch) through the whole
+        chain; adds (bit errors, symbol errors, compared) to counters[point[b]].  Everything is
+        enqueued on the current stream; nothing is synchronised.  ``events`` (optional list)
+        receives five CUDA events recorded on that stream around the four kernels."""
+        cfg, lib, dev = self.cfg, _ffi.lib(), self.device
+        B = sigma.shape[0]
+        if B > self.max_batch:
+            raise ValueError(f"batch {B} exceeds max_batch {self.max_batch}")
+        st = _dev.stream_ptr(dev)
+        dt = _dev.COMPLEX[cfg.dtype]
+        seed = cfg.seed & (2**64 - 1)
+        def mark():
+            if events is not None:
+                e = torch.cuda.Event(enable_timing=True)
+                e.record(torch.cuda.current_stream(dev))
+                events.append(e)
+
+        with torch.cuda.device(dev):
+            mark()
+            _ffi.check(lib.wf_prbs_encode(self.mask, cfg.pn_degree, self.period, self.period, None, int(first_frame), B,
+                                          cfg.n_bits, self.encoder, None, None, _dev.ptr(self.packed), self.ld_words,
+                                          _dev.ptr(self.syms), st))
+            mark()
+            _ffi.check(lib.wf_cpm_modulate(_dev.ptr(self.syms), B, self.n_sym, _dev.f64_ptr(self.h), self.h.size,
+                                           _dev.f64_ptr(self.pulse), self.pulse.size, cfg.sps, math.pi / 4, -math.pi / 4,
+                                           dt, _dev.ptr(self.rx), self.ld_rx, _dev.ptr(sigma), _dev.ptr(point), seed,
+                                           int(first_frame), st))
+            mark()
+            _ffi.check(lib.wf_mf_bank(_dev.ptr(self.rx), dt, B, self.n_samples, self.ld_rx, _dev.f64_ptr(self._tap_re),
+                                      None if self._tap_im is None else _dev.f64_ptr(self._tap_im),
+                                      self._taps.shape[0], self._taps.shape[1], (self._taps.shape[1] - 1) // 2,
+                                      None if self._comb_re is None else _dev.f64_ptr(self._comb_re),
+                                      None if self._comb_im is None else _dev.f64_ptr(self._comb_im), self._n_out,
+                                      cfg.sps, self.first_instant, self.n_calls, _dev.ptr(self.z), self.ld_z, st))
+            mark()
+            _ffi.check(lib.wf_viterbi_soqpsk(_dev.ptr(self.z), dt, B, self.n_calls, self.ld_z, int(cfg.differential),
+                                             cfg.length, None, None, _dev.ptr(self.packed), self.ld_words, None,
+                                             self.n_sym, _dev.ptr(point), _dev.ptr(counters), None, st))
+            mark()
+        self.launches += 4
+
+    # ------------------------------------------------------------------ host-facing calls
+    def run(self, ebn0_db, n_frames: int, first_frame: int = 0) -> np.ndarray:
+        """End-to-end call with HOST inputs and outputs: ``ebn0_db`` is a host sequence of P
+        Eb/N0 points; every point is simulated on frames first_frame .. first_frame+n_frames-1.
+        Per-frame sigma / point tables are staged through pinned memory; returns int64[P, 3] =
+        (bit errors, symbol errors, compared bits) as a numpy array."""
+        eb = np.atleast_1d(np.asarray(ebn0_db, dtype=np.float64))
+        P = eb.size
+        sig = sigma_from_ebn0_db(eb, self.cfg.sps, self.bits_per_symbol).astype(np.float32)
+        counters = torch.zeros((P, 3), dtype=torch.int64, device=self.device)
+        for p in range(P):
+            for f0 in range(0, n_frames, self.max_batch):
+                B = min(self.max_batch, n_frames - f0)
+                h_sigma = torch.full((B,), float(sig[p]), dtype=torch.float32).pin_memory()
+                h_point = torch.full((B,), p, dtype=torch.int32).pin_memory()
+                d_sigma = h_sigma.to(self.device, non_blocking=True)
+                d_point = h_point.to(self.device, non_blocking=True)
+                self.run_batch(first_frame + f0, d_sigma, d_point, counters)
+        return counters.cpu().numpy()
+
+    def sweep(self, ebn0_db, n_frames: int, first_frame: int = 0, group=None) -> np.ndarray:
+        """Multi-GPU ``run``: this rank simulates its contiguous share of the n_frames of every
+        point, then the counters are all-reduced (NCCL, SUM, int64[P,3] -- the only traffic that
+        crosses NVLink).  Without an initialised process group it equals ``run``."""
+        import torch.distributed as dist
+
+        eb = np.atleast_1d(np.asarray(ebn0_db, dtype=np.float64))
+        if not (dist.is_available() and dist.is_initialized()):
+            return self.run(eb, n_frames, first_frame)
+        rank, world = dist.get_rank(group), dist.get_world_size(group)
+        lo, hi = shard_range(n_frames, rank, world)
+        local = self.run(eb, hi - lo, first_frame + lo) if hi > lo else np.zeros((eb.size, 3), dtype=np.int64)
+        return allreduce_counters(local, self.device, group)
+
+
+def allreduce_counters(local: np.ndarray, device, group=None) -> np.ndarray:
+    """SUM all-reduce of the int64 counter table across ranks: on the GPU over NCCL
+    (NVLink/NVSwitch), on host tensors when the group's backend is gloo (CPU tests)."""
+    import torch.distributed as dist
+
+    t = torch.from_numpy(np.ascontiguousarray(local, dtype=np.int64))
+    if dist.get_backend(group) == "nccl":
+        t = t.to(device)
+    dist.all_reduce(t, op=dist.ReduceOp.SUM, group=group)
+    return t.cpu().numpy()
+
+
+def shard_range(n_items: int, rank: int, world: int) -> tuple[int, int]:
+    """Contiguous, balanced [lo, hi) share of n_items for ``rank`` of ``world``."""
+    base, rem = divmod(n_items, world)
+    lo = rank * base + min(rank, rem)
+    return lo, lo + base + (1 if rank < rem else 0)
+
+
+def ber_confidence_interval(errors: int, bits: int, level: float = 0.95) -> tuple[float, float]:
+    """Clopper-Pearson interval for a bit-error ratio (the reference computes none)."""
+    from scipy.stats import beta
+
+    if bits == 0:
+        return 0.0, 1.0
+    a = (1 - level) / 2
+    lo = 0.0 if errors == 0 else float(beta.ppf(a, errors, bits - errors + 1))
+    hi = 1.0 if errors == bits else float(beta.ppf(1 - a, errors + 1, bits - errors))
+    return lo, hi
