@@ -15,7 +15,7 @@ ROOT = os.path.dirname(os.path.dirname(HERE))
 CSRC = os.path.join(ROOT, "waveforms_b200", "csrc")
 OUT = os.environ.get("WFEMU_DIR", "/tmp/wfemu")
 
-LAUNCH = re.compile(r"^(\s*)(if \(.*?\) |else )?([A-Za-z_][\w:<>, ]*?)<<<(.*?)>>>\((.*)\);(\s*\\?)$")
+LAUNCH = re.compile(r"^(\s*)(else if \(.*?\) |if \(.*?\) |else )?([A-Za-z_][\w:<>, ]*?)<<<(.*?)>>>\((.*)\);(\s*\\?)$")
 
 
 def split_top(s):

@@ -152,3 +152,5 @@ using std::fma;
 using std::fmin;
 using std::rint;
 using std::floor;
+static inline void __syncwarp(unsigned = 0xFFFFFFFFu) { ::emu::t_warp->bar.wait(); }
+template <typename T> static inline T __ldg(const T* p) { return *p; }

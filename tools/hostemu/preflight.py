@@ -317,7 +317,29 @@ def t_stream():
     assert np.max(np.abs(out32 - np.exp(1j * 1.7 * f[0]))) < 1e-6
 
 
-TESTS = {"lfsr": t_lfsr, "prbs": t_prbs, "mod": t_mod, "mf": t_mf, "vit": t_vit, "noise": t_noise, "stream": t_stream}
+def t_lean():
+    """counter-only path (no decisions requested): many frames, ragged sizes, per-frame points"""
+    rng = np.random.default_rng(5)
+    for B, n_calls, S, dtype in ((70, 101, 99, 0), (33, 37, 40, 1), (5, 64, 62, 0), (64, 8, 6, 0), (40, 3, 1, 1)):
+        z = (rng.normal(size=(B, n_calls, 3)) + 1j * rng.normal(size=(B, n_calls, 3)))
+        zz = np.ascontiguousarray(z.astype(np.complex64 if dtype == 0 else np.complex128))
+        db, _ = o.detect_soqpsk_fast(zz.astype(np.complex128), True)
+        tx = rng.integers(0, 2, size=(B, S)).astype(np.uint8)
+        n_cmp = max(0, min(S, n_calls - 2))
+        pts = (np.arange(B) % 3).astype(np.int32)
+        want = np.zeros((3, 3), np.int64)
+        for b in range(B):
+            want[pts[b], 0] += int(np.sum(db[b, 2:2 + n_cmp] != tx[b, :n_cmp]))
+            want[pts[b], 2] += n_cmp
+        pk = np.packbits(tx, axis=1, bitorder="little")
+        pk = np.ascontiguousarray(np.concatenate((pk, np.zeros((B, (-pk.shape[1]) % 4), np.uint8)), axis=1)).view(np.uint32)
+        cnt = np.zeros((3, 3), np.int64)
+        ok(L.wf_viterbi_soqpsk(ptr(zz), dtype, B, n_calls, n_calls, 1, 2, None, None, ptr(pk), pk.shape[1], None, S,
+                               ptr(pts), ptr(cnt), None, None))
+        assert np.array_equal(cnt, want), (B, n_calls, S, dtype, cnt, want)
+
+
+TESTS = {"lfsr": t_lfsr, "prbs": t_prbs, "mod": t_mod, "mf": t_mf, "vit": t_vit, "noise": t_noise, "stream": t_stream, "lean": t_lean}
 
 if __name__ == "__main__":
     names = sys.argv[1:] or list(TESTS)

@@ -3,6 +3,7 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 #include <stdio.h>
+#include <string.h>
 #include <stdarg.h>
 #include "../../include/wfb200.h"
 
@@ -81,6 +82,16 @@ __device__ __forceinline__ float fast_sqrt(float x) {
 #endif
 }
 
+__device__ __forceinline__ float fast_log2(float x) {  // MUFU.LG2 without the denormal fix-up (x >= 2^-33 here)
+#ifdef WF_HOSTEMU
+  return log2f(x);
+#else
+  float r;
+  asm("lg2.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
+  return r;
+#endif
+}
+
 // Box-Muller on two 32-bit uniforms -> one complex N(0,1)+jN(0,1) sample.
 // Uniforms are built from mantissa bits (no I2F on the XU pipe, which already
 // carries LG2/SQRT/SIN/COS).  u1's top 23 bits give x in (0,1); when they are all
@@ -90,13 +101,35 @@ __device__ __forceinline__ float2 box_muller(uint32_t u1, uint32_t u2) {
   float x = __uint_as_float(0x3F800000u | (u1 >> 9)) - 1.0f + 5.9604644775390625e-08f;  // (m + 0.5) 2^-23
   if ((u1 >> 9) == 0u) x = ((float)(u1 & 0x1FFu) + 0.5f) * 2.3283064365386963e-10f;     // (u1 + 0.5) 2^-32
   // r^2 = -2 ln x = -2 ln2 log2 x
-  float r = fast_sqrt(-1.3862943611198906f * __log2f(x));
+  float r = fast_sqrt(-1.3862943611198906f * fast_log2(x));
   // angle uniform in [-pi, pi): (f - 1.5) * 2 pi with f in [1,2), plus half a step
   float ang = fmaf(__uint_as_float(0x3F800000u | (u2 >> 9)), 6.283185307179586f, -9.42477796f);
   float s, c;
   __sincosf(ang, &s, &c);
   return make_float2(r * c, r * s);
 }
+// ---- cp.async helpers (LDGSTS): global -> shared without a register round trip ----
+template <int BYTES>
+__device__ __forceinline__ void cp_async(void* smem_dst, const void* gmem_src) {
+#ifdef WF_HOSTEMU
+  memcpy(smem_dst, gmem_src, BYTES);
+#else
+  const uint32_t d = (uint32_t)__cvta_generic_to_shared(smem_dst);
+  asm volatile("cp.async.ca.shared.global [%0], [%1], %2;" ::"r"(d), "l"(gmem_src), "n"(BYTES) : "memory");
+#endif
+}
+__device__ __forceinline__ void cp_async_commit() {
+#ifndef WF_HOSTEMU
+  asm volatile("cp.async.commit_group;" ::: "memory");
+#endif
+}
+template <int N>
+__device__ __forceinline__ void cp_async_wait() {
+#ifndef WF_HOSTEMU
+  asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory");
+#endif
+}
+
 #endif
 
 }  // namespace wf

@@ -65,14 +65,57 @@ mf_bank_kernel(const __grid_constant__ MfParams<T> p) {
   const int64_t n_lo = p.first_instant + i0 * sps + p.center - (nt - 1);
   const int n_samp = (SYM - 1) * sps + nt;
 
-  // ---- stage the rx tile, transposed ------------------------------------------
-  for (int m = tid; m < n_samp; m += kMfThreads) {
-    const int64_t n = n_lo + m;
-    C v;
-    v.x = 0; v.y = 0;
-    if (n >= 0 && n < p.Tn) v = rx[n];
-    const int r = m % sps, q = m / sps;
-    tile[(r * R + (q % R)) * qs + q / R] = v;
+  // ---- stage the rx tile, transposed ----------------------------------------------------
+  // interior float tiles: 128-bit global loads, four in flight per thread, each split into two
+  // 64-bit shared stores (samples n, n+1 live in adjacent rows of the transposed tile)
+  bool staged = false;
+  if constexpr (sizeof(T) == 4) {
+    const bool fast = ((n_lo & 1) == 0) && ((p.ld_rx & 1) == 0) && ((sps & 1) == 0) && n_lo >= 0 &&
+                      n_lo + n_samp <= p.Tn && ((reinterpret_cast<uintptr_t>(p.rx) & 15) == 0);
+    if (fast) {
+      const float4* src = reinterpret_cast<const float4*>(rx + n_lo);
+      const int npair = n_samp >> 1;
+      for (int base = 0; base < npair; base += 4 * kMfThreads) {
+        float4 v[4];
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+          const int pi = base + k * kMfThreads + tid;
+          if (pi < npair) v[k] = __ldg(src + pi);
+        }
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+          const int pi = base + k * kMfThreads + tid;
+          if (pi < npair) {
+            const int mm = 2 * pi, r = mm % sps, q = mm / sps;
+            C* d = &tile[(r * R + (q % R)) * qs + q / R];
+            d[0] = make_float2(v[k].x, v[k].y);
+            d[R * qs] = make_float2(v[k].z, v[k].w);
+          }
+        }
+      }
+      if ((n_samp & 1) && tid == 0) {
+        const int mm = n_samp - 1, r = mm % sps, q = mm / sps;
+        tile[(r * R + (q % R)) * qs + q / R] = rx[n_lo + mm];
+      }
+      staged = true;
+    }
+  }
+  if (!staged) {  // edges of the frame, float64, odd alignments: cp.async per sample, zeros outside [0, T)
+#pragma unroll 4
+    for (int m = tid; m < n_samp; m += kMfThreads) {
+      const int64_t n = n_lo + m;
+      const int r = m % sps, q = m / sps;
+      C* d = &tile[(r * R + (q % R)) * qs + q / R];
+      if (n >= 0 && n < p.Tn) {
+        cp_async<sizeof(C)>(d, rx + n);
+      } else {
+        C zero;
+        zero.x = 0; zero.y = 0;
+        *d = zero;
+      }
+    }
+    cp_async_commit();
+    cp_async_wait<0>();
   }
   __syncthreads();
 

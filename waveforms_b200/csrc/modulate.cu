@@ -71,7 +71,7 @@ cpm_modulate_kernel(const __grid_constant__ ModParams<T> p) {
   using Tr = ModTraits<T>;
   using Fix = typename Tr::Fix;
   using Vec2 = typename Tr::Vec2;
-  __shared__ T w_s[kRing];
+  __shared__ T w_s[kRing + 16];  // slots [kRing, kRing+16) mirror [0, 16): a J-wide window never wraps
   __shared__ Fix f_s[kRing];
   __shared__ uint64_t warp_tot[kModThreads / 32];
   __shared__ T c0_s;
@@ -87,7 +87,7 @@ cpm_modulate_kernel(const __grid_constant__ ModParams<T> p) {
   const bool vec_ok = ((p.ld_out & 1) == 0) && ((reinterpret_cast<uintptr_t>(p.out) & (2 * sizeof(Vec2) - 1)) == 0);
 
   // zero the ring (covers symbols k < 0 and F[m <= 0])
-  for (int i = tid; i < kRing; i += kModThreads) { w_s[i] = (T)0; f_s[i] = 0; }
+  for (int i = tid; i < kRing + 16; i += kModThreads) { w_s[i] = (T)0; if (i < kRing) f_s[i] = 0; }
   if (tid == 0) {
     // frame-start truncation of "same" convolution: sum_k w_k Q[clip(off-(k+1)sps,0,K)]
     T c0 = 0;
@@ -158,7 +158,9 @@ cpm_modulate_kernel(const __grid_constant__ ModParams<T> p) {
 #pragma unroll
       for (int i = 0; i < kScanPer; ++i) {
         const int64_t k = k0 + i;
-        w_s[k & (kRing - 1)] = wv[i];
+        const int slot = (int)(k & (kRing - 1));
+        w_s[slot] = wv[i];
+        if (slot < 16) w_s[slot + kRing] = wv[i];
         f_s[(k + 1) & (kRing - 1)] = Tr::narrow(base + inc[i]);  // F[k+1]
       }
       carry += total;
@@ -167,19 +169,20 @@ cpm_modulate_kernel(const __grid_constant__ ModParams<T> p) {
     }
 
     // ---- (b) samples of symbols-intervals [cs, cs + chunk) --------------------
-    const int64_t n_base = cs * sps;
+    const int n_base = (int)cs * sps;  // Tn < 2^31 (checked on the host): 32-bit sample indices
     const int npairs = kChunkSyms * sps / 2;
+    const int Ti = (int)Tn;
     for (int q = tid; q < npairs; q += kModThreads) {
-      const int64_t n = n_base + 2 * (int64_t)q;
-      if (n >= Tn) break;
+      const int n = n_base + 2 * q;
+      if (n >= Ti) break;
       T ph[2];
       if (JT > 0) {
-        const int64_t a = n + off;
-        const int64_t khi = a / SPSD - 1;
+        const int khi = (int)((n + off) / SPSD) - 1;
+        const T* wwin = &w_s[(khi - (JT - 1)) & (kRing - 1)];  // symbols khi-JT+1 .. khi, contiguous (mirrored tail)
         T acc0 = 0, acc1 = 0;
 #pragma unroll
         for (int j = 0; j < JT; ++j) {
-          const T w = w_s[(khi - j) & (kRing - 1)];
+          const T w = wwin[JT - 1 - j];
           acc0 = fma(w, qa[j], acc0);
           acc1 = fma(w, qb[j], acc1);
         }
@@ -189,9 +192,9 @@ cpm_modulate_kernel(const __grid_constant__ ModParams<T> p) {
       } else {
 #pragma unroll
         for (int e = 0; e < 2; ++e) {
-          const int64_t a = n + e + off;
-          const int64_t khi = a / sps - 1;
-          const int rho = (int)(a - (khi + 1) * sps);
+          const int a = n + e + off;
+          const int khi = a / sps - 1;
+          const int rho = a - (khi + 1) * sps;
           T acc = 0;
           for (int j = 0; j < J; ++j) acc = fma(w_s[(khi - j) & (kRing - 1)], p.q[rho + 1 + j * sps], acc);
           const T old = Tr::turns(f_s[(khi - J + 1) & (kRing - 1)]) + p.phase0_turns;
@@ -202,12 +205,12 @@ cpm_modulate_kernel(const __grid_constant__ ModParams<T> p) {
       Tr::unit(ph[0], c[0], s[0]);
       Tr::unit(ph[1], c[1], s[1]);
       if (NOISE) {
-        u32x4 r = philox4x32_10(noise_counter((uint64_t)(n >> 1), gframe, pt), (uint32_t)p.seed, (uint32_t)(p.seed >> 32));
+        u32x4 r = philox4x32_10(noise_counter((uint64_t)(uint32_t)(n >> 1), gframe, pt), (uint32_t)p.seed, (uint32_t)(p.seed >> 32));
         float2 g0 = box_muller(r.x, r.y), g1 = box_muller(r.z, r.w);
         c[0] += (T)(sig * g0.x); s[0] += (T)(sig * g0.y);
         c[1] += (T)(sig * g1.x); s[1] += (T)(sig * g1.y);
       }
-      if (vec_ok && n + 1 < Tn) {
+      if (vec_ok && n + 1 < Ti) {
         if (sizeof(T) == 4) {
           *reinterpret_cast<float4*>(out + n) = make_float4((float)c[0], (float)s[0], (float)c[1], (float)s[1]);
         } else {
@@ -218,7 +221,7 @@ cpm_modulate_kernel(const __grid_constant__ ModParams<T> p) {
       } else {
         Vec2 v0; v0.x = c[0]; v0.y = s[0];
         out[n] = v0;
-        if (n + 1 < Tn) { Vec2 v1; v1.x = c[1]; v1.y = s[1]; out[n + 1] = v1; }
+        if (n + 1 < Ti) { Vec2 v1; v1.x = c[1]; v1.y = s[1]; out[n + 1] = v1; }
       }
     }
     // next chunk's scan starts with a __syncthreads-protected phase; ring slots it
@@ -393,6 +396,7 @@ int wf_cpm_modulate(const int8_t* d_syms, int64_t B, int64_t S, const double* mo
   WF_REQUIRE(n_h >= 1 && n_h <= kMaxH && mod_index, "n_h=%d outside 1..%d", n_h, kMaxH);
   WF_REQUIRE(dtype == WF_F32 || dtype == WF_F64, "dtype must be WF_F32 or WF_F64");
   WF_REQUIRE(ld_out >= (S + 1) * sps, "ld_out smaller than (S+1)*sps");
+  WF_REQUIRE((S + 1) * sps < 0x7FFFFFFF, "frame longer than 2^31 samples");
   WF_REQUIRE(B <= 0x7FFFFFFF, "batch too large for one launch");
   int rc;
   if ((rc = require_device())) return rc;

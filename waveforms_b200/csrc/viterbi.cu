@@ -176,54 +176,128 @@ __device__ __forceinline__ void stage_chunk(const C* __restrict__ z, int64_t fra
   }
 }
 
-template <typename T, bool DIFF>
-__global__ void __launch_bounds__(kVitThreads)
+constexpr int kL2Threads = 64;  // two warps; each warp owns its 32 frames and its own staging buffers
+
+// length-2 detector, the throughput path.  Every WARP is autonomous: it stages the next
+// chunk of its 32 frames' rows with cp.async (coalesced 192-byte runs, double buffered)
+// while it runs add-compare-select on the current chunk; there is no block barrier.
+// FULL = decisions and/or symbol errors requested (API path); otherwise only packed bit
+// errors are counted: decisions are collected 32 calls at a time and compared with the
+// transmitted bits by funnel-shift (the 2-call decision delay) + XOR + popcount.
+template <typename T, bool DIFF, bool FULL>
+__global__ void __launch_bounds__(kL2Threads)
 viterbi_soqpsk_l2_kernel(const __grid_constant__ VitParams<T> p) {
   using C = typename std::conditional<sizeof(T) == 4, float2, double2>::type;
-  constexpr int kVitChunk = VitChunk<T>::n;
-  constexpr int PITCH = kVitChunk * 3 + 1;  // odd pitch: lanes hit distinct banks
-  __shared__ C tile[kVitThreads * PITCH];
+  constexpr int CH = VitChunk<T>::n;       // calls per chunk (divides 32)
+  constexpr int ROW = CH * 3;              // complex elements per frame per chunk
+  constexpr int PITCH = ROW + 1;           // odd pitch: the 32 lanes hit distinct banks
+  constexpr int ROWS_PER_STEP = 96 / ROW;  // e = lane + 32 j: every 3 j's the (row, column) pattern repeats
+  constexpr int STEPS = ROW / 3;
+  __align__(16) __shared__ C tile[2][kL2Threads * PITCH];
 
-  const int64_t frame0 = (int64_t)blockIdx.x * kVitThreads;
-  const int64_t frame = frame0 + threadIdx.x;
+  const int lane = threadIdx.x & 31, wrow0 = threadIdx.x & ~31;
+  const int64_t wframe0 = (int64_t)blockIdx.x * kL2Threads + wrow0;
+  if (wframe0 >= p.B) return;  // whole warp
+  const int64_t frame = wframe0 + lane;
   const bool active = frame < p.B;
-  const C* z = reinterpret_cast<const C*>(p.z);
-  const int64_t n_calls = p.n_calls;
-  const int64_t n_cmp = max((int64_t)0, min(p.S, n_calls - 2));
+  const int n_calls = (int)p.n_calls;
+  const int n_cmp = max(0, (int)min(p.S, (int64_t)n_calls - 2));
   const uint32_t* txw = (active && p.tx_packed) ? p.tx_packed + frame * p.ld_words : nullptr;
-  const int8_t* txs = (active && p.tx_syms) ? p.tx_syms + frame * p.S : nullptr;
-  uint8_t* ob = (active && p.dec_bits) ? p.dec_bits + frame * n_calls : nullptr;
-  int8_t* os = (active && p.dec_syms) ? p.dec_syms + frame * n_calls : nullptr;
+  const int8_t* txs = (FULL && active && p.tx_syms) ? p.tx_syms + frame * p.S : nullptr;
+  uint8_t* ob = (FULL && active && p.dec_bits) ? p.dec_bits + frame * p.n_calls : nullptr;
+  int8_t* os = (FULL && active && p.dec_syms) ? p.dec_syms + frame * p.n_calls : nullptr;
+
+  // staging pattern of this lane: three (row, column) pairs, each repeated STEPS times ROWS_PER_STEP rows apart
+  const C* src[3];
+  int dst[3], col[3];
+#pragma unroll
+  for (int r = 0; r < 3; ++r) {
+    const int e = lane + 32 * r, f = e / ROW, k = e - f * ROW;
+    src[r] = reinterpret_cast<const C*>(p.z) + (wframe0 + f) * p.ld_z * 3 + k;
+    dst[r] = (wrow0 + f) * PITCH + k;
+    col[r] = k / 3;
+  }
+  const int64_t src_step = (int64_t)ROWS_PER_STEP * p.ld_z * 3;
+  const int64_t last_row = p.B - 1 - wframe0;  // rows beyond it are clamped to it (valid memory, never used)
+
+  auto stage = [&](int buf, int c0) {
+    const bool whole = c0 + CH <= n_calls;
+#pragma unroll
+    for (int r = 0; r < 3; ++r) {
+      const int f0 = (lane + 32 * r) / ROW;
+#pragma unroll
+      for (int m = 0; m < STEPS; ++m) {
+        const int64_t rowi = f0 + m * ROWS_PER_STEP;
+        const int64_t back = rowi > last_row ? (rowi - last_row) * p.ld_z * 3 : 0;
+        if (whole || c0 + col[r] < n_calls)
+          cp_async<sizeof(C)>(&tile[buf][dst[r] + m * ROWS_PER_STEP * PITCH], src[r] + m * src_step - back + (int64_t)c0 * 3);
+      }
+    }
+    cp_async_commit();
+  };
 
   T M[4] = {0, 0, 0, 0};
   T zpr[3] = {0, 0, 0}, zpi[3] = {0, 0, 0};
-  ErrCount ec;
-  const C* row = tile + threadIdx.x * PITCH;
+  uint32_t decw = 0, w_prev = 0;
+  unsigned long long bit_err = 0, sym_err = 0;
 
-  for (int64_t c0 = 0; c0 < n_calls; c0 += kVitChunk) {
-    __syncthreads();
-    stage_chunk<C, kVitChunk>(z, frame0, p.B, p.ld_z, c0, n_calls, tile, PITCH);
-    __syncthreads();
-    if (active) {
+  // compare the 32 decisions of calls [g, g+32) with transmitted bits [g-2, g+30)
+  auto count_group = [&](int g) {
+    if (txw == nullptr) return;
+    const int lo = max(g, 2), hi = min(g + 32, n_cmp + 2);  // valid call range
+    if (hi > lo) {
+      const int wi = g >> 5;
+      const uint32_t w_cur = (wi < (int)((n_cmp + 31) >> 5)) ? txw[wi] : 0u;
+      const uint32_t tx = (w_cur << 2) | (w_prev >> 30);
+      uint32_t mask = 0xFFFFFFFFu;
+      if (lo > g) mask &= 0xFFFFFFFFu << (lo - g);
+      if (hi < g + 32) mask &= 0xFFFFFFFFu >> (g + 32 - hi);
+      bit_err += __popc((decw ^ tx) & mask);
+      w_prev = w_cur;
+    }
+  };
+
+  const int n_chunks = (n_calls + CH - 1) / CH;
+  if (n_chunks > 0) stage(0, 0);
+  for (int c = 0; c < n_chunks; ++c) {
+    const int c0 = c * CH;
+    if (c + 1 < n_chunks) {
+      stage((c + 1) & 1, c0 + CH);
+      cp_async_wait<1>();
+    } else {
+      cp_async_wait<0>();
+    }
+    __syncwarp();
+    const C* row = &tile[c & 1][threadIdx.x * PITCH];
 #pragma unroll
-      for (int u = 0; u < kVitChunk; ++u) {
-        const int64_t i = c0 + u;
-        if (i < n_calls) {
-          T zr[3], zi[3];
+    for (int u = 0; u < CH; ++u) {
+      const int i = c0 + u;
+      if (c0 + CH <= n_calls || i < n_calls) {
+        T zr[3], zi[3];
 #pragma unroll
-          for (int r = 0; r < 3; ++r) { const C v = row[u * 3 + r]; zr[r] = v.x; zi[r] = v.y; }
-          const uint32_t d = (u & 1) ? detector_call_l2<T, 1, DIFF>(M, zpr, zpi, zr, zi)
-                                     : detector_call_l2<T, 0, DIFF>(M, zpr, zpi, zr, zi);
-          const uint32_t bit = d & 1u;
+        for (int r = 0; r < 3; ++r) { const C v = row[u * 3 + r]; zr[r] = v.x; zi[r] = v.y; }
+        const uint32_t d = (u & 1) ? detector_call_l2<T, 1, DIFF>(M, zpr, zpi, zr, zi)
+                                   : detector_call_l2<T, 0, DIFF>(M, zpr, zpi, zr, zi);
+        decw |= (d & 1u) << (i & 31);
+        if (FULL) {
           const int sym = 2 * (int)(d >> 1) - 2;
-          if (ob) ob[i] = (uint8_t)bit;
+          if (ob) ob[i] = (uint8_t)(d & 1u);
           if (os) os[i] = (int8_t)sym;
-          ec.add(i - 2, n_cmp, bit, sym, txw, txs);
+          if (txs && i >= 2 && i - 2 < n_cmp) sym_err += (sym != (int)txs[i - 2]) ? 1u : 0u;
         }
       }
     }
+    if (((c0 + CH) & 31) == 0) { count_group(c0 + CH - 32); decw = 0; }
+    __syncwarp();  // all lanes are done with tile[c & 1] before chunk c+2 is staged into it
   }
-  if (p.counters) flush_counters(ec, n_cmp, active, (active && p.point) ? p.point[frame] : 0, p.counters);
+  if ((n_chunks * CH) & 31) count_group((n_chunks * CH) & ~31);  // group left open by the last chunk
+
+  if (p.counters) {
+    ErrCount ec;
+    ec.bit_err = bit_err;
+    ec.sym_err = sym_err;
+    flush_counters(ec, n_cmp, active, (active && p.point) ? p.point[frame] : 0, p.counters);
+  }
 }
 
 // ---------------------------------------------------------------------------
@@ -338,8 +412,12 @@ template <typename T>
 static int launch_viterbi(const VitParams<T>& p, int diff, cudaStream_t stream) {
   const unsigned grid = (unsigned)((p.B + kVitThreads - 1) / kVitThreads);
   if (p.length == 2 && !p.state) {
-    if (diff) viterbi_soqpsk_l2_kernel<T, true><<<grid, kVitThreads, 0, stream>>>(p);
-    else viterbi_soqpsk_l2_kernel<T, false><<<grid, kVitThreads, 0, stream>>>(p);
+    const unsigned g2 = (unsigned)((p.B + kL2Threads - 1) / kL2Threads);
+    const bool full = p.dec_bits || p.dec_syms || p.tx_syms;
+    if (diff && full) viterbi_soqpsk_l2_kernel<T, true, true><<<g2, kL2Threads, 0, stream>>>(p);
+    else if (diff) viterbi_soqpsk_l2_kernel<T, true, false><<<g2, kL2Threads, 0, stream>>>(p);
+    else if (full) viterbi_soqpsk_l2_kernel<T, false, true><<<g2, kL2Threads, 0, stream>>>(p);
+    else viterbi_soqpsk_l2_kernel<T, false, false><<<g2, kL2Threads, 0, stream>>>(p);
   } else {
     if (diff) viterbi_soqpsk_any_kernel<T, true><<<grid, kVitThreads, 0, stream>>>(p);
     else viterbi_soqpsk_any_kernel<T, false><<<grid, kVitThreads, 0, stream>>>(p);
