@@ -182,6 +182,22 @@ WF_API int wf_bert(const uint8_t* d_dec_bits, const int8_t* d_dec_syms, int64_t 
             int64_t B, int64_t skip, int64_t n_cmp,
             const int32_t* d_point, int64_t* d_counters, void* stream);
 
+/* ---- A11/A12  generic pulse-truncated coherent CPM trellis detector (PCM/FM, ARTM multi-h).
+ *      NO reference implementation exists (waveforms.viterbi has only the SOQPSK detector);
+ *      waveform parameters from examples/irig_comparison.py:50-72, design in DESIGN.md 4.5,
+ *      float64 statement in oracle/cpm_generic.py.  Parity unpinned. ---------------------- */
+/* d_z complex[B][ld_z][n_h * M^Lp]: per detection step the bank outputs for every symbol
+ * hypothesis (newest symbol most significant), one block of M^Lp per step parity i % n_h.
+ * h = h_num[k % n_h] / p.  State count 2p * M^(Lp-1) <= 256; register-exchange survivors of
+ * `depth` symbols (0 -> 64 / log2 M).  Outputs: d_dec_syms int8[B][n_steps] (alphabet values,
+ * may be NULL) and, when d_tx_syms int8[B][S] is given, counters[point][3] += (bit errors,
+ * symbol errors, compared symbols) over symbols [skip_head, min(S, n_steps) - skip_tail). */
+WF_API int wf_viterbi_cpm(const void* d_z, int dtype, int64_t B, int64_t n_steps, int64_t ld_z,
+                          int M, int Lp, int p, const int32_t* h_num, int n_h, int depth,
+                          int8_t* d_dec_syms, const int8_t* d_tx_syms, int64_t S,
+                          int64_t skip_head, int64_t skip_tail,
+                          const int32_t* d_point, int64_t* d_counters, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -1,0 +1,123 @@
+"""Float64 numpy statement of the generic pulse-truncated coherent CPM trellis detector
+(TEST INFRASTRUCTURE ONLY) -- rows A11/A12 of SURVEY section 8(a).
+
+PARITY UNPINNED: the reference has NO detector for PCM/FM or ARTM multi-h CPM
+(waveforms.viterbi exports only SOQPSKTrellisDetector).  This is the builder's own design,
+generalising the reference's pulse-truncation idea (examples/soqpsk_detection.py:134-156:
+filters exp(-2j pi h alpha q(t)) over the central symbol of the phase pulse, metric
+Re{e^{-j theta_state} z}) to L' >= 1 symbols of memory, M-ary alphabets and cycling
+modulation indices (waveform parameters from examples/irig_comparison.py:50-72).
+It is validated by noiseless round trips, by the modulators (which ARE pinned, G4) and by
+monotone BER curves; the CUDA kernel (csrc/cpmdet.cu) is tested against it decision by decision.
+
+Model.  With Q the cumulative frequency pulse, off = (K-1)//2 and
+Qn[j] = Q[clip(j,0,K)]/sps, the modulator's phase is 2 pi sum_k h_k a_k Qn[n + off + 1 - (k+1) sps].
+Truncation to Lp symbols: Qn is taken as 0 before index a = ((K-1) - Lp sps)//2 and as its final
+value after a + Lp sps.  Detection step i covers samples c_i + u, u in [0, sps),
+c_i = (i+1) sps - off - 1 + a, where symbols i, i-1, .., i-Lp+1 are in transit and older ones
+contribute the phase state theta_i = pi/p sum_{k <= i-Lp} K_k a_k  (h_k = K_k / p).
+"""
+from __future__ import annotations
+
+from itertools import product
+
+import numpy as np
+
+
+class CpmTrellis:
+    def __init__(self, pulse, h_num, p, M, sps, Lp):
+        self.g = np.asarray(pulse, dtype=np.float64)
+        self.h_num = [int(x) for x in np.atleast_1d(h_num)]
+        self.p, self.M, self.sps, self.Lp = int(p), int(M), int(sps), int(Lp)
+        K = self.g.size
+        self.off = (K - 1) // 2
+        self.a = max(0, ((K - 1) - self.Lp * self.sps) // 2)
+        self.first_instant = self.sps - self.off - 1 + self.a  # c_0
+        self.n_h = len(self.h_num)
+        self.alphabet = [2 * v - (self.M - 1) for v in range(self.M)]
+        self.n_filt = self.M ** self.Lp
+        self.n_hist = self.M ** (self.Lp - 1)
+        self.n_states = 2 * self.p * self.n_hist
+        Q = np.concatenate(([0.0], np.cumsum(self.g)))
+        self.Qn = Q / self.sps
+        self.full = float(self.Qn[-1])  # 1/2 for a normalised pulse
+
+    # hypothesis index f = sum_l v_l M^(Lp-1-l), v_0 = newest symbol (a_l = alphabet[v_l])
+    def templates(self):
+        """complex[n_h, n_filt, sps]: exp(+j 2 pi sum_l h_{i-l} a_l Qn[a + l sps + u]) for step parity i % n_h."""
+        out = np.zeros((self.n_h, self.n_filt, self.sps), dtype=np.complex128)
+        u = np.arange(self.sps)
+        for par in range(self.n_h):
+            for f, vs in enumerate(product(range(self.M), repeat=self.Lp)):
+                ph = np.zeros(self.sps)
+                for l, v in enumerate(vs):
+                    h = self.h_num[(par - l) % self.n_h] / self.p
+                    idx = np.clip(self.a + l * self.sps + u, 0, self.g.size)
+                    ph += h * self.alphabet[v] * self.Qn[idx]
+                out[par, f] = np.exp(2j * np.pi * ph)
+        return out
+
+    def bank_taps(self):
+        """taps complex[n_h * n_filt, sps] for the convolution-form bank
+        y[i] = sum_t rx[c_i + (sps-1) - t] taps[t]  (center = sps-1): conj(template) reversed."""
+        t = self.templates().reshape(self.n_h * self.n_filt, self.sps)
+        return np.conj(t[:, ::-1])
+
+    def bank(self, rx, n_steps):
+        """z complex[n_steps, n_h * n_filt] by direct correlation (rx = 0 outside the frame)."""
+        tpl = np.conj(self.templates().reshape(self.n_h * self.n_filt, self.sps))
+        z = np.zeros((n_steps, tpl.shape[0]), dtype=np.complex128)
+        for i in range(n_steps):
+            c = self.first_instant + i * self.sps
+            seg = np.zeros(self.sps, dtype=np.complex128)
+            lo, hi = max(c, 0), min(c + self.sps, rx.size)
+            if hi > lo:
+                seg[lo - c:hi - c] = rx[lo:hi]
+            z[i] = tpl @ seg
+        return z
+
+    def detect(self, z, depth=None):
+        """Register-exchange Viterbi, maximising sum Re{e^{-j pi v/p} z}.  z complex[n_steps, n_h*n_filt].
+        Returns symbol INDICES (0..M-1) uint8[n_steps]; decision delay = depth-1 steps, the tail is
+        flushed from the best final state.  All states start equal (unknown start)."""
+        M, Lp, p2 = self.M, self.Lp, 2 * self.p
+        bits = max(1, (M - 1).bit_length())
+        D = depth or (64 // bits)
+        n_steps = z.shape[0]
+        NS, NH = self.n_states, self.n_hist
+        pm = np.zeros(NS)
+        hist = np.zeros(NS, dtype=np.uint64)
+        rot = np.exp(-1j * np.pi * np.arange(p2) / self.p)
+        out = np.zeros(n_steps, dtype=np.uint8)
+        mask = np.uint64((1 << 64) - 1) if D * bits >= 64 else np.uint64((1 << (D * bits)) - 1)
+        sp = np.arange(NS)
+        vnew, hnew = sp // NH, sp % NH          # next state = (v', [a_0 .. a_{Lp-2}])
+        for i in range(n_steps):
+            par = i % self.n_h
+            K_leave = self.h_num[(i - Lp + 1) % self.n_h]
+            zi = z[i, par * self.n_filt:(par + 1) * self.n_filt]
+            best = np.full(NS, -np.inf)
+            arg = np.zeros(NS, dtype=np.int64)
+            argx = np.zeros(NS, dtype=np.int64)
+            for x in range(M):                   # x = index of the symbol leaving the window
+                vpred = (vnew - K_leave * self.alphabet[x]) % p2
+                if Lp == 1:
+                    pred, f = vpred, np.full(NS, x)
+                else:
+                    pred = vpred * NH + (hnew % (NH // M)) * M + x
+                    f = hnew * M + x
+                cand = pm[pred] + np.real(rot[vpred] * zi[f])
+                take = cand > best               # strict: the lowest x wins ties
+                best = np.where(take, cand, best)
+                arg = np.where(take, pred, arg)
+                argx = np.where(take, x, argx)
+            newest = argx if Lp == 1 else hnew // (NH // M)   # symbol index of step i
+            hist = ((hist[arg] << np.uint64(bits)) | newest.astype(np.uint64)) & mask
+            pm = best - best.max()
+            if i >= D - 1:
+                s = int(np.argmax(pm))
+                out[i - D + 1] = int((hist[s] >> np.uint64((D - 1) * bits)) & np.uint64((1 << bits) - 1))
+        s = int(np.argmax(pm))
+        for d in range(min(D - 1, n_steps)):
+            out[n_steps - 1 - d] = int((hist[s] >> np.uint64(d * bits)) & np.uint64((1 << bits) - 1))
+        return out

@@ -381,3 +381,32 @@ def test_link_batching_independence_and_e2e_host_call():
     first = LinkSimulator(cfg, device=DEV, max_batch=64).run([3.0, 6.0], 32)
     second = LinkSimulator(cfg, device=DEV, max_batch=64).run([3.0, 6.0], 32, first_frame=32)
     assert np.array_equal(first + second, a)  # frame sharding (multi-GPU) adds up exactly
+
+
+def test_ber_waterfall_inside_reference_confidence_intervals():
+    """north_star: simulated BER (Philox noise) against the REFERENCE's own waterfall (G10: the
+    reference run on 96 frames x 13 Eb/N0 points, both detectors).  The reference interval is
+    Clopper-Pearson 95 % around the reference's estimate; our estimate uses 2048 frames per point
+    (8.4e6 bits).  Every point must agree with the reference within 3.5 combined standard
+    deviations, and at least 24 of the 26 (point, detector) pairs must fall inside the reference's
+    95 % interval (26 independent 95 % intervals are expected to miss 1.3 times by chance)."""
+    from waveforms_b200.linksim import ber_confidence_interval
+
+    g = golden("g10_ber_table.npz")
+    eb = g["ebn0_db"].astype(float)
+    n_ref = g["compared"]
+    inside, report = 0, []
+    for det, key in (("PAM", "pam_errors"), ("PT", "pt_errors")):
+        got = LinkSimulator(LinkConfig(detector=det), device=DEV, max_batch=2048).run(eb, 2048, first_frame=10_000)
+        for k in range(eb.size):
+            e_ref, p_ref = int(g[key][k]), g[key][k] / n_ref[k]
+            p_us = got[k, 0] / got[k, 2]
+            lo, hi = ber_confidence_interval(e_ref, int(n_ref[k]))
+            ok = lo <= p_us <= hi
+            inside += ok
+            report.append((det, eb[k], p_ref, p_us, lo, hi, ok))
+            sd = np.sqrt(p_ref * (1 - p_ref) / n_ref[k] + p_us * (1 - p_us) / got[k, 2])
+            assert abs(p_us - p_ref) <= 3.5 * sd + 1e-12, (det, eb[k], p_ref, p_us)
+    for r in report:
+        print("%s %4.1f dB ref %.4e ours %.4e CI [%.4e, %.4e] %s" % r)
+    assert inside >= 24, report

@@ -174,6 +174,18 @@ def mf(rx, taps, comb, sps, n_calls, dtype, first=0):
     return out[:, :n_calls]
 
 
+def mf_center(rx, taps, sps, n_calls, dtype, first, center):
+    B, T = rx.shape
+    n_filt, n_taps = taps.shape
+    out = np.zeros((B, n_calls, n_filt), np.complex64 if dtype == 0 else np.complex128)
+    rxx = np.ascontiguousarray(rx.astype(out.dtype))
+    tr, trp = darr(taps.real.ravel())
+    ti, tip = darr(taps.imag.ravel())
+    ok(L.wf_mf_bank(ptr(rxx), dtype, B, T, T, trp, tip, n_filt, n_taps, center, None, None, n_filt, sps, first, n_calls,
+                    ptr(out), n_calls, None))
+    return out
+
+
 def pam_tables(pulse, h, sps):
     rho = o.rho_pulses(pulse, h, sps, 2)
     d = max(r.size for r in rho)
@@ -339,7 +351,45 @@ def t_lean():
         assert np.array_equal(cnt, want), (B, n_calls, S, dtype, cnt, want)
 
 
-TESTS = {"lfsr": t_lfsr, "prbs": t_prbs, "mod": t_mod, "mf": t_mf, "vit": t_vit, "noise": t_noise, "stream": t_stream, "lean": t_lean}
+def t_cpm():
+    """generic CPM detector (PCM/FM, multi-h) vs oracle/cpm_generic.py, bank + trellis"""
+    from oracle.cpm_generic import CpmTrellis
+    rng = np.random.default_rng(11)
+    cases = (("pcmfm", o.pulse_pcmfm(8, 4), [7], 10, 2, 2, 512), ("pcmfm1", o.pulse_pcmfm(8, 4), [7], 10, 2, 1, 256),
+             ("multih", o.pulse_multih(8), [4, 5], 16, 4, 2, 600), ("multih1", o.pulse_multih(8), [4, 5], 16, 4, 1, 200))
+    for name, pulse, hnum, p, M, Lp, nbits in cases:
+        tr = CpmTrellis(pulse, hnum, p, M, 8, Lp)
+        B = 3
+        bits = rng.integers(0, 2, (B, nbits)).astype(np.uint8)
+        syms = np.stack([o.map_pcmfm(b) if M == 2 else o.map_multih(b) for b in bits])
+        S = syms.shape[1]
+        bps = 1 if M == 2 else 2
+        sg = o.sigma_from_ebn0_db(5.0, 8, bps)
+        rx = np.stack([o.cpm_modulate_closed_form(sy, np.array(hnum) / p, pulse, 8) * np.exp(-1j * np.pi / 4) for sy in syms])
+        rx = rx + sg * (rng.normal(size=rx.shape) + 1j * rng.normal(size=rx.shape))
+        taps = tr.bank_taps()
+        for dtype in (1, 0):
+            z = mf_center(rx, taps, 8, S, dtype, tr.first_instant, 7)
+            zref = np.stack([tr.bank(r, S) for r in rx])
+            err = np.max(np.abs(z - zref))
+            assert err < (1e-9 if dtype else 2e-4), (name, dtype, err)
+            zz = np.ascontiguousarray(z)
+            dec = np.zeros((B, S), np.int8)
+            cnt = np.zeros((1, 3), np.int64)
+            hn = np.array(hnum, np.int32)
+            ok(L.wf_viterbi_cpm(ptr(zz), dtype, B, S, S, M, Lp, p, ptr(hn), len(hnum), 0, ptr(dec), ptr(np.ascontiguousarray(syms)), S, 4, 4,
+                                None, ptr(cnt), None))
+            ref = np.stack([2 * tr.detect(zref[b]).astype(np.int64) - (M - 1) for b in range(B)])
+            nd = int(np.sum(dec != ref))
+            se = int(np.sum(ref[:, 4:S - 4] != syms[:, 4:S - 4]))
+            print(f"  {name} dtype={dtype}: bank err {err:.1e}, decisions differing from oracle {nd}, symbol errors {cnt[0,1]} (oracle {se})")
+            if dtype == 1:
+                assert nd == 0 and cnt[0, 1] == se and cnt[0, 2] == B * (S - 8)
+            else:
+                assert nd <= 2
+
+
+TESTS = {"lfsr": t_lfsr, "prbs": t_prbs, "mod": t_mod, "mf": t_mf, "vit": t_vit, "noise": t_noise, "stream": t_stream, "lean": t_lean, "cpm": t_cpm}
 
 if __name__ == "__main__":
     names = sys.argv[1:] or list(TESTS)

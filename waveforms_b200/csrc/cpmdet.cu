@@ -1,0 +1,200 @@
+// cpmdet.cu -- A11/A12: generic pulse-truncated coherent CPM trellis detector
+// (PCM/FM, ARTM multi-h CPM, any M-ary single/multi-h CPM).  The reference has NO detector
+// for these waveforms (waveforms.viterbi exports only SOQPSKTrellisDetector); the design
+// generalises its pulse-truncation bank + Re{e^{-j theta} z} metric
+// (examples/soqpsk_detection.py:134-156, viterbi/algorithm.py:57-63) and is specified by the
+// float64 statement oracle/cpm_generic.py (parity unpinned).
+//
+// One WARP per frame, lane-per-state: state s = v * M^(Lp-1) + hist with v the phase state
+// (theta = pi v / p, v in Z_2p) and hist the Lp-1 newest symbols; lane l owns states l, l+32, ...
+// Path metrics and REGISTER-EXCHANGE survivor words (the last `depth` symbols of each survivor,
+// 64 bits) ping-pong in shared memory, so there is no traceback: each step emits the oldest symbol
+// of the best survivor.  Per step the warp stages the bank outputs of the step, every lane does M
+// add-compare-selects per owned state, then two warp reductions (max for normalisation, argmax for
+// the output) run on shuffles.
+#include "common.cuh"
+#include <math.h>
+#include <string.h>
+#include <type_traits>
+
+namespace wf {
+
+constexpr int kCpmWarps = 4;
+constexpr int kCpmMaxStates = 256;
+constexpr int kCpmMaxCols = 128;  // n_h * M^Lp bank outputs per step
+constexpr int kCpmMaxH = 8;
+
+struct CpmParams {
+  const void* z;
+  int8_t* dec_syms;
+  const int8_t* tx_syms;
+  const int32_t* point;
+  unsigned long long* counters;
+  int64_t B, n_steps, ld_z, S, skip_head, skip_tail;
+  int M, Lp, p, n_h, depth, bits, n_filt, n_hist, n_states, n_cols;
+  int delta[kCpmMaxH][16];  // (K_h * alphabet[x]) mod 2p
+};
+
+template <typename T>
+__global__ void __launch_bounds__(kCpmWarps * 32)
+viterbi_cpm_kernel(const __grid_constant__ CpmParams p) {
+  using C = typename std::conditional<sizeof(T) == 4, float2, double2>::type;
+  __shared__ T pm_s[kCpmWarps][2][kCpmMaxStates];
+  __shared__ unsigned long long hist_s[kCpmWarps][2][kCpmMaxStates];
+  __shared__ C z_s[kCpmWarps][kCpmMaxCols];
+  __shared__ T rot_c[64], rot_s[64];
+
+  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+  const int p2 = 2 * p.p;
+  for (int i = threadIdx.x; i < p2; i += blockDim.x) {
+    double sn, cs;
+    sincospi((double)i / (double)p.p, &sn, &cs);
+    rot_c[i] = (T)cs;
+    rot_s[i] = (T)sn;
+  }
+  __syncthreads();
+  const int64_t frame = (int64_t)blockIdx.x * kCpmWarps + wid;
+  if (frame >= p.B) return;  // whole warp; no block barrier after this point
+
+  const int M = p.M, Lp = p.Lp, NS = p.n_states, NH = p.n_hist, bits = p.bits, D = p.depth;
+  const int NHM = NH >= M ? NH / M : 1;
+  const unsigned long long hmask = (D * bits >= 64) ? ~0ull : ((1ull << (D * bits)) - 1ull);
+  const unsigned sym_mask = (1u << bits) - 1u;
+  const C* zrow = reinterpret_cast<const C*>(p.z) + frame * p.ld_z * p.n_cols;
+  const int8_t* tx = p.tx_syms ? p.tx_syms + frame * p.S : nullptr;
+  int8_t* out = p.dec_syms ? p.dec_syms + frame * p.n_steps : nullptr;
+  const int64_t n_steps = p.n_steps;
+  const int64_t cmp_lo = p.skip_head, cmp_hi = min(p.S, n_steps) - p.skip_tail;
+
+  T* pm[2] = {pm_s[wid][0], pm_s[wid][1]};
+  unsigned long long* hs[2] = {hist_s[wid][0], hist_s[wid][1]};
+  for (int s = lane; s < NS; s += 32) { pm[0][s] = (T)0; hs[0][s] = 0ull; }
+  __syncwarp();
+
+  unsigned long long sym_err = 0, bit_err = 0, compared = 0;
+  auto emit = [&](int64_t idx, unsigned v) {  // lane 0 only
+    const int a = 2 * (int)v - (M - 1);
+    if (out) out[idx] = (int8_t)a;
+    if (tx && idx >= cmp_lo && idx < cmp_hi) {
+      const unsigned t = (unsigned)(((int)tx[idx] + (M - 1)) >> 1);
+      sym_err += (t != v) ? 1u : 0u;
+      bit_err += __popc((t ^ v) & sym_mask);
+      ++compared;
+    }
+  };
+
+  int cur = 0;
+  for (int64_t i = 0; i < n_steps; ++i) {
+    const int par = (int)(i % p.n_h);
+    int lpar = (int)((i - Lp + 1) % p.n_h);
+    if (lpar < 0) lpar += p.n_h;
+    const C* zi = zrow + i * p.n_cols + par * p.n_filt;
+    for (int f = lane; f < p.n_filt; f += 32) z_s[wid][f] = zi[f];
+    __syncwarp();
+    const T* pmo = pm[cur];
+    const unsigned long long* ho = hs[cur];
+    T* pmn = pm[cur ^ 1];
+    unsigned long long* hn = hs[cur ^ 1];
+    T lane_max = (T)-1e300;
+    if (sizeof(T) == 4) lane_max = (T)-3.0e38f;
+    for (int s = lane; s < NS; s += 32) {
+      const int vnew = s / NH, hnew = s - vnew * NH;
+      T best = lane_max;  // overwritten by x = 0 below
+      int arg = 0, argx = 0;
+      for (int x = 0; x < M; ++x) {
+        int vpred = vnew - p.delta[lpar][x];
+        if (vpred < 0) vpred += p2;
+        const int pred = (Lp == 1) ? vpred : vpred * NH + (hnew % NHM) * M + x;
+        const int f = (Lp == 1) ? x : hnew * M + x;
+        const C zz = z_s[wid][f];
+        // pm + Re{e^{-j pi v/p} z} = pm + (cos * zr + sin * zi), evaluated in this order
+        const T cand = pmo[pred] + (rot_c[vpred] * zz.x + rot_s[vpred] * zz.y);
+        if (x == 0 || cand > best) { best = cand; arg = pred; argx = x; }
+      }
+      const unsigned newest = (Lp == 1) ? (unsigned)argx : (unsigned)(hnew / NHM);
+      hn[s] = ((ho[arg] << bits) | (unsigned long long)newest) & hmask;
+      pmn[s] = best;
+      lane_max = (s == lane) ? best : (best > lane_max ? best : lane_max);
+    }
+    // warp max (for normalisation) and argmax with the LOWEST state index on ties
+    T wmax = lane_max;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+      const T t = __shfl_xor_sync(0xFFFFFFFFu, wmax, o);
+      wmax = t > wmax ? t : wmax;
+    }
+    __syncwarp();
+    int best_s = 0x7FFFFFFF;
+    for (int s = lane; s < NS; s += 32) {
+      const T v = pmn[s];
+      if (v == wmax && s < best_s) best_s = s;
+      pmn[s] = v - wmax;
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+      const int t = __shfl_xor_sync(0xFFFFFFFFu, best_s, o);
+      best_s = t < best_s ? t : best_s;
+    }
+    __syncwarp();
+    cur ^= 1;
+    if (lane == 0 && i >= D - 1) emit(i - D + 1, (unsigned)((hs[cur][best_s] >> ((D - 1) * bits)) & sym_mask));
+    if (i == n_steps - 1 && lane == 0) {  // flush the tail from the best final survivor
+      const unsigned long long h = hs[cur][best_s];
+      for (int d = 0; d < D - 1 && d < n_steps; ++d) emit(n_steps - 1 - d, (unsigned)((h >> (d * bits)) & sym_mask));
+    }
+  }
+  if (lane == 0 && p.counters) {
+    const int64_t pt = p.point ? p.point[frame] : 0;
+    atomicAdd(&p.counters[3 * pt + 0], bit_err);
+    atomicAdd(&p.counters[3 * pt + 1], sym_err);
+    atomicAdd(&p.counters[3 * pt + 2], compared);
+  }
+}
+
+}  // namespace wf
+
+extern "C" int wf_viterbi_cpm(const void* d_z, int dtype, int64_t B, int64_t n_steps, int64_t ld_z, int M, int Lp,
+                              int p, const int32_t* h_num, int n_h, int depth, int8_t* d_dec_syms,
+                              const int8_t* d_tx_syms, int64_t S, int64_t skip_head, int64_t skip_tail,
+                              const int32_t* d_point, int64_t* d_counters, void* stream) {
+  using namespace wf;
+  WF_REQUIRE(B >= 0 && n_steps >= 0 && ld_z >= n_steps, "bad shape");
+  WF_REQUIRE(dtype == WF_F32 || dtype == WF_F64, "dtype must be WF_F32 or WF_F64");
+  WF_REQUIRE(M >= 2 && M <= 16 && (M & (M - 1)) == 0, "alphabet size M must be a power of two in 2..16");
+  WF_REQUIRE(Lp >= 1 && Lp <= 4 && p >= 1 && 2 * p <= 64, "need 1 <= Lp <= 4 and p <= 32");
+  WF_REQUIRE(n_h >= 1 && n_h <= kCpmMaxH && h_num, "n_h outside 1..8");
+  CpmParams q;
+  memset(&q, 0, sizeof(q));
+  q.M = M; q.Lp = Lp; q.p = p; q.n_h = n_h;
+  q.bits = 0;
+  while ((1 << q.bits) < M) ++q.bits;
+  q.n_filt = 1;
+  for (int i = 0; i < Lp; ++i) q.n_filt *= M;
+  q.n_hist = q.n_filt / M;
+  q.n_states = 2 * p * q.n_hist;
+  q.n_cols = n_h * q.n_filt;
+  WF_REQUIRE(q.n_states <= kCpmMaxStates, "trellis has %d states (max %d)", q.n_states, kCpmMaxStates);
+  WF_REQUIRE(q.n_cols <= kCpmMaxCols, "bank has %d outputs per step (max %d)", q.n_cols, kCpmMaxCols);
+  q.depth = depth > 0 ? depth : 64 / q.bits;
+  WF_REQUIRE(q.depth >= 1 && q.depth * q.bits <= 64, "survivor depth x bits/symbol exceeds 64");
+  WF_REQUIRE(skip_head >= 0 && skip_tail >= 0, "negative skip");
+  WF_REQUIRE(!d_tx_syms || d_counters, "error counting needs d_counters");
+  for (int h = 0; h < n_h; ++h)
+    for (int x = 0; x < M; ++x) {
+      int d = (h_num[h] * (2 * x - (M - 1))) % (2 * p);
+      if (d < 0) d += 2 * p;
+      q.delta[h][x] = d;
+    }
+  int rc;
+  if ((rc = require_device())) return rc;
+  if (B == 0 || n_steps == 0) return WF_OK;
+  WF_REQUIRE(d_z, "d_z is NULL");
+  q.z = d_z; q.dec_syms = d_dec_syms; q.tx_syms = d_tx_syms; q.point = d_point;
+  q.counters = reinterpret_cast<unsigned long long*>(d_counters);
+  q.B = B; q.n_steps = n_steps; q.ld_z = ld_z; q.S = S; q.skip_head = skip_head; q.skip_tail = skip_tail;
+  const unsigned grid = (unsigned)((B + kCpmWarps - 1) / kCpmWarps);
+  if (dtype == WF_F32) viterbi_cpm_kernel<float><<<grid, kCpmWarps * 32, 0, as_stream(stream)>>>(q);
+  else viterbi_cpm_kernel<double><<<grid, kCpmWarps * 32, 0, as_stream(stream)>>>(q);
+  WF_LAUNCH_CHECK("viterbi_cpm_kernel");
+  return WF_OK;
+}

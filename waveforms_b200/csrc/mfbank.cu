@@ -20,7 +20,16 @@ namespace wf {
 
 constexpr int kMfThreads = 128;
 constexpr int kMfMaxTapEntries = 448;  // n_filt * n_taps
-constexpr int kMfMaxComb = 16;         // n_out * n_filt
+constexpr int kMfMaxComb = 96;         // n_out * n_filt
+
+// row stride (complex elements) of the transposed tile; 2*qs*R == 4 (mod 32) words keeps the
+// transposing stores spread over the banks for sps = 8
+__host__ __device__ constexpr int mf_qs(int sps, int nt, int R) {
+  const int sym = R * kMfThreads;
+  int qs = (((sym - 1) * sps + nt - 1) / sps) / R + 2;
+  for (int guard = 0; guard < 16 && (qs * R) % 16 != 2; ++guard) ++qs;
+  return qs;
+}
 
 template <typename T> struct Cplx;
 template <> struct Cplx<float> { using type = float2; };
@@ -53,7 +62,7 @@ mf_bank_kernel(const __grid_constant__ MfParams<T> p) {
   const int nt = CT ? NT : p.n_taps;
   const int nf = CT ? NF : p.n_filt;
   const int n_out = p.n_out;
-  const int qs = p.qs;
+  const int qs = CT ? mf_qs(SPS > 0 ? SPS : 1, NT > 0 ? NT : 1, R) : p.qs;  // compile-time stride: LDS with immediate offsets
   const int tid = threadIdx.x;
   constexpr int SYM = R * kMfThreads;
 
@@ -120,7 +129,7 @@ mf_bank_kernel(const __grid_constant__ MfParams<T> p) {
   __syncthreads();
 
   // ---- R calls per thread ----------------------------------------------------------
-  constexpr int NFM = CT ? NF : 8;
+  constexpr int NFM = CT ? NF : 32;  // run-time shape: up to 32 filters (multi-h bank), accumulators in local memory
   T yr[R][NFM], yi[R][NFM];
 #pragma unroll
   for (int e = 0; e < R; ++e)
@@ -209,10 +218,7 @@ mf_bank_kernel(const __grid_constant__ MfParams<T> p) {
 template <typename T>
 static size_t mf_smem_bytes(int sps, int nt, int R, int n_out, int& qs) {
   const int SYM = R * kMfThreads;
-  const int qmax = ((SYM - 1) * sps + nt - 1) / sps;  // largest q
-  qs = qmax / R + 2;
-  // 2*qs*R == 4 (mod 32) words keeps the transposing stores conflict free for sps = 8 (float)
-  for (int guard = 0; guard < 16 && (qs * R) % 16 != 2; ++guard) ++qs;
+  qs = mf_qs(sps, nt, R);
   size_t in_bytes = (size_t)sps * R * qs * 2 * sizeof(T);
   size_t out_bytes = (size_t)SYM * n_out * 2 * sizeof(T);
   return in_bytes > out_bytes ? in_bytes : out_bytes;
@@ -276,7 +282,7 @@ int wf_mf_bank(const void* d_rx, int dtype, int64_t B, int64_t T, int64_t ld_rx,
   using namespace wf;
   WF_REQUIRE(B >= 0 && T >= 0 && n_calls >= 0, "negative shape");
   WF_REQUIRE(dtype == WF_F32 || dtype == WF_F64, "dtype must be WF_F32 or WF_F64");
-  WF_REQUIRE(taps_re && n_filt >= 1 && n_filt <= 8 && n_taps >= 1, "bad filter bank shape (1..8 filters)");
+  WF_REQUIRE(taps_re && n_filt >= 1 && n_filt <= 32 && n_taps >= 1, "bad filter bank shape (1..32 filters)");
   WF_REQUIRE(n_filt * n_taps <= kMfMaxTapEntries, "filter bank has %d taps in total (max %d)", n_filt * n_taps, kMfMaxTapEntries);
   WF_REQUIRE(sps >= 1 && sps <= 64, "sps=%d outside 1..64", sps);
   WF_REQUIRE(ld_rx >= T && ld_out >= n_calls, "leading dimension too small");

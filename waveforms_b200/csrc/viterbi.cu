@@ -269,23 +269,28 @@ viterbi_soqpsk_l2_kernel(const __grid_constant__ VitParams<T> p) {
     }
     __syncwarp();
     const C* row = &tile[c & 1][threadIdx.x * PITCH];
-#pragma unroll
-    for (int u = 0; u < CH; ++u) {
+    auto one_call = [&](int u, int par) {
       const int i = c0 + u;
-      if (c0 + CH <= n_calls || i < n_calls) {
-        T zr[3], zi[3];
+      T zr[3], zi[3];
 #pragma unroll
-        for (int r = 0; r < 3; ++r) { const C v = row[u * 3 + r]; zr[r] = v.x; zi[r] = v.y; }
-        const uint32_t d = (u & 1) ? detector_call_l2<T, 1, DIFF>(M, zpr, zpi, zr, zi)
-                                   : detector_call_l2<T, 0, DIFF>(M, zpr, zpi, zr, zi);
-        decw |= (d & 1u) << (i & 31);
-        if (FULL) {
-          const int sym = 2 * (int)(d >> 1) - 2;
-          if (ob) ob[i] = (uint8_t)(d & 1u);
-          if (os) os[i] = (int8_t)sym;
-          if (txs && i >= 2 && i - 2 < n_cmp) sym_err += (sym != (int)txs[i - 2]) ? 1u : 0u;
-        }
+      for (int r = 0; r < 3; ++r) { const C v = row[u * 3 + r]; zr[r] = v.x; zi[r] = v.y; }
+      const uint32_t d = par ? detector_call_l2<T, 1, DIFF>(M, zpr, zpi, zr, zi)
+                             : detector_call_l2<T, 0, DIFF>(M, zpr, zpi, zr, zi);
+      decw |= (d & 1u) << (i & 31);
+      if (FULL) {
+        const int sym = 2 * (int)(d >> 1) - 2;
+        if (ob) ob[i] = (uint8_t)(d & 1u);
+        if (os) os[i] = (int8_t)sym;
+        if (txs && i >= 2 && i - 2 < n_cmp) sym_err += (sym != (int)txs[i - 2]) ? 1u : 0u;
       }
+    };
+    if (c0 + CH <= n_calls) {  // whole chunk: one straight-line block, calls overlap in the schedule
+#pragma unroll
+      for (int u = 0; u < CH; ++u) one_call(u, u & 1);
+    } else {
+#pragma unroll
+      for (int u = 0; u < CH; ++u)
+        if (c0 + u < n_calls) one_call(u, u & 1);
     }
     if (((c0 + CH) & 31) == 0) { count_group(c0 + CH - 32); decw = 0; }
     __syncwarp();  // all lanes are done with tile[c & 1] before chunk c+2 is staged into it
