@@ -410,3 +410,60 @@ def test_ber_waterfall_inside_reference_confidence_intervals():
     for r in report:
         print("%s %4.1f dB ref %.4e ours %.4e CI [%.4e, %.4e] %s" % r)
     assert inside >= 24, report
+
+
+# ------------------------------------------------------------------ A11/A12 PCM/FM and multi-h detection
+# (no reference detector exists: parity is against the builder's float64 statement oracle/cpm_generic.py)
+_GEN = {
+    "pcmfm": (lambda: freq_pulse_pcmfm(8, 4), [7], 10, 2, PCMFMSymbolMapper),
+    "multih": (lambda: freq_pulse_multih_irig(8), [4, 5], 16, 4, MultiHSymbolMapper),
+} if torch.cuda.is_available() else {}
+
+
+@pytest.mark.parametrize("name", ["pcmfm", "multih"])
+@pytest.mark.parametrize("memory", [1, 2])
+def test_generic_cpm_detector_vs_oracle(name, memory, pn15_stream):
+    from oracle.cpm_generic import CpmTrellis
+    from waveforms_b200.viterbi.cpm import CPMTrellisDetector
+
+    pf, hnum, p, M, mapper = _GEN[name]
+    pulse = pf()
+    bits = cu(np.stack([pn15_stream[k * 1500:k * 1500 + 1200] for k in range(4)]))
+    syms = mapper()(bits)
+    bps = 1 if M == 2 else 2
+    sg = torch.full((4,), float(o.sigma_from_ebn0_db(5.0, 8, bps)), dtype=torch.float32, device=DEV)
+    rx = wmod.modulate_frames(syms, np.array(hnum) / p, pulse, 8, dtype=torch.complex128, derotate=-np.pi / 4,
+                              sigma=sg, seed=3, first_frame=0)
+    det = CPMTrellisDetector(pulse, hnum, p, M, 8, memory=memory)
+    S = syms.shape[1]
+    z = det.bank(rx, S)
+    counters = torch.zeros((1, 3), dtype=torch.int64, device=DEV)
+    dec = det.detect(z, tx_symbols=syms, counters=counters).cpu().numpy()
+    tr = CpmTrellis(pulse, hnum, p, M, 8, memory)
+    rxh, symh = rx.cpu().numpy(), syms.cpu().numpy()
+    errs = 0
+    for b in range(4):
+        zref = tr.bank(rxh[b], S)
+        assert np.max(np.abs(z[b].cpu().numpy() - zref)) < 1e-9
+        ref = 2 * tr.detect(zref).astype(np.int64) - (M - 1)
+        assert np.array_equal(dec[b], ref), (name, memory, b)
+        errs += int(np.sum(ref[4:S - 4] != symh[b, 4:S - 4]))
+    assert counters[0, 1].item() == errs and counters[0, 2].item() == 4 * (S - 8)
+    # float32 path: same decisions up to float32-resolution ties
+    z32 = det.bank(rx.to(torch.complex64), S)
+    dec32 = det.detect(z32).cpu().numpy()
+    assert int(np.sum(dec32 != dec)) <= 2
+
+
+@pytest.mark.parametrize("name", ["pcmfm", "multih"])
+def test_generic_link_round_trip_and_waterfall(name):
+    """BASELINE configs[1]/[2] at N = 4096: noiseless frames decode without error; BER falls
+    monotonically with Eb/N0 and is below 1e-2 at 9 dB (sanity; no reference curve exists)."""
+    sim = LinkSimulator(LinkConfig(waveform=name), device=DEV, max_batch=1024)
+    counters = torch.zeros((1, 3), dtype=torch.int64, device=DEV)
+    sim.run_batch(77, torch.zeros(1024, dtype=torch.float32, device=DEV), None, counters)
+    be, se, n = counters[0].tolist()
+    assert (be, se) == (0, 0) and n == 1024 * (sim.n_sym - 8)
+    got = sim.run([3.0, 6.0, 9.0], 256)
+    ser = got[:, 1] / got[:, 2]
+    assert ser[0] > ser[1] > ser[2] and ser[2] < 1e-2, ser

@@ -265,6 +265,8 @@ static int launch_mf(const void* d_rx, int64_t B, int64_t Tn, int64_t ld_rx, con
   else if (sps == 8 && n_filt == 3 && n_taps == 9 && !real_taps) WF_MF_CASE(8, 3, 9, true, 2);   // PT bank
   else if (sps == 10 && n_filt == 2 && n_taps == 91 && real_taps) WF_MF_CASE(10, 2, 91, false, 2);
   else if (sps == 10 && n_filt == 3 && n_taps == 11 && !real_taps) WF_MF_CASE(10, 3, 11, true, 2);
+  else if (sps == 8 && n_filt == 4 && n_taps == 8 && !real_taps && !comb_re) WF_MF_CASE(8, 4, 8, true, 2);    // PCM/FM, Lp = 2
+  else if (sps == 8 && n_filt == 32 && n_taps == 8 && !real_taps && !comb_re) WF_MF_CASE(8, 32, 8, true, 1);  // multi-h, Lp = 2
   else WF_MF_CASE(0, 0, 0, true, 1);
 #undef WF_MF_CASE
   WF_LAUNCH_CHECK("mf_bank_kernel");

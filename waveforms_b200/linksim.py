@@ -61,12 +61,12 @@ class LinkSimulator:
     def __init__(self, cfg: LinkConfig | None = None, device=None, max_batch: int = 4096) -> None:
         self.cfg = cfg = cfg or LinkConfig()
         self.device = torch.device(device) if device is not None else _dev.default_device()
+        self._max_batch_arg = int(max_batch)
         if cfg.waveform not in WAVEFORMS:
             raise KeyError(f"unknown waveform {cfg.waveform!r}; choose from {sorted(WAVEFORMS)}")
         enc, h, pulse_fn, bps = WAVEFORMS[cfg.waveform]
-        if not cfg.waveform.startswith("soqpsk"):
-            raise NotImplementedError("LinkSimulator detects SOQPSK waveforms; use cpm.modulate for the others")
-        self.encoder = enc if cfg.differential else _ffi.ENC_SOQPSK
+        self.soqpsk = cfg.waveform.startswith("soqpsk")
+        self.encoder = (enc if cfg.differential else _ffi.ENC_SOQPSK) if self.soqpsk else enc
         self.h = _dev.host_f64(h)
         self.bits_per_symbol = bps
         self.pulse = _dev.host_f64(pulse_fn(cfg.sps))
@@ -74,6 +74,9 @@ class LinkSimulator:
         self.period = (1 << cfg.pn_degree) - 1
         self.n_sym = cfg.n_bits // bps
         self.n_samples = (self.n_sym + 1) * cfg.sps
+        if not self.soqpsk:
+            self._init_generic(h, bps)
+            return
         self.first_instant, self.n_calls = _mf.symbol_instants(self.n_samples, cfg.sps, cfg.timing_offset, cfg.length)
         self.n_compared = max(0, min(self.n_sym, self.n_calls - cfg.length))
         if cfg.detector.upper() == "PAM":
@@ -92,17 +95,40 @@ class LinkSimulator:
         self._alloc(int(max_batch))
         self.launches = 0  # kernels launched so far (4 per run_batch)
 
+    def _init_generic(self, h, bps) -> None:
+        """PCM/FM and multi-h: generic pulse-truncated trellis detector (no reference detector exists)."""
+        from fractions import Fraction
+
+        from .viterbi.cpm import CPMTrellisDetector
+
+        cfg = self.cfg
+        fr = [Fraction(float(x)).limit_denominator(64) for x in h]
+        den = int(np.lcm.reduce([f.denominator for f in fr]))
+        self.det = CPMTrellisDetector(self.pulse, [int(f * den) for f in fr], den, 2 ** bps, cfg.sps,
+                                      memory=int(cfg.extra.get("memory", 2)), depth=int(cfg.extra.get("depth", 0)))
+        self.skip = int(cfg.extra.get("skip", 4))
+        self.first_instant, self.n_calls = self.det.first_instant, self.n_sym
+        self.n_compared = max(0, self.n_sym - 2 * self.skip)
+        self._taps = self.det.taps
+        self._tap_re = _dev.host_f64(self._taps.real.ravel())
+        self._tap_im = _dev.host_f64(self._taps.imag.ravel())
+        self._comb_re = self._comb_im = None
+        self._n_out = self._taps.shape[0]
+        self.max_batch = 0
+        self._alloc(int(self._max_batch_arg))
+        self.launches = 0
+
     # ------------------------------------------------------------------ buffers
     def _alloc(self, max_batch: int) -> None:
         cfg, dev = self.cfg, self.device
         self.max_batch = max_batch
         self.ld_words = (cfg.n_bits + 31) // 32
         self.ld_rx = (self.n_samples + 1) & ~1
-        self.ld_z = (self.n_calls + 3) & ~3
+        self.ld_z = (self.n_calls + 3) & ~3 if self.soqpsk else self.n_calls
         self.packed = torch.zeros((max_batch, self.ld_words), dtype=torch.int32, device=dev)
         self.syms = torch.empty((max_batch, self.n_sym), dtype=torch.int8, device=dev)
         self.rx = torch.empty((max_batch, self.ld_rx), dtype=cfg.dtype, device=dev)
-        self.z = torch.empty((max_batch, self.ld_z, 3), dtype=cfg.dtype, device=dev)
+        self.z = torch.empty((max_batch, self.ld_z, self._n_out), dtype=cfg.dtype, device=dev)
 
     def workspace_bytes(self) -> int:
         return sum(t.numel() * t.element_size() for t in (self.packed, self.syms, self.rx, self.z))
@@ -140,11 +166,20 @@ class LinkSimulator:
             mark()
             _ffi.check(lib.wf_mf_bank(_dev.ptr(self.rx), dt, B, self.n_samples, self.ld_rx, _dev.f64_ptr(self._tap_re),
                                       None if self._tap_im is None else _dev.f64_ptr(self._tap_im),
-                                      self._taps.shape[0], self._taps.shape[1], (self._taps.shape[1] - 1) // 2,
+                                      self._taps.shape[0], self._taps.shape[1],
+                                      (self._taps.shape[1] - 1) // 2 if self.soqpsk else cfg.sps - 1,
                                       None if self._comb_re is None else _dev.f64_ptr(self._comb_re),
                                       None if self._comb_im is None else _dev.f64_ptr(self._comb_im), self._n_out,
                                       cfg.sps, self.first_instant, self.n_calls, _dev.ptr(self.z), self.ld_z, st))
             mark()
+            if not self.soqpsk:
+                d = self.det
+                _ffi.check(lib.wf_viterbi_cpm(_dev.ptr(self.z), dt, B, self.n_calls, self.ld_z, d.M, d.Lp, d.p,
+                                              d.h_num.ctypes.data, d.n_h, d.depth, None, _dev.ptr(self.syms), self.n_sym,
+                                              self.skip, self.skip, _dev.ptr(point), _dev.ptr(counters), st))
+                mark()
+                self.launches += 4
+                return
             _ffi.check(lib.wf_viterbi_soqpsk(_dev.ptr(self.z), dt, B, self.n_calls, self.ld_z, int(cfg.differential),
                                              cfg.length, None, None, _dev.ptr(self.packed), self.ld_words, None,
                                              self.n_sym, _dev.ptr(point), _dev.ptr(counters), None, st))
