@@ -60,6 +60,31 @@ __host__ __device__ __forceinline__ u32x4 philox4x32_10(u32x4 c, uint32_t k0, ui
   return c;
 }
 
+// Same function with the ten round keys (k + r W) precomputed by the host: they are then
+// constant-bank operands of the XORs instead of per-call integer adds.
+struct PhiloxKeys { uint32_t k[20]; };
+static inline PhiloxKeys philox_round_keys(uint64_t seed) {
+  PhiloxKeys rk;
+  uint32_t k0 = (uint32_t)seed, k1 = (uint32_t)(seed >> 32);
+  for (int r = 0; r < 10; ++r) { rk.k[2 * r] = k0; rk.k[2 * r + 1] = k1; k0 += 0x9E3779B9u; k1 += 0xBB67AE85u; }
+  return rk;
+}
+__host__ __device__ __forceinline__ u32x4 philox4x32_10_rk(u32x4 c, const PhiloxKeys& rk) {
+  const uint32_t M0 = 0xD2511F53u, M1 = 0xCD9E8D57u;
+#pragma unroll
+  for (int r = 0; r < 10; ++r) {
+    uint32_t hi0 = mulhi32(M0, c.x), lo0 = M0 * c.x;
+    uint32_t hi1 = mulhi32(M1, c.z), lo1 = M1 * c.z;
+    u32x4 n;
+    n.x = hi1 ^ c.y ^ rk.k[2 * r];
+    n.y = lo1;
+    n.z = hi0 ^ c.w ^ rk.k[2 * r + 1];
+    n.w = lo0;
+    c = n;
+  }
+  return c;
+}
+
 // Counter layout shared by every noise kernel: results depend only on
 // (seed, point, global frame, sample pair) -- never on batching or sharding.
 __host__ __device__ __forceinline__ u32x4 noise_counter(uint64_t pair, uint64_t frame, uint32_t point) {
@@ -92,18 +117,18 @@ __device__ __forceinline__ float fast_log2(float x) {  // MUFU.LG2 without the d
 #endif
 }
 
-// Box-Muller on two 32-bit uniforms -> one complex N(0,1)+jN(0,1) sample.
-// Uniforms are built from mantissa bits (no I2F on the XU pipe, which already
-// carries LG2/SQRT/SIN/COS).  u1's top 23 bits give x in (0,1); when they are all
-// zero (p = 2^-23) the low 9 bits refine the tail, so radii reach
-// sqrt(2 ln 2^33) = 6.76 sigma instead of clipping at 5.65.
-__device__ __forceinline__ float2 box_muller(uint32_t u1, uint32_t u2) {
-  float x = __uint_as_float(0x3F800000u | (u1 >> 9)) - 1.0f + 5.9604644775390625e-08f;  // (m + 0.5) 2^-23
-  if ((u1 >> 9) == 0u) x = ((float)(u1 & 0x1FFu) + 0.5f) * 2.3283064365386963e-10f;     // (u1 + 0.5) 2^-32
-  // r^2 = -2 ln x = -2 ln2 log2 x
-  float r = fast_sqrt(-1.3862943611198906f * fast_log2(x));
-  // angle uniform in [-pi, pi): (f - 1.5) * 2 pi with f in [1,2), plus half a step
-  float ang = fmaf(__uint_as_float(0x3F800000u | (u2 >> 9)), 6.283185307179586f, -9.42477796f);
+// Box-Muller on two 32-bit uniforms -> one complex sigma*(N(0,1)+jN(0,1)) sample.
+// `coef` = -2 ln2 sigma^2 (see noise_coef): sigma rides inside the radius, so the caller
+// adds the result to the signal with no further multiply.  Uniforms come from I2FP
+// (ALU pipe, not the XU pipe that already carries LG2/SQRT/SIN/COS):
+//   x = (u1 + 0.5) 2^-32 in (0, 1]   -> radii reach sqrt(2 ln 2^33) = 6.76 sigma,
+//   angle = int32(u2) 2 pi 2^-32 in [-pi, pi].
+__device__ __forceinline__ float noise_coef(float sigma) { return -1.3862943611198906f * sigma * sigma; }
+
+__device__ __forceinline__ float2 box_muller(uint32_t u1, uint32_t u2, float coef) {
+  const float x = fmaf((float)u1, 2.3283064365386963e-10f, 1.1641532182693481e-10f);
+  const float r = fast_sqrt(coef * fast_log2(x));  // sigma sqrt(-2 ln x)
+  const float ang = (float)(int32_t)u2 * 1.4629180792671596e-09f;  // 2 pi 2^-32
   float s, c;
   __sincosf(ang, &s, &c);
   return make_float2(r * c, r * s);
@@ -116,6 +141,15 @@ __device__ __forceinline__ void cp_async(void* smem_dst, const void* gmem_src) {
 #else
   const uint32_t d = (uint32_t)__cvta_generic_to_shared(smem_dst);
   asm volatile("cp.async.ca.shared.global [%0], [%1], %2;" ::"r"(d), "l"(gmem_src), "n"(BYTES) : "memory");
+#endif
+}
+// 16-byte copy that bypasses L1 (streaming data read once per block)
+__device__ __forceinline__ void cp_async_cg16(void* smem_dst, const void* gmem_src) {
+#ifdef WF_HOSTEMU
+  memcpy(smem_dst, gmem_src, 16);
+#else
+  const uint32_t d = (uint32_t)__cvta_generic_to_shared(smem_dst);
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(d), "l"(gmem_src) : "memory");
 #endif
 }
 __device__ __forceinline__ void cp_async_commit() {

@@ -215,6 +215,169 @@ mf_bank_kernel(const __grid_constant__ MfParams<T> p) {
   for (int k = tid; k < n_el; k += kMfThreads) out[k] = tile[k];
 }
 
+// ---------------------------------------------------------------------------
+// complex64 register-tiled path (compile-time shapes, even sps, 16-byte aligned rows).
+// Each thread owns R = 4 consecutive calls: R*SPS + NT - SPS staged samples feed
+// R*NT*NF*(2|4) FFMAs, so one 128-bit shared load (two samples) is amortised over up to
+// 2*R*(NT/SPS) FFMA groups.  The rx tile keeps its NATURAL sample order -- it lands in
+// shared memory with 16-byte cp.async.cg straight from HBM, no register round trip, no
+// transposing stores -- and every thread's R*SPS-sample segment is followed by one 16-byte
+// pad: thread stride = (R*SPS/2 + 1) 16-byte units, an odd number, so the eight lanes of a
+// quarter-warp LDS.128 hit eight different bank groups (conflict free).  All shared
+// addresses are thread base + immediate.  Output: R*n_out consecutive values per thread
+// staged through the (reused) tile and stored with coalesced 128-bit words.
+// ---------------------------------------------------------------------------
+template <int SPS, int NT, int R>
+struct MfTile {
+  static constexpr int RS = R * SPS;                       // samples per thread segment
+  static constexpr int SEG = RS + 2;                       // + one 16-byte pad
+  static constexpr int SYM = R * kMfThreads;               // calls per block
+  static constexpr int NSAMP = (SYM - 1) * SPS + NT;       // samples per block tile
+  static constexpr int NV = (R - 1) * SPS + NT;            // samples one thread touches
+  static constexpr int SLOTS = NSAMP + 2 * ((NSAMP + RS - 1) / RS) + 2;
+  __host__ __device__ static constexpr int pos(int m) { return m + 2 * (m / RS); }
+};
+
+template <int SPS, int NF, int NT, bool CPLX, int R>
+__global__ void __launch_bounds__(kMfThreads)
+mf_bank_f32_kernel(const __grid_constant__ MfParams<float> p) {
+  using TL = MfTile<SPS, NT, R>;
+  static_assert((TL::RS % 4) == 0 && (SPS % 2) == 0, "segment stride must be an odd number of 16-byte units");
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  float2* tile = reinterpret_cast<float2*>(smem_raw);
+  const int tid = threadIdx.x;
+  const int n_out = p.n_out;
+
+  const int n_tiles = (int)((p.n_calls + TL::SYM - 1) / TL::SYM);
+  const int frame = (int)(blockIdx.x / (unsigned)n_tiles);  // consecutive blocks share a frame (halo hits L2)
+  const int i0 = ((int)blockIdx.x - frame * n_tiles) * TL::SYM;
+  const int n_sym = min(TL::SYM, (int)p.n_calls - i0);
+  const float2* rx = reinterpret_cast<const float2*>(p.rx) + (int64_t)frame * p.ld_rx;
+  const int n_lo = (int)p.first_instant + i0 * SPS + p.center - (NT - 1);  // even (checked by the launcher)
+  const int Tn = (int)p.Tn;
+
+  // ---- stage: pairs of samples, 16 bytes each; zeros outside [0, T) -------------------
+  // pair pi = tid + 128 k sits at tile offset pos(2 tid) + k (256 + 16): source and
+  // destination both advance by compile-time strides, so the unrolled loop is LDGSTS +
+  // immediates.  Interior tiles skip the bounds checks altogether.
+  {
+    constexpr int NPAIR = (TL::NSAMP + 1) / 2;
+    constexpr int NK = (NPAIR + kMfThreads - 1) / kMfThreads;
+    constexpr int DSTEP = 2 * kMfThreads + 2 * (2 * kMfThreads / TL::RS);  // pos() advance per k
+    constexpr bool kConstStep = (2 * kMfThreads) % TL::RS == 0;  // pair stride = whole segments (sps 8)
+    const float2* src = rx + n_lo + 2 * tid;
+    float2* dst = tile + TL::pos(2 * tid);
+    const bool interior = n_lo >= 0 && n_lo + TL::NSAMP + 1 <= Tn;
+    if (interior) {
+#pragma unroll
+      for (int k = 0; k < NK; ++k) {
+        const int m = 2 * (tid + k * kMfThreads);
+        if ((k + 1) * kMfThreads <= NPAIR || m < TL::NSAMP)
+          cp_async_cg16(kConstStep ? dst + k * DSTEP : tile + TL::pos(m), src + k * 2 * kMfThreads);
+      }
+    } else {
+      const int n0 = n_lo + 2 * tid;
+#pragma unroll
+      for (int k = 0; k < NK; ++k) {
+        const int m = 2 * (tid + k * kMfThreads), n = n0 + k * 2 * kMfThreads;
+        if ((k + 1) * kMfThreads <= NPAIR || m < TL::NSAMP) {
+          float2* d = kConstStep ? dst + k * DSTEP : tile + TL::pos(m);
+          if ((unsigned)n < (unsigned)(Tn - 1)) {
+            cp_async_cg16(d, src + k * 2 * kMfThreads);
+          } else {
+#pragma unroll
+            for (int s = 0; s < 2; ++s) {
+              if (n + s >= 0 && n + s < Tn) cp_async<8>(d + s, rx + n + s);
+              else d[s] = make_float2(0.f, 0.f);
+            }
+          }
+        }
+      }
+    }
+    cp_async_commit();
+    cp_async_wait<0>();
+  }
+  __syncthreads();
+
+  // ---- R calls per thread --------------------------------------------------------------
+  float yr[R][NF], yi[R][NF];
+#pragma unroll
+  for (int e = 0; e < R; ++e)
+#pragma unroll
+    for (int f = 0; f < NF; ++f) { yr[e][f] = 0.f; yi[e][f] = 0.f; }
+
+  const float2* seg = tile + tid * TL::SEG;
+#pragma unroll
+  for (int v = 0; v < TL::NV; v += 2) {
+    float4 xx;
+    if (v + 1 < TL::NV) {
+      xx = *reinterpret_cast<const float4*>(seg + TL::pos(v));
+    } else {
+      const float2 x1 = seg[TL::pos(v)];
+      xx = make_float4(x1.x, x1.y, 0.f, 0.f);
+    }
+#pragma unroll
+    for (int s = 0; s < 2; ++s) {
+      if (v + s < TL::NV) {
+        const float xr = s ? xx.z : xx.x, xi = s ? xx.w : xx.y;
+#pragma unroll
+        for (int e = 0; e < R; ++e) {
+          const int u = v + s - e * SPS;
+          if (u >= 0 && u < NT) {
+            const int tt = NT - 1 - u;
+#pragma unroll
+            for (int f = 0; f < NF; ++f) {
+              const float tr = p.tap_re[f * NT + tt];
+              if (CPLX) {
+                const float ti = p.tap_im[f * NT + tt];
+                yr[e][f] = fmaf(xr, tr, yr[e][f]); yr[e][f] = fmaf(-xi, ti, yr[e][f]);
+                yi[e][f] = fmaf(xr, ti, yi[e][f]); yi[e][f] = fmaf(xi, tr, yi[e][f]);
+              } else {
+                yr[e][f] = fmaf(xr, tr, yr[e][f]);
+                yi[e][f] = fmaf(xi, tr, yi[e][f]);
+              }
+            }
+          }
+        }
+      }
+    }
+  }
+  __syncthreads();  // every thread is done reading the rx tile; reuse it for the output
+
+  // ---- combine + stage the output tile [SYM][n_out] -------------------------------------
+#pragma unroll
+  for (int e = 0; e < R; ++e) {
+    const int s = R * tid + e;
+    if (p.has_comb) {
+      for (int r = 0; r < n_out; ++r) {
+        float zr = 0.f, zi = 0.f;
+#pragma unroll
+        for (int f = 0; f < NF; ++f) {
+          const float cr = p.comb_re[r * NF + f], ci = p.comb_im[r * NF + f];
+          zr = fmaf(cr, yr[e][f], zr); zr = fmaf(-ci, yi[e][f], zr);
+          zi = fmaf(cr, yi[e][f], zi); zi = fmaf(ci, yr[e][f], zi);
+        }
+        tile[s * n_out + r] = make_float2(zr, zi);
+      }
+    } else {
+#pragma unroll
+      for (int f = 0; f < NF; ++f) tile[s * NF + f] = make_float2(yr[e][f], yi[e][f]);
+    }
+  }
+  __syncthreads();
+  float2* out = reinterpret_cast<float2*>(p.out) + ((int64_t)frame * p.ld_out + i0) * n_out;
+  const int n_el = n_sym * n_out;
+  if (((reinterpret_cast<uintptr_t>(out) & 15) == 0)) {
+    const int n4 = n_el >> 1;
+    float4* o4 = reinterpret_cast<float4*>(out);
+    const float4* t4 = reinterpret_cast<const float4*>(tile);
+    for (int k = tid; k < n4; k += kMfThreads) o4[k] = t4[k];
+    if ((n_el & 1) && tid == 0) out[n_el - 1] = tile[n_el - 1];
+  } else {
+    for (int k = tid; k < n_el; k += kMfThreads) out[k] = tile[k];
+  }
+}
+
 template <typename T>
 static size_t mf_smem_bytes(int sps, int nt, int R, int n_out, int& qs) {
   const int SYM = R * kMfThreads;
@@ -261,6 +424,36 @@ static int launch_mf(const void* d_rx, int64_t B, int64_t Tn, int64_t ld_rx, con
   } while (0)
 
   const bool real_taps = taps_im == nullptr;
+  if constexpr (sizeof(T) == 4) {
+    // register-tiled complex64 path: even tile origin, even row pitch, 16-byte aligned rows
+    const bool tiled_ok = (((first_instant + center - (n_taps - 1)) & 1) == 0) && ((ld_rx & 1) == 0) &&
+                          ((reinterpret_cast<uintptr_t>(d_rx) & 15) == 0) && Tn < 0x7FFFFFF0 && n_calls < 0x7FFFFFF0 &&
+                          first_instant < 0x7FFFFFF0 && (!comb_re || n_out <= n_filt + 2);
+#define WF_MFT_CASE(SPS_, NF_, NT_, CPLX_, R_)                                                        \
+  do {                                                                                                \
+    using TL = MfTile<SPS_, NT_, R_>;                                                                 \
+    size_t sm = (size_t)TL::SLOTS * sizeof(float2);                                                   \
+    const size_t so = (size_t)TL::SYM * n_out * sizeof(float2);                                       \
+    if (so > sm) sm = so;                                                                             \
+    auto kfn = mf_bank_f32_kernel<SPS_, NF_, NT_, CPLX_, R_>;                                         \
+    if (sm > 48 * 1024) {                                                                             \
+      cudaError_t e = cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm);\
+      if (e != cudaSuccess) return cuda_fail(e, "cudaFuncSetAttribute(mf_bank_f32_kernel)");          \
+    }                                                                                                 \
+    dim3 grid((unsigned)(((n_calls + TL::SYM - 1) / TL::SYM) * B));                                   \
+    kfn<<<grid, kMfThreads, sm, stream>>>(p);                                                         \
+    WF_LAUNCH_CHECK("mf_bank_f32_kernel");                                                            \
+    return WF_OK;                                                                                     \
+  } while (0)
+    if (tiled_ok) {
+      if (sps == 8 && n_filt == 2 && n_taps == 73 && real_taps) WF_MFT_CASE(8, 2, 73, false, 4);       // PAM bank, TG
+      else if (sps == 8 && n_filt == 3 && n_taps == 9 && !real_taps) WF_MFT_CASE(8, 3, 9, true, 4);   // PT bank
+      else if (sps == 10 && n_filt == 2 && n_taps == 91 && real_taps) WF_MFT_CASE(10, 2, 91, false, 4);
+      else if (sps == 10 && n_filt == 3 && n_taps == 11 && !real_taps) WF_MFT_CASE(10, 3, 11, true, 4);
+      else if (sps == 8 && n_filt == 4 && n_taps == 8 && !real_taps && !comb_re) WF_MFT_CASE(8, 4, 8, true, 4);  // PCM/FM, Lp = 2
+    }
+#undef WF_MFT_CASE
+  }
   if (sps == 8 && n_filt == 2 && n_taps == 73 && real_taps) WF_MF_CASE(8, 2, 73, false, 2);       // PAM bank, TG
   else if (sps == 8 && n_filt == 3 && n_taps == 9 && !real_taps) WF_MF_CASE(8, 3, 9, true, 2);   // PT bank
   else if (sps == 10 && n_filt == 2 && n_taps == 91 && real_taps) WF_MF_CASE(10, 2, 91, false, 2);

@@ -60,6 +60,7 @@ struct ModParams {
   T hw[kMaxH];
   uint64_t hfix[kMaxH];
   T q[kQMax];  // Q[0..K], padded with Q[K]
+  PhiloxKeys rk;  // round keys of `seed`
 };
 
 // SPS > 0: compile-time samples/symbol; JT > 0: compile-time J with the thread's
@@ -99,11 +100,11 @@ cpm_modulate_kernel(const __grid_constant__ ModParams<T> p) {
     c0_s = c0;
   }
 
-  float sig = 0.f;
+  float ncoef = 0.f;
   uint32_t pt = 0;
   uint64_t gframe = 0;
   if (NOISE) {
-    sig = p.sigma[frame];
+    ncoef = noise_coef(p.sigma[frame]);
     pt = p.point ? (uint32_t)p.point[frame] : 0u;
     gframe = p.first_frame + (uint64_t)frame;
   }
@@ -206,9 +207,9 @@ cpm_modulate_kernel(const __grid_constant__ ModParams<T> p) {
       Tr::unit(ph[1], c[1], s[1]);
       if (NOISE) {
         u32x4 r = philox4x32_10(noise_counter((uint64_t)(uint32_t)(n >> 1), gframe, pt), (uint32_t)p.seed, (uint32_t)(p.seed >> 32));
-        float2 g0 = box_muller(r.x, r.y), g1 = box_muller(r.z, r.w);
-        c[0] += (T)(sig * g0.x); s[0] += (T)(sig * g0.y);
-        c[1] += (T)(sig * g1.x); s[1] += (T)(sig * g1.y);
+        float2 g0 = box_muller(r.x, r.y, ncoef), g1 = box_muller(r.z, r.w, ncoef);
+        c[0] += (T)g0.x; s[0] += (T)g0.y;
+        c[1] += (T)g1.x; s[1] += (T)g1.y;
       }
       if (vec_ok && n + 1 < Ti) {
         if (sizeof(T) == 4) {
@@ -230,6 +231,181 @@ cpm_modulate_kernel(const __grid_constant__ ModParams<T> p) {
 }
 
 // ---------------------------------------------------------------------------
+// complex64 fast path for sps = 8 (every SOQPSK / PCM-FM benchmark shape).
+// Same maths as above; what differs is the sample -> thread map.  Four lanes own
+// the four sample PAIRS of one symbol interval and walk kRun consecutive intervals,
+// so the J-symbol window slides through registers (one LDS per new symbol instead
+// of J), every ring / output address is base + immediate, the thread's Q
+// coefficients (pre-scaled to radians) stay in registers, and a warp store covers
+// eight 64-byte runs of full 32-byte sectors.  The frame-start constant and the
+// initial phase ride inside the fixed-point prefix sum, so the phase needs no
+// separate range reduction: angle = fixed(F) * 2pi/2^32 in [-pi, pi) plus the
+// J-tap partial.  Issue-slot budget per sample pair (the binding resource; see
+// DESIGN 4.2): 2J FFMA + ~12 for the signal, ~70 for Philox + Box-Muller, 12 MUFU.
+// ---------------------------------------------------------------------------
+constexpr int kFMirror = 32;    // slots [ring, ring+32) mirror [0, 32): windows of <= 33 never wrap
+
+// RUN consecutive intervals per thread -> 64*RUN intervals per block pass; a scan step adds
+// 4*threads = 1024 symbols, so the ring must hold pass + 1023 + J symbols.
+template <int JT, bool NOISE, int RUN, int MINB>
+__global__ void __launch_bounds__(kModThreads, MINB)
+cpm_modulate_f32s8_kernel(const __grid_constant__ ModParams<float> p) {
+  constexpr int kFRun = RUN;
+  constexpr int kFChunk = RUN * (kModThreads / 4);
+  constexpr int kFRing = (kFChunk + 1024 + 64 <= 2048) ? 2048 : 4096;
+  static_assert(JT + kFRun - 1 <= kFMirror + 1, "window longer than the mirrored tail");
+  __shared__ float w_s[kFRing + kFMirror];
+  __shared__ uint32_t f_s[kFRing + kFMirror];
+  __shared__ uint64_t warp_tot[kModThreads / 32];
+  __shared__ uint64_t base_s;
+
+  const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+  const int64_t frame = blockIdx.x;
+  const int off = p.off;
+  const int S = (int)p.S, Ti = (int)p.Tn;
+  const int8_t* sy = p.syms + frame * (int64_t)S;
+  float4* out = reinterpret_cast<float4*>(reinterpret_cast<float2*>(p.out) + frame * p.ld_out);  // indexed by pair
+  const bool sym_vec = ((S & 3) == 0) && ((reinterpret_cast<uintptr_t>(p.syms) & 3) == 0);
+
+  if (tid == 0) {
+    // per-frame constant folded into the prefix sum: initial phase minus the frame-start
+    // truncation of "same" convolution, sum_k w_k Q[clip(off-(k+1)8, 0, K)] / 8  (turns)
+    double c0 = 0.0;
+    for (int k = 0; k < S && (k + 1) * 8 < off; ++k) {
+      int idx = off - (k + 1) * 8;
+      if (idx > p.K) idx = p.K;
+      c0 += (double)sy[k] * (double)p.hw[k % p.n_h] * (double)p.q[idx];
+    }
+    double t = (double)p.phase0_turns - c0 * 0.125;
+    t -= rint(t);                                                  // [-1/2, 1/2]
+    base_s = (uint64_t)(int64_t)llrint(t * 9223372036854775808.0 * 0.5) << 2;  // t 2^64 without overflowing
+  }
+  __syncthreads();
+  uint64_t carry = base_s;  // F[scanned] (+ the constant)
+  for (int i = tid; i < kFRing + kFMirror; i += kModThreads) { w_s[i] = 0.f; f_s[i] = (uint32_t)(carry >> 32); }
+
+  float ncoef = 0.f;
+  uint32_t pt = 0, fr_lo = 0, fr_hi = 0;
+  if (NOISE) {
+    ncoef = noise_coef(p.sigma[frame]);
+    pt = p.point ? (uint32_t)p.point[frame] : 0u;
+    const uint64_t gframe = p.first_frame + (uint64_t)frame;
+    fr_lo = (uint32_t)gframe; fr_hi = (uint32_t)(gframe >> 32);
+  }
+
+  // a = n + off = 8 A + rho: this thread owns rho = 2 sub, 2 sub + 1 of kFRun consecutive A
+  const int sub = tid & 3, grp = tid >> 2;
+  const int rho = 2 * sub;
+  float qa[JT], qb[JT];
+#pragma unroll
+  for (int j = 0; j < JT; ++j) {
+    qa[j] = p.q[rho + 1 + 8 * j] * 0.78539816339744831f;  // Q * 2 pi / sps  (radians per unit w)
+    qb[j] = p.q[rho + 2 + 8 * j] * 0.78539816339744831f;
+  }
+  const int A_first = off >> 3;
+  const int A_last = (Ti - 1 + off) >> 3;
+  int scanned = 0;
+  const bool one_h = (p.n_h == 1);
+  __syncthreads();
+
+  for (int cs = 0; A_first + cs <= A_last; cs += kFChunk) {
+    // ---- (a) extend the scan so symbols < A_first + cs + chunk are in the ring ----------
+    const int want = cs + kFChunk + A_first;
+    while (scanned < want) {  // uniform across the block; each step adds 4 * threads = chunk symbols
+      const int k0 = scanned + 4 * tid;
+      int a[4];
+      if (sym_vec && k0 + 3 < S) {
+        const uint32_t v = *reinterpret_cast<const uint32_t*>(sy + k0);
+        a[0] = (int8_t)(v & 0xFF); a[1] = (int8_t)((v >> 8) & 0xFF); a[2] = (int8_t)((v >> 16) & 0xFF); a[3] = (int8_t)(v >> 24);
+      } else {
+#pragma unroll
+        for (int i = 0; i < 4; ++i) a[i] = (k0 + i < S) ? (int)sy[k0 + i] : 0;
+      }
+      uint64_t inc[4], run = 0;
+      float wv[4];
+      if (one_h) {
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+          wv[i] = (float)a[i] * p.hw[0];
+          run += (uint64_t)((int64_t)a[i]) * p.hfix[0];
+          inc[i] = run;
+        }
+      } else {
+        int hi = k0 % p.n_h;
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+          wv[i] = (float)a[i] * p.hw[hi];
+          run += (uint64_t)((int64_t)a[i]) * p.hfix[hi];
+          inc[i] = run;
+          if (++hi == p.n_h) hi = 0;
+        }
+      }
+      uint64_t incl = run;
+#pragma unroll
+      for (int s = 1; s < 32; s <<= 1) {
+        const uint64_t t = __shfl_up_sync(0xFFFFFFFFu, incl, s);
+        if (lane >= s) incl += t;
+      }
+      if (lane == 31) warp_tot[wid] = incl;
+      __syncthreads();  // also: every warp has left phase (b) of the previous chunk
+      uint64_t base = carry + (incl - run), total = 0;
+#pragma unroll
+      for (int i = 0; i < kModThreads / 32; ++i) {
+        const uint64_t t = warp_tot[i];
+        if (i < wid) base += t;
+        total += t;
+      }
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        const int slot = (k0 + i) & (kFRing - 1);
+        w_s[slot] = wv[i];
+        if (slot < kFMirror) w_s[slot + kFRing] = wv[i];
+        const int fslot = (k0 + i + 1) & (kFRing - 1);
+        const uint32_t fv = (uint32_t)((base + inc[i]) >> 32);  // F[k+1]
+        f_s[fslot] = fv;
+        if (fslot < kFMirror) f_s[fslot + kFRing] = fv;
+      }
+      carry += total;
+      scanned += 4 * kModThreads;
+      __syncthreads();
+    }
+
+    // ---- (b) kFRun consecutive intervals per thread ----------------------------------
+    const int A0 = A_first + cs + grp * kFRun;
+    const int s0 = (A0 - JT) & (kFRing - 1);
+    const float* wp = w_s + s0;        // symbols A0-JT .. A0+kFRun-2
+    const uint32_t* fp = f_s + s0;     // F[A0-JT .. ]
+    float w[JT + kFRun - 1];
+#pragma unroll
+    for (int j = 0; j < JT + kFRun - 1; ++j) w[j] = wp[j];
+    const int n0 = 8 * A0 + rho - off;  // first sample of this thread's first pair (may be < 0 in chunk 0)
+    float4* o = out + (n0 >> 1);
+#pragma unroll
+    for (int i = 0; i < kFRun; ++i) {
+      float acc0 = 0.f, acc1 = 0.f;
+#pragma unroll
+      for (int j = 0; j < JT; ++j) {
+        const float wj = w[i + JT - 1 - j];  // symbol A-1-j
+        acc0 = fmaf(wj, qa[j], acc0);
+        acc1 = fmaf(wj, qb[j], acc1);
+      }
+      const float old = (float)(int32_t)fp[i] * 1.4629180792671596e-09f;  // F[A-JT] in radians, [-pi, pi)
+      float c0, s0f, c1, s1f;
+      __sincosf(acc0 + old, &s0f, &c0);
+      __sincosf(acc1 + old, &s1f, &c1);
+      if (NOISE) {
+        u32x4 ctr;
+        ctr.x = (uint32_t)((n0 >> 1) + 4 * i); ctr.y = fr_lo; ctr.z = fr_hi; ctr.w = pt;
+        const u32x4 r = philox4x32_10_rk(ctr, p.rk);
+        const float2 g0 = box_muller(r.x, r.y, ncoef), g1 = box_muller(r.z, r.w, ncoef);
+        c0 += g0.x; s0f += g0.y; c1 += g1.x; s1f += g1.y;
+      }
+      if ((unsigned)(n0 + 8 * i) < (unsigned)Ti) o[4 * i] = make_float4(c0, s0f, c1, s1f);
+    }
+  }
+}
+
+// ---------------------------------------------------------------------------
 // Stand-alone AWGN: in-place add / fill.  One thread per sample pair, grid-stride.
 // ---------------------------------------------------------------------------
 template <typename T, bool ADD>
@@ -243,22 +419,22 @@ awgn_kernel(T* __restrict__ sig, int64_t B, int64_t Tn, int64_t ld, const float*
     const int64_t b = i / pairs_per_frame;
     const int64_t pr = i - b * pairs_per_frame;
     const int64_t n = pr << 1;
-    const float sg = sigma ? sigma[b] : 1.0f;
+    const float nc = noise_coef(sigma ? sigma[b] : 1.0f);
     const uint32_t pt = point ? (uint32_t)point[b] : 0u;
     u32x4 r = philox4x32_10(noise_counter((uint64_t)pr, first_frame + (uint64_t)b, pt), (uint32_t)seed, (uint32_t)(seed >> 32));
-    float2 g0 = box_muller(r.x, r.y), g1 = box_muller(r.z, r.w);
+    float2 g0 = box_muller(r.x, r.y, nc), g1 = box_muller(r.z, r.w, nc);
     T* row = sig + 2 * (b * ld + n);
     if (vec_ok && n + 1 < Tn && sizeof(T) == 4) {
       float4* q = reinterpret_cast<float4*>(row);
       float4 v = ADD ? *q : make_float4(0.f, 0.f, 0.f, 0.f);
-      v.x += sg * g0.x; v.y += sg * g0.y; v.z += sg * g1.x; v.w += sg * g1.y;
+      v.x += g0.x; v.y += g0.y; v.z += g1.x; v.w += g1.y;
       *q = v;
     } else {
-      row[0] = (ADD ? row[0] : (T)0) + (T)(sg * g0.x);
-      row[1] = (ADD ? row[1] : (T)0) + (T)(sg * g0.y);
+      row[0] = (ADD ? row[0] : (T)0) + (T)g0.x;
+      row[1] = (ADD ? row[1] : (T)0) + (T)g0.y;
       if (n + 1 < Tn) {
-        row[2] = (ADD ? row[2] : (T)0) + (T)(sg * g1.x);
-        row[3] = (ADD ? row[3] : (T)0) + (T)(sg * g1.y);
+        row[2] = (ADD ? row[2] : (T)0) + (T)g1.x;
+        row[3] = (ADD ? row[3] : (T)0) + (T)g1.y;
       }
     }
   }
@@ -338,7 +514,7 @@ static int launch_modulate(const int8_t* d_syms, int64_t B, int64_t S, const dou
   memset(&p, 0, sizeof(p));
   p.syms = d_syms; p.out = d_out; p.sigma = d_sigma; p.point = d_point;
   p.B = B; p.S = S; p.Tn = (S + 1) * sps; p.ld_out = ld_out;
-  p.seed = seed; p.first_frame = first_frame;
+  p.seed = seed; p.first_frame = first_frame; p.rk = philox_round_keys(seed);
   p.n_h = n_h; p.K = K; p.sps = sps; p.off = (K - 1) / 2;
   p.J = (K - 1 + sps - 1) / sps;
   if (p.J < 1) p.J = 1;
@@ -370,6 +546,23 @@ static int launch_modulate(const int8_t* d_syms, int64_t B, int64_t S, const dou
     if (noise) cpm_modulate_kernel<T, SPS_, JT_, true><<<grid, block, 0, stream>>>(p);     \
     else cpm_modulate_kernel<T, SPS_, JT_, false><<<grid, block, 0, stream>>>(p);          \
   } while (0)
+  if (sizeof(T) == 4 && fast8 && (p.J == 8 || p.J == 3 || p.J == 1) && (ld_out & 1) == 0 &&
+      (reinterpret_cast<uintptr_t>(d_out) & 15) == 0) {
+    const ModParams<float>& pf = reinterpret_cast<const ModParams<float>&>(p);  // T == float on this branch
+#define WF_MODF_LAUNCH(JT_, RUN_, MINB_)                                                                  \
+  do {                                                                                                   \
+    if (noise) cpm_modulate_f32s8_kernel<JT_, true, RUN_, MINB_><<<grid, block, 0, stream>>>(pf);       \
+    else cpm_modulate_f32s8_kernel<JT_, false, RUN_, MINB_><<<grid, block, 0, stream>>>(pf);            \
+  } while (0)
+    // RUN = 8 intervals per thread at 4 resident blocks/SM (64 registers) measured fastest on B200
+    // among RUN in {4, 8, 16} x blocks/SM in {2..5} (profiles/r1c_kbench_mod_variants.log)
+    if (p.J == 8) WF_MODF_LAUNCH(8, 8, 4);
+    else if (p.J == 3) WF_MODF_LAUNCH(3, 8, 4);
+    else WF_MODF_LAUNCH(1, 8, 4);
+#undef WF_MODF_LAUNCH
+    WF_LAUNCH_CHECK("cpm_modulate_f32s8_kernel");
+    return WF_OK;
+  }
   if (fast8 && p.J == 8) WF_MOD_LAUNCH(8, 8);
   else if (fast8 && p.J == 3) WF_MOD_LAUNCH(8, 3);
   else if (fast8 && p.J == 1) WF_MOD_LAUNCH(8, 1);
