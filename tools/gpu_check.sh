@@ -21,11 +21,11 @@ timeout 900 python bench.py --impl reference --steps 2 --warmup 1 > $OUT/bench_r
 echo "bench ref exit $?"
 
 # ncu: only after the identical command exited 0 without ncu
-NCU_CMD="python bench.py --frames 2048 --steps 2 --warmup 3 --no-cpu-baseline"
+NCU_CMD="python bench.py --frames ${NCU_FRAMES:-32768} --steps 2 --warmup 3 --no-cpu-baseline"
 $NCU_CMD > $OUT/ncu_plain.log 2>&1 &&
 ncu --metrics gpu__time_duration.sum --clock-control none -c 200 --csv --log-file $OUT/launches.csv $NCU_CMD > $OUT/ncu_launches.log 2>&1
 echo "ncu launches exit $?"
 $NCU_CMD > $OUT/ncu_plain2.log 2>&1 &&
-ncu --set full --clock-control none --import-source on -k regex:'cpm_modulate|mf_bank|viterbi|encode_frames' -s 12 -c 4 -o $OUT/prof $NCU_CMD > $OUT/ncu_full.log 2>&1
+timeout 900 ncu --set full --clock-control none --import-source on -k regex:'cpm_modulate|mf_bank|viterbi|encode_frames' -s 12 -c 4 -o $OUT/prof $NCU_CMD > $OUT/ncu_full.log 2>&1
 echo "ncu full exit $?"
 ls -la $OUT

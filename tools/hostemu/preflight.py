@@ -297,6 +297,31 @@ def t_noise():
     ok(L.wf_awgn_add(ptr(buf), 0, 1, T1, T1, ptr(sg), None, 99, 5, None))
     s2 = modulate(sy, [0.25], o.pulse_soqpsk_tg(8), 8, 0, derot=-np.pi / 4, sigma=sg, seed=99, first=5)
     assert np.max(np.abs(buf - s2)) < 1e-6, np.max(np.abs(buf - s2))
+    # same identity on every fused kernel shape: the sps-8 fast path with aligned (TG, off 32) and
+    # late-starting lanes (multi-h off 12, MIL off 4), a multi-segment frame, the generic kernel
+    # (sps 10, float64), with enough pairs that the 2^-15 tail-refinement path is exercised
+    rng = np.random.default_rng(11)
+    cases = [("tg", 4, 4096, [0.25], o.pulse_soqpsk_tg(8), 8, 0, (-2, 0, 2)),
+             ("multih", 4, 2048, [4 / 16, 5 / 16], o.pulse_multih(8), 8, 0, (-3, -1, 1, 3)),
+             ("mil", 4, 3000, [0.25], o.pulse_soqpsk_mil(8), 8, 0, (-2, 0, 2)),
+             ("tg long", 2, 11001, [0.25], o.pulse_soqpsk_tg(8), 8, 0, (-2, 0, 2)),
+             ("tg sps10", 2, 3001, [0.25], o.pulse_soqpsk_tg(10), 10, 0, (-2, 0, 2)),
+             ("tg f64", 2, 3001, [0.25], o.pulse_soqpsk_tg(8), 8, 1, (-2, 0, 2))]
+    for lab, B, S, h, pulse, sps, dtype, alpha in cases:
+        sy = rng.choice(np.array(alpha, np.int8), size=(B, S)).astype(np.int8)
+        sg = np.linspace(0.5, 1.5, B).astype(np.float32)
+        clean = modulate(sy, h, pulse, sps, dtype)
+        Tn = clean.shape[1]
+        buf = np.ascontiguousarray(clean.copy())
+        ok(L.wf_awgn_add(ptr(buf), dtype, B, Tn, Tn, ptr(sg), None, 77, 3, None))
+        fused = modulate(sy, h, pulse, sps, dtype, sigma=sg, seed=77, first=3)
+        err = np.max(np.abs(buf - fused))
+        nz = (buf - clean) / sg[:, None]
+        print(f"  fused vs separate {lab}: max diff {err:.2e}; noise var {nz.real.var():.4f} max |n| {np.abs(nz).max():.2f}")
+        assert err < 2e-6, (lab, err)
+        if dtype == 0 and sps == 8:
+            ref = np.stack([o.cpm_modulate_closed_form(sy[b], h if len(h) > 1 else h[0], pulse, sps) for b in range(B)])
+            assert np.max(np.abs(clean - ref)) < 1e-5, (lab, np.max(np.abs(clean - ref)))
 
 
 def t_stream():

@@ -24,7 +24,8 @@ BYTES = {"prbs_encode": 1.125, "modulate_awgn": 65.0, "mf_bank": 88.0, "viterbi_
 
 def measure(sim, B, reps, cfg):
     dev = sim.device
-    sg = torch.full((B,), (cfg.sps / (2.0 * 10.0 ** 0.6)) ** 0.5  # 6 dB, 1 bit/symbol, dtype=torch.float32, device=dev)
+    sigma = (cfg.sps / (2.0 * 10.0 ** 0.6)) ** 0.5  # 6 dB, 1 bit/symbol
+    sg = torch.full((B,), sigma, dtype=torch.float32, device=dev)
     counters = torch.zeros((1, 3), dtype=torch.int64, device=dev)
     for _ in range(2):
         sim.run_batch(0, sg, None, counters)

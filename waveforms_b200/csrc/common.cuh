@@ -85,14 +85,20 @@ __host__ __device__ __forceinline__ u32x4 philox4x32_10_rk(u32x4 c, const Philox
   return c;
 }
 
-// Counter layout shared by every noise kernel: results depend only on
-// (seed, point, global frame, sample pair) -- never on batching or sharding.
-__host__ __device__ __forceinline__ u32x4 noise_counter(uint64_t pair, uint64_t frame, uint32_t point) {
+// Noise layout shared by every noise kernel: results depend only on
+// (seed, point, global frame, sample) -- never on batching or sharding.
+// One Philox call feeds FOUR complex samples (one 32-bit word each).  Sample pair p
+// (samples 2p, 2p+1) of a frame uses
+//   call(p) = 4 (p >> 3) + (p & 3),   words (x, y) if (p & 4) == 0 else (z, w),
+// i.e. pairs p and p ^ 4 (same offset inside two neighbouring sps-8 symbol intervals)
+// share a call, so a thread that walks consecutive intervals amortises one call over two.
+__host__ __device__ __forceinline__ uint64_t noise_call_of_pair(uint64_t pair) { return ((pair >> 3) << 2) | (pair & 3u); }
+__host__ __device__ __forceinline__ u32x4 noise_counter(uint64_t call, uint64_t frame, uint32_t point) {
   u32x4 c;
-  c.x = (uint32_t)pair;
+  c.x = (uint32_t)call;
   c.y = (uint32_t)frame;
-  c.z = (uint32_t)(frame >> 32) ^ ((uint32_t)(pair >> 32) << 16);
-  c.w = point;
+  c.z = (uint32_t)(frame >> 32) ^ ((uint32_t)(call >> 32) << 16);
+  c.w = point;  // < 2^31; bit 31 marks the tail-refinement call (noise_tail_log2)
   return c;
 }
 
@@ -117,22 +123,73 @@ __device__ __forceinline__ float fast_log2(float x) {  // MUFU.LG2 without the d
 #endif
 }
 
-// Box-Muller on two 32-bit uniforms -> one complex sigma*(N(0,1)+jN(0,1)) sample.
-// `coef` = -2 ln2 sigma^2 (see noise_coef): sigma rides inside the radius, so the caller
-// adds the result to the signal with no further multiply.  Uniforms come from I2FP
-// (ALU pipe, not the XU pipe that already carries LG2/SQRT/SIN/COS):
-//   x = (u1 + 0.5) 2^-32 in (0, 1]   -> radii reach sqrt(2 ln 2^33) = 6.76 sigma,
-//   angle = int32(u2) 2 pi 2^-32 in [-pi, pi].
-__device__ __forceinline__ float noise_coef(float sigma) { return -1.3862943611198906f * sigma * sigma; }
+// Box-Muller on ONE 32-bit word -> one complex sigma*(N(0,1)+jN(0,1)) sample.
+//   low 16 bits m:  x = (m + 0.5) 2^-16 in (0, 1).  m == 0 (probability 2^-16) refines the
+//                   tail with a fresh 32-bit draw t: x = (t + 0.5) 2^-48, so the radius
+//                   distribution is exact down to 2^-48 (8.1 sigma) -- never clipped at 4.7.
+//   high 16 bits a: angle = (a + 0.5) 2 pi 2^-16 - pi, 65536 directions symmetric about 0.
+// sigma rides inside the radius: r = sqrt(coef (log2(m + 0.5) - 16)), coef = -2 ln2 sigma^2, so
+// the caller adds the result to the signal with no further multiply.  Both 16-bit fields become
+// floats by OR-ing them under the exponent of 2^23 (one LOP3 / PRMT) and an FADD / FFMA on the
+// FMA pipe: no I2F on the XU pipe, which already carries LG2 / SQRT / SIN / COS.
+struct NoiseCoef { float coef, c16; };
+__device__ __forceinline__ NoiseCoef noise_coef(float sigma) {
+  NoiseCoef nc;
+  nc.coef = -1.3862943611198906f * sigma * sigma;
+  nc.c16 = -16.0f * nc.coef;
+  return nc;
+}
 
-__device__ __forceinline__ float2 box_muller(uint32_t u1, uint32_t u2, float coef) {
-  const float x = fmaf((float)u1, 2.3283064365386963e-10f, 1.1641532182693481e-10f);
-  const float r = fast_sqrt(coef * fast_log2(x));  // sigma sqrt(-2 ln x)
-  const float ang = (float)(int32_t)u2 * 1.4629180792671596e-09f;  // 2 pi 2^-32
+// log2(t + 0.5) - 32 of the refined 32-bit uniform t for word `word` of the call whose counter is c (rare path)
+static __device__ __noinline__ float noise_tail_lgt(uint32_t cx, uint32_t cy, uint32_t cz, uint32_t cw, uint32_t k0, uint32_t k1,
+                                                    int word) {
+  u32x4 c;
+  c.x = cx; c.y = cy; c.z = cz; c.w = cw | 0x80000000u;
+  const u32x4 r = philox4x32_10(c, k0, k1);
+  const uint32_t t = word == 0 ? r.x : (word == 1 ? r.y : (word == 2 ? r.z : r.w));
+  return fast_log2((float)t + 0.5f) - 32.0f;
+}
+
+// log2(m + 0.5) of the low 16 bits
+__device__ __forceinline__ float noise_lgt(uint32_t w) {
+  return fast_log2(__uint_as_float((w & 0xFFFFu) | 0x4B000000u) - 8388607.5f);
+}
+// lgt = log2 of the radius uniform + 16 (noise_lgt, or the tail refinement)
+__device__ __forceinline__ float2 box_muller16(uint32_t w, float lgt, NoiseCoef nc) {
+  const float r = fast_sqrt(fmaf(lgt, nc.coef, nc.c16));  // sigma sqrt(-2 ln x)
+  // (2^23 + a) * 2pi/65536 - (2^23 + 32767.5) * 2pi/65536
+  const float ang = fmaf(__uint_as_float((w >> 16) | 0x4B000000u), 9.58738019107841e-05f, -807.3892822265625f);
   float s, c;
   __sincosf(ang, &s, &c);
   return make_float2(r * c, r * s);
 }
+// the two complex samples of a pair: words (wa, wb) = words (2 half, 2 half + 1) of call counter c
+__device__ __forceinline__ void noise_pair(uint32_t wa, uint32_t wb, int half, const u32x4& c, uint32_t k0, uint32_t k1,
+                                           NoiseCoef nc, float2& g0, float2& g1) {
+  float la = noise_lgt(wa), lb = noise_lgt(wb);
+  if (((wa & 0xFFFFu) == 0u) | ((wb & 0xFFFFu) == 0u)) {  // p = 2^-15 per pair
+    if ((wa & 0xFFFFu) == 0u) la = noise_tail_lgt(c.x, c.y, c.z, c.w, k0, k1, 2 * half);
+    if ((wb & 0xFFFFu) == 0u) lb = noise_tail_lgt(c.x, c.y, c.z, c.w, k0, k1, 2 * half + 1);
+  }
+  g0 = box_muller16(wa, la, nc);
+  g1 = box_muller16(wb, lb, nc);
+}
+// packed FP32 FMA (Blackwell FFMA2): one issue slot for two independent fused multiply-adds
+__device__ __forceinline__ float2 ffma2(float2 a, float2 b, float2 c) {
+#ifdef WF_HOSTEMU
+  return make_float2(fmaf(a.x, b.x, c.x), fmaf(a.y, b.y, c.y));
+#else
+  unsigned long long ra, rb, rc, rd;
+  asm("mov.b64 %0, {%1, %2};" : "=l"(ra) : "f"(a.x), "f"(a.y));
+  asm("mov.b64 %0, {%1, %2};" : "=l"(rb) : "f"(b.x), "f"(b.y));
+  asm("mov.b64 %0, {%1, %2};" : "=l"(rc) : "f"(c.x), "f"(c.y));
+  asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(rd) : "l"(ra), "l"(rb), "l"(rc));
+  float2 d;
+  asm("mov.b64 {%0, %1}, %2;" : "=f"(d.x), "=f"(d.y) : "l"(rd));
+  return d;
+#endif
+}
+
 // ---- cp.async helpers (LDGSTS): global -> shared without a register round trip ----
 template <int BYTES>
 __device__ __forceinline__ void cp_async(void* smem_dst, const void* gmem_src) {

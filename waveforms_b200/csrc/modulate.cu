@@ -15,6 +15,10 @@
 #include <math.h>
 #include <string.h>
 
+#ifndef WF_MOD_FFMA2
+#define WF_MOD_FFMA2 1
+#endif
+
 namespace wf {
 
 constexpr int kModThreads = 256;
@@ -100,7 +104,7 @@ cpm_modulate_kernel(const __grid_constant__ ModParams<T> p) {
     c0_s = c0;
   }
 
-  float ncoef = 0.f;
+  NoiseCoef ncoef = noise_coef(0.f);
   uint32_t pt = 0;
   uint64_t gframe = 0;
   if (NOISE) {
@@ -206,8 +210,13 @@ cpm_modulate_kernel(const __grid_constant__ ModParams<T> p) {
       Tr::unit(ph[0], c[0], s[0]);
       Tr::unit(ph[1], c[1], s[1]);
       if (NOISE) {
-        u32x4 r = philox4x32_10(noise_counter((uint64_t)(uint32_t)(n >> 1), gframe, pt), (uint32_t)p.seed, (uint32_t)(p.seed >> 32));
-        float2 g0 = box_muller(r.x, r.y, ncoef), g1 = box_muller(r.z, r.w, ncoef);
+        const uint32_t pr = (uint32_t)(n >> 1);
+        const int half = (int)((pr >> 2) & 1u);
+        const u32x4 ctr = noise_counter(noise_call_of_pair(pr), gframe, pt);
+        const uint32_t k0 = (uint32_t)p.seed, k1 = (uint32_t)(p.seed >> 32);
+        const u32x4 r = philox4x32_10(ctr, k0, k1);
+        float2 g0, g1;
+        noise_pair(half ? r.z : r.x, half ? r.w : r.y, half, ctr, k0, k1, ncoef, g0, g1);
         c[0] += (T)g0.x; s[0] += (T)g0.y;
         c[1] += (T)g1.x; s[1] += (T)g1.y;
       }
@@ -231,31 +240,62 @@ cpm_modulate_kernel(const __grid_constant__ ModParams<T> p) {
 }
 
 // ---------------------------------------------------------------------------
-// complex64 fast path for sps = 8 (every SOQPSK / PCM-FM benchmark shape).
-// Same maths as above; what differs is the sample -> thread map.  Four lanes own
-// the four sample PAIRS of one symbol interval and walk kRun consecutive intervals,
-// so the J-symbol window slides through registers (one LDS per new symbol instead
-// of J), every ring / output address is base + immediate, the thread's Q
-// coefficients (pre-scaled to radians) stay in registers, and a warp store covers
-// eight 64-byte runs of full 32-byte sectors.  The frame-start constant and the
-// initial phase ride inside the fixed-point prefix sum, so the phase needs no
-// separate range reduction: angle = fixed(F) * 2pi/2^32 in [-pi, pi) plus the
-// J-tap partial.  Issue-slot budget per sample pair (the binding resource; see
-// DESIGN 4.2): 2J FFMA + ~12 for the signal, ~70 for Philox + Box-Muller, 12 MUFU.
+// complex64 fast path for sps = 8 and an even "same"-mode offset (SOQPSK-TG/A/B/MIL, multi-h).
+// Same maths as above; what differs is the schedule.
+//  * The block first turns a whole SEGMENT of the frame (kFSeg symbol intervals: the whole
+//    frame when S <= ~5100) into w_k (float) and the fixed-point prefix sum F (top 32 bits)
+//    in shared memory -- five scan steps back to back -- and then produces the samples with
+//    NO further barrier, so the eight warps of a block drift freely through the long
+//    MUFU/Philox part instead of meeting at a barrier every 1024 symbols.
+//  * Four lanes own the four sample PAIRS of one symbol interval and walk RUN consecutive
+//    intervals: the J-symbol window slides through registers (one LDS per new symbol), every
+//    shared / global address is base + immediate, the thread's 2J Q coefficients (pre-scaled
+//    to radians) stay in registers, and a warp store covers eight 64-byte runs of full sectors.
+//  * One Philox call feeds the same pair offset of TWO neighbouring intervals (common.cuh),
+//    i.e. two loop iterations of a thread.  Lanes whose pair index would start on the odd
+//    half of a call begin one interval later (`e`), so every thread's calls are whole.
+//  * The frame-start constant and the initial phase ride inside the prefix sum, so the angle
+//    is fixed(F) * 2pi/2^32 in [-pi, pi) plus the J-tap partial: no range reduction.
 // ---------------------------------------------------------------------------
-constexpr int kFMirror = 32;    // slots [ring, ring+32) mirror [0, 32): windows of <= 33 never wrap
+constexpr int kFSeg = 5120;                   // symbol intervals per segment (multiple of 1024)
+constexpr int kFLB = 16;                      // look-back slots in front of a segment (>= J + 2)
+constexpr int kFSlots = kFLB + kFSeg + 8;     // + spill of the lanes that start one interval late
+constexpr size_t kFSmemBytes = (size_t)kFSlots * 8;
 
-// RUN consecutive intervals per thread -> 64*RUN intervals per block pass; a scan step adds
-// 4*threads = 1024 symbols, so the ring must hold pass + 1023 + J symbols.
+// Rare path (p = 2^-15 per pair): one pair again, this time with the tail refinement of the
+// radius uniform.  Kept out of line so the unrolled main loop stays branch free.
+// wwin = w_s + slot(A - JT) (symbols A-JT .. A-1), f_old = F[A - JT].
+template <int JT>
+static __device__ __noinline__ float4 mod_f32s8_slow_pair(const ModParams<float>& p, const float* wwin, uint32_t f_old, int rho,
+                                                          u32x4 ctr, int half, NoiseCoef ncoef) {
+  float acc0 = 0.f, acc1 = 0.f;
+#pragma unroll
+  for (int j = 0; j < JT; ++j) {
+    const float wj = wwin[JT - 1 - j];
+    acc0 = fmaf(wj, p.q[rho + 1 + 8 * j] * 0.78539816339744831f, acc0);
+    acc1 = fmaf(wj, p.q[rho + 2 + 8 * j] * 0.78539816339744831f, acc1);
+  }
+  const float old = (float)(int32_t)f_old * 1.4629180792671596e-09f;
+  float c0f, s0f, c1f, s1f;
+  __sincosf(acc0 + old, &s0f, &c0f);
+  __sincosf(acc1 + old, &s1f, &c1f);
+  const uint32_t k0 = (uint32_t)p.seed, k1 = (uint32_t)(p.seed >> 32);
+  const u32x4 r = philox4x32_10(ctr, k0, k1);
+  float2 g0, g1;
+  noise_pair(half ? r.z : r.x, half ? r.w : r.y, half, ctr, k0, k1, ncoef, g0, g1);
+  return make_float4(c0f + g0.x, s0f + g0.y, c1f + g1.x, s1f + g1.y);
+}
+
 template <int JT, bool NOISE, int RUN, int MINB>
 __global__ void __launch_bounds__(kModThreads, MINB)
 cpm_modulate_f32s8_kernel(const __grid_constant__ ModParams<float> p) {
-  constexpr int kFRun = RUN;
   constexpr int kFChunk = RUN * (kModThreads / 4);
-  constexpr int kFRing = (kFChunk + 1024 + 64 <= 2048) ? 2048 : 4096;
-  static_assert(JT + kFRun - 1 <= kFMirror + 1, "window longer than the mirrored tail");
-  __shared__ float w_s[kFRing + kFMirror];
-  __shared__ uint32_t f_s[kFRing + kFMirror];
+  constexpr int kScanStep = 4 * kModThreads;
+  static_assert(kFSeg % kFChunk == 0 && kFSeg % kScanStep == 0, "segment = whole chunks and whole scan steps");
+  static_assert(JT + 2 <= kFLB && (RUN % 2) == 0, "look-back too short / odd run");
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  float* w_s = reinterpret_cast<float*>(smem_raw);          // slot(k) = k - k_lo + kFLB holds w_k
+  uint32_t* f_s = reinterpret_cast<uint32_t*>(w_s + kFSlots);  // slot(k) holds F[k + 1]
   __shared__ uint64_t warp_tot[kModThreads / 32];
   __shared__ uint64_t base_s;
 
@@ -282,37 +322,45 @@ cpm_modulate_f32s8_kernel(const __grid_constant__ ModParams<float> p) {
   }
   __syncthreads();
   uint64_t carry = base_s;  // F[scanned] (+ the constant)
-  for (int i = tid; i < kFRing + kFMirror; i += kModThreads) { w_s[i] = 0.f; f_s[i] = (uint32_t)(carry >> 32); }
+  if (tid < kFLB) { w_s[tid] = 0.f; f_s[tid] = (uint32_t)(carry >> 32); }  // symbols k < 0, F[k <= 0]
 
-  float ncoef = 0.f;
-  uint32_t pt = 0, fr_lo = 0, fr_hi = 0;
+  NoiseCoef ncoef = noise_coef(0.f);
+  u32x4 ctr;
+  ctr.x = 0; ctr.y = 0; ctr.z = 0; ctr.w = 0;
   if (NOISE) {
     ncoef = noise_coef(p.sigma[frame]);
-    pt = p.point ? (uint32_t)p.point[frame] : 0u;
     const uint64_t gframe = p.first_frame + (uint64_t)frame;
-    fr_lo = (uint32_t)gframe; fr_hi = (uint32_t)(gframe >> 32);
+    ctr.y = (uint32_t)gframe; ctr.z = (uint32_t)(gframe >> 32);
+    ctr.w = p.point ? (uint32_t)p.point[frame] : 0u;
   }
 
-  // a = n + off = 8 A + rho: this thread owns rho = 2 sub, 2 sub + 1 of kFRun consecutive A
+  // a = n + off = 8 A + rho: this thread owns rho = 2 sub, 2 sub + 1 of RUN consecutive A.
+  // Its pair index at interval A is 4 A + sub - off/2; e makes (pair >> 2) even at the first
+  // interval of every run, so iterations (2m, 2m+1) share Philox call c0 + 4m.
   const int sub = tid & 3, grp = tid >> 2;
   const int rho = 2 * sub;
+  const int e = ((sub - (off >> 1)) >> 2) & 1;
   float qa[JT], qb[JT];
 #pragma unroll
   for (int j = 0; j < JT; ++j) {
     qa[j] = p.q[rho + 1 + 8 * j] * 0.78539816339744831f;  // Q * 2 pi / sps  (radians per unit w)
     qb[j] = p.q[rho + 2 + 8 * j] * 0.78539816339744831f;
   }
-  const int A_first = off >> 3;
   const int A_last = (Ti - 1 + off) >> 3;
-  int scanned = 0;
   const bool one_h = (p.n_h == 1);
-  __syncthreads();
 
-  for (int cs = 0; A_first + cs <= A_last; cs += kFChunk) {
-    // ---- (a) extend the scan so symbols < A_first + cs + chunk are in the ring ----------
-    const int want = cs + kFChunk + A_first;
-    while (scanned < want) {  // uniform across the block; each step adds 4 * threads = chunk symbols
-      const int k0 = scanned + 4 * tid;
+  for (int k_lo = 0; k_lo <= A_last; k_lo += kFSeg) {
+    if (k_lo > 0) {  // carry the newest kFLB slots of the previous segment to the front
+      __syncthreads();
+      float wv = 0.f; uint32_t fv = 0;
+      if (tid < kFLB) { wv = w_s[kFSeg + tid]; fv = f_s[kFSeg + tid]; }
+      __syncthreads();
+      if (tid < kFLB) { w_s[tid] = wv; f_s[tid] = fv; }
+    }
+    // ---- (a) scan the segment's symbols: w_k and F[k+1] for k in [k_lo, k_lo + kFSeg) ------
+    int sc = 0;
+    for (; sc < kFSeg && k_lo + sc < S; sc += kScanStep) {
+      const int k0 = k_lo + sc + 4 * tid;
       int a[4];
       if (sym_vec && k0 + 3 < S) {
         const uint32_t v = *reinterpret_cast<const uint32_t*>(sy + k0);
@@ -347,7 +395,7 @@ cpm_modulate_f32s8_kernel(const __grid_constant__ ModParams<float> p) {
         if (lane >= s) incl += t;
       }
       if (lane == 31) warp_tot[wid] = incl;
-      __syncthreads();  // also: every warp has left phase (b) of the previous chunk
+      __syncthreads();
       uint64_t base = carry + (incl - run), total = 0;
 #pragma unroll
       for (int i = 0; i < kModThreads / 32; ++i) {
@@ -355,91 +403,130 @@ cpm_modulate_f32s8_kernel(const __grid_constant__ ModParams<float> p) {
         if (i < wid) base += t;
         total += t;
       }
-#pragma unroll
-      for (int i = 0; i < 4; ++i) {
-        const int slot = (k0 + i) & (kFRing - 1);
-        w_s[slot] = wv[i];
-        if (slot < kFMirror) w_s[slot + kFRing] = wv[i];
-        const int fslot = (k0 + i + 1) & (kFRing - 1);
-        const uint32_t fv = (uint32_t)((base + inc[i]) >> 32);  // F[k+1]
-        f_s[fslot] = fv;
-        if (fslot < kFMirror) f_s[fslot + kFRing] = fv;
-      }
+      const int slot = kFLB + sc + 4 * tid;  // 16-byte aligned: one 128-bit store per array
+      *reinterpret_cast<float4*>(w_s + slot) = make_float4(wv[0], wv[1], wv[2], wv[3]);
+      *reinterpret_cast<uint4*>(f_s + slot) = make_uint4((uint32_t)((base + inc[0]) >> 32), (uint32_t)((base + inc[1]) >> 32),
+                                                         (uint32_t)((base + inc[2]) >> 32), (uint32_t)((base + inc[3]) >> 32));
       carry += total;
-      scanned += 4 * kModThreads;
-      __syncthreads();
+      __syncthreads();  // warp_tot is reused by the next step; the last one publishes the ring
     }
+    // the intervals just past the last symbol (A <= S + off/8) read w = 0, F = F[S] up to kFLB slots
+    // beyond the scanned range (only when S ends exactly on a scan step; otherwise the step zero-filled them)
+    if (sc < kFSeg && tid < kFLB) { w_s[kFLB + sc + tid] = 0.f; f_s[kFLB + sc + tid] = (uint32_t)(carry >> 32); }
+    __syncthreads();
 
-    // ---- (b) kFRun consecutive intervals per thread ----------------------------------
-    const int A0 = A_first + cs + grp * kFRun;
-    const int s0 = (A0 - JT) & (kFRing - 1);
-    const float* wp = w_s + s0;        // symbols A0-JT .. A0+kFRun-2
-    const uint32_t* fp = f_s + s0;     // F[A0-JT .. ]
-    float w[JT + kFRun - 1];
+    // ---- (b) RUN consecutive intervals per thread, barrier free ---------------------------
+    for (int cs = 0; cs < kFSeg && k_lo + cs <= A_last; cs += kFChunk) {
+      const int r0 = cs + grp * RUN + e;             // first interval of this run, relative to k_lo
+      if (k_lo + r0 > A_last) break;                 // this run (and every later one of the thread) is past the frame
+      const float* wp = w_s + (r0 - JT + kFLB);      // symbols A0-JT .. A0+RUN-2
+      const uint32_t* fp = f_s + (r0 - JT - 1 + kFLB);  // F[A0-JT ..]
+      float w[JT + RUN - 1];
 #pragma unroll
-    for (int j = 0; j < JT + kFRun - 1; ++j) w[j] = wp[j];
-    const int n0 = 8 * A0 + rho - off;  // first sample of this thread's first pair (may be < 0 in chunk 0)
-    float4* o = out + (n0 >> 1);
+      for (int j = 0; j < JT + RUN - 1; ++j) w[j] = wp[j];
+      const int n0 = 8 * (k_lo + r0) + rho - off;    // first sample of the first pair (< 0 before the frame starts)
+      float4* o = out + (n0 >> 1);
+#ifndef WF_HOSTEMU
+      asm volatile("" : "+l"(o));  // keep the row pointer live: every store is then pointer + immediate
+#endif
+      const int P0 = n0 >> 1;                         // pair index; (P0 >> 2) is even by construction
+      const uint32_t c0 = (uint32_t)(((P0 >> 3) << 2) | (P0 & 3));
+      u32x4 r;
+      r.x = r.y = r.z = r.w = 0;
+      uint32_t m_min = 0xFFFFu;
 #pragma unroll
-    for (int i = 0; i < kFRun; ++i) {
-      float acc0 = 0.f, acc1 = 0.f;
+      for (int i = 0; i < RUN; ++i) {
+        float acc0 = 0.f, acc1 = 0.f;
+#if WF_MOD_FFMA2
+        float2 acc = make_float2(0.f, 0.f);
 #pragma unroll
-      for (int j = 0; j < JT; ++j) {
-        const float wj = w[i + JT - 1 - j];  // symbol A-1-j
-        acc0 = fmaf(wj, qa[j], acc0);
-        acc1 = fmaf(wj, qb[j], acc1);
+        for (int j = 0; j < JT; ++j) {
+          const float wj = w[i + JT - 1 - j];  // symbol A-1-j
+          acc = ffma2(make_float2(wj, wj), make_float2(qa[j], qb[j]), acc);
+        }
+        acc0 = acc.x; acc1 = acc.y;
+#else
+#pragma unroll
+        for (int j = 0; j < JT; ++j) {
+          const float wj = w[i + JT - 1 - j];  // symbol A-1-j
+          acc0 = fmaf(wj, qa[j], acc0);
+          acc1 = fmaf(wj, qb[j], acc1);
+        }
+#endif
+        const float old = (float)(int32_t)fp[i] * 1.4629180792671596e-09f;  // F[A-JT] in radians, [-pi, pi)
+        float c0f, s0f, c1f, s1f;
+        __sincosf(acc0 + old, &s0f, &c0f);
+        __sincosf(acc1 + old, &s1f, &c1f);
+        if (NOISE) {
+          if ((i & 1) == 0) {
+            ctr.x = c0 + 2u * (uint32_t)i;
+            r = philox4x32_10_rk(ctr, p.rk);
+          }
+          const uint32_t wa = (i & 1) ? r.z : r.x, wb = (i & 1) ? r.w : r.y;
+          m_min = min(m_min, min(wa & 0xFFFFu, wb & 0xFFFFu));
+          const float2 g0 = box_muller16(wa, noise_lgt(wa), ncoef), g1 = box_muller16(wb, noise_lgt(wb), ncoef);
+          c0f += g0.x; s0f += g0.y; c1f += g1.x; s1f += g1.y;
+        }
+        if ((unsigned)(n0 + 8 * i) < (unsigned)Ti) o[4 * i] = make_float4(c0f, s0f, c1f, s1f);
       }
-      const float old = (float)(int32_t)fp[i] * 1.4629180792671596e-09f;  // F[A-JT] in radians, [-pi, pi)
-      float c0, s0f, c1, s1f;
-      __sincosf(acc0 + old, &s0f, &c0);
-      __sincosf(acc1 + old, &s1f, &c1);
-      if (NOISE) {
-        u32x4 ctr;
-        ctr.x = (uint32_t)((n0 >> 1) + 4 * i); ctr.y = fr_lo; ctr.z = fr_hi; ctr.w = pt;
-        const u32x4 r = philox4x32_10_rk(ctr, p.rk);
-        const float2 g0 = box_muller(r.x, r.y, ncoef), g1 = box_muller(r.z, r.w, ncoef);
-        c0 += g0.x; s0f += g0.y; c1 += g1.x; s1f += g1.y;
+      if (NOISE && m_min == 0u) {  // some radius uniform of this run needs its tail refined: redo those pairs
+#pragma unroll 1
+        for (int i = 0; i < RUN; ++i) {
+          ctr.x = c0 + 4u * (uint32_t)(i >> 1);
+          const u32x4 rr = philox4x32_10_rk(ctr, p.rk);
+          const uint32_t wa = (i & 1) ? rr.z : rr.x, wb = (i & 1) ? rr.w : rr.y;
+          if (((wa & 0xFFFFu) == 0u || (wb & 0xFFFFu) == 0u) && (unsigned)(n0 + 8 * i) < (unsigned)Ti)
+            o[4 * i] = mod_f32s8_slow_pair<JT>(p, wp + i, fp[i], rho, ctr, i & 1, ncoef);
+        }
       }
-      if ((unsigned)(n0 + 8 * i) < (unsigned)Ti) o[4 * i] = make_float4(c0, s0f, c1, s1f);
     }
   }
 }
 
 // ---------------------------------------------------------------------------
-// Stand-alone AWGN: in-place add / fill.  One thread per sample pair, grid-stride.
+// Stand-alone AWGN: in-place add / fill.  One thread per Philox call (= the two sample
+// pairs p, p + 4 that share it, see common.cuh), grid-stride.
 // ---------------------------------------------------------------------------
 template <typename T, bool ADD>
 __global__ void __launch_bounds__(256)
 awgn_kernel(T* __restrict__ sig, int64_t B, int64_t Tn, int64_t ld, const float* __restrict__ sigma,
             const int32_t* __restrict__ point, uint64_t seed, uint64_t first_frame) {
   const int64_t pairs_per_frame = (Tn + 1) >> 1;
-  const int64_t total = B * pairs_per_frame;
+  const int64_t calls_per_frame = ((pairs_per_frame + 7) >> 3) << 2;
+  const int64_t total = B * calls_per_frame;
   const bool vec_ok = ((ld & 1) == 0) && ((reinterpret_cast<uintptr_t>(sig) & (4 * sizeof(T) - 1)) == 0);
+  const uint32_t k0 = (uint32_t)seed, k1 = (uint32_t)(seed >> 32);
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
-    const int64_t b = i / pairs_per_frame;
-    const int64_t pr = i - b * pairs_per_frame;
-    const int64_t n = pr << 1;
-    const float nc = noise_coef(sigma ? sigma[b] : 1.0f);
+    const int64_t b = i / calls_per_frame;
+    const int64_t call = i - b * calls_per_frame;
+    const NoiseCoef nc = noise_coef(sigma ? sigma[b] : 1.0f);
     const uint32_t pt = point ? (uint32_t)point[b] : 0u;
-    u32x4 r = philox4x32_10(noise_counter((uint64_t)pr, first_frame + (uint64_t)b, pt), (uint32_t)seed, (uint32_t)(seed >> 32));
-    float2 g0 = box_muller(r.x, r.y, nc), g1 = box_muller(r.z, r.w, nc);
-    T* row = sig + 2 * (b * ld + n);
-    if (vec_ok && n + 1 < Tn && sizeof(T) == 4) {
-      float4* q = reinterpret_cast<float4*>(row);
-      float4 v = ADD ? *q : make_float4(0.f, 0.f, 0.f, 0.f);
-      v.x += g0.x; v.y += g0.y; v.z += g1.x; v.w += g1.y;
-      *q = v;
-    } else {
-      row[0] = (ADD ? row[0] : (T)0) + (T)g0.x;
-      row[1] = (ADD ? row[1] : (T)0) + (T)g0.y;
-      if (n + 1 < Tn) {
-        row[2] = (ADD ? row[2] : (T)0) + (T)g1.x;
-        row[3] = (ADD ? row[3] : (T)0) + (T)g1.y;
+    const u32x4 ctr = noise_counter((uint64_t)call, first_frame + (uint64_t)b, pt);
+    const u32x4 r = philox4x32_10(ctr, k0, k1);
+#pragma unroll
+    for (int half = 0; half < 2; ++half) {
+      const int64_t pr = ((call >> 2) << 3) + (call & 3) + 4 * half;
+      if (pr >= pairs_per_frame) continue;
+      const int64_t n = pr << 1;
+      float2 g0, g1;
+      noise_pair(half ? r.z : r.x, half ? r.w : r.y, half, ctr, k0, k1, nc, g0, g1);
+      T* row = sig + 2 * (b * ld + n);
+      if (vec_ok && n + 1 < Tn && sizeof(T) == 4) {
+        float4* q = reinterpret_cast<float4*>(row);
+        float4 v = ADD ? *q : make_float4(0.f, 0.f, 0.f, 0.f);
+        v.x += g0.x; v.y += g0.y; v.z += g1.x; v.w += g1.y;
+        *q = v;
+      } else {
+        row[0] = (ADD ? row[0] : (T)0) + (T)g0.x;
+        row[1] = (ADD ? row[1] : (T)0) + (T)g0.y;
+        if (n + 1 < Tn) {
+          row[2] = (ADD ? row[2] : (T)0) + (T)g1.x;
+          row[3] = (ADD ? row[3] : (T)0) + (T)g1.y;
+        }
       }
     }
   }
 }
-
 
 // ---------------------------------------------------------------------------
 // frequency_modulate (cpm/modulate.py:28-54) for arbitrary per-sample frequency
@@ -547,15 +634,15 @@ static int launch_modulate(const int8_t* d_syms, int64_t B, int64_t S, const dou
     else cpm_modulate_kernel<T, SPS_, JT_, false><<<grid, block, 0, stream>>>(p);          \
   } while (0)
   if (sizeof(T) == 4 && fast8 && (p.J == 8 || p.J == 3 || p.J == 1) && (ld_out & 1) == 0 &&
-      (reinterpret_cast<uintptr_t>(d_out) & 15) == 0) {
+      (reinterpret_cast<uintptr_t>(d_out) & 15) == 0 && p.Tn < 0x7FFFF000) {
     const ModParams<float>& pf = reinterpret_cast<const ModParams<float>&>(p);  // T == float on this branch
 #define WF_MODF_LAUNCH(JT_, RUN_, MINB_)                                                                  \
   do {                                                                                                   \
-    if (noise) cpm_modulate_f32s8_kernel<JT_, true, RUN_, MINB_><<<grid, block, 0, stream>>>(pf);       \
-    else cpm_modulate_f32s8_kernel<JT_, false, RUN_, MINB_><<<grid, block, 0, stream>>>(pf);            \
+    if (noise) cpm_modulate_f32s8_kernel<JT_, true, RUN_, MINB_><<<grid, block, kFSmemBytes, stream>>>(pf);  \
+    else cpm_modulate_f32s8_kernel<JT_, false, RUN_, MINB_><<<grid, block, kFSmemBytes, stream>>>(pf);       \
   } while (0)
     // RUN = 8 intervals per thread at 4 resident blocks/SM (64 registers) measured fastest on B200
-    // among RUN in {4, 8, 16} x blocks/SM in {2..5} (profiles/r1c_kbench_mod_variants.log)
+    // among RUN in {4, 8, 16} x blocks/SM in {3, 4, 5} (profiles/r1f_kbench_mod_variants.log)
     if (p.J == 8) WF_MODF_LAUNCH(8, 8, 4);
     else if (p.J == 3) WF_MODF_LAUNCH(3, 8, 4);
     else WF_MODF_LAUNCH(1, 8, 4);
@@ -612,7 +699,7 @@ static int awgn_common(void* d_sig, int dtype, int64_t B, int64_t T, int64_t ld,
   if ((rc = require_device())) return rc;
   if (B == 0 || T == 0) return WF_OK;
   WF_REQUIRE(d_sig, "signal pointer is NULL");
-  const int64_t total = B * ((T + 1) / 2);
+  const int64_t total = B * ((((T + 1) / 2 + 7) / 8) * 4);  // one thread per Philox call
   int64_t blocks = (total + 255) / 256;
   const int64_t cap = (int64_t)sm_count() * 16;
   if (blocks > cap) blocks = cap;
