@@ -300,11 +300,15 @@ mf_bank_f32_kernel(const __grid_constant__ MfParams<float> p) {
   __syncthreads();
 
   // ---- R calls per thread --------------------------------------------------------------
-  float yr[R][NF], yi[R][NF];
+  // y[e][f] = (re, im) of filter f at call e.  Taps arrive DUPLICATED, (t, t) per entry, so one
+  // packed FFMA2 does (re, im) += (x_re, x_im) * (t, t); complex taps add (-x_im, x_re) * (ti, ti).
+  const float2* tap2_re = reinterpret_cast<const float2*>(p.tap_re);
+  const float2* tap2_im = reinterpret_cast<const float2*>(p.tap_im);
+  float2 y[R][NF];
 #pragma unroll
   for (int e = 0; e < R; ++e)
 #pragma unroll
-    for (int f = 0; f < NF; ++f) { yr[e][f] = 0.f; yi[e][f] = 0.f; }
+    for (int f = 0; f < NF; ++f) y[e][f] = make_float2(0.f, 0.f);
 
   const float2* seg = tile + tid * TL::SEG;
 #pragma unroll
@@ -319,7 +323,8 @@ mf_bank_f32_kernel(const __grid_constant__ MfParams<float> p) {
 #pragma unroll
     for (int s = 0; s < 2; ++s) {
       if (v + s < TL::NV) {
-        const float xr = s ? xx.z : xx.x, xi = s ? xx.w : xx.y;
+        const float2 x = s ? make_float2(xx.z, xx.w) : make_float2(xx.x, xx.y);
+        const float2 xj = make_float2(-x.y, x.x);  // j x
 #pragma unroll
         for (int e = 0; e < R; ++e) {
           const int u = v + s - e * SPS;
@@ -327,15 +332,8 @@ mf_bank_f32_kernel(const __grid_constant__ MfParams<float> p) {
             const int tt = NT - 1 - u;
 #pragma unroll
             for (int f = 0; f < NF; ++f) {
-              const float tr = p.tap_re[f * NT + tt];
-              if (CPLX) {
-                const float ti = p.tap_im[f * NT + tt];
-                yr[e][f] = fmaf(xr, tr, yr[e][f]); yr[e][f] = fmaf(-xi, ti, yr[e][f]);
-                yi[e][f] = fmaf(xr, ti, yi[e][f]); yi[e][f] = fmaf(xi, tr, yi[e][f]);
-              } else {
-                yr[e][f] = fmaf(xr, tr, yr[e][f]);
-                yi[e][f] = fmaf(xi, tr, yi[e][f]);
-              }
+              y[e][f] = ffma2(x, tap2_re[f * NT + tt], y[e][f]);
+              if (CPLX) y[e][f] = ffma2(xj, tap2_im[f * NT + tt], y[e][f]);
             }
           }
         }
@@ -354,14 +352,14 @@ mf_bank_f32_kernel(const __grid_constant__ MfParams<float> p) {
 #pragma unroll
         for (int f = 0; f < NF; ++f) {
           const float cr = p.comb_re[r * NF + f], ci = p.comb_im[r * NF + f];
-          zr = fmaf(cr, yr[e][f], zr); zr = fmaf(-ci, yi[e][f], zr);
-          zi = fmaf(cr, yi[e][f], zi); zi = fmaf(ci, yr[e][f], zi);
+          zr = fmaf(cr, y[e][f].x, zr); zr = fmaf(-ci, y[e][f].y, zr);
+          zi = fmaf(cr, y[e][f].y, zi); zi = fmaf(ci, y[e][f].x, zi);
         }
         tile[s * n_out + r] = make_float2(zr, zi);
       }
     } else {
 #pragma unroll
-      for (int f = 0; f < NF; ++f) tile[s * NF + f] = make_float2(yr[e][f], yi[e][f]);
+      for (int f = 0; f < NF; ++f) tile[s * NF + f] = y[e][f];
     }
   }
   __syncthreads();
@@ -432,6 +430,11 @@ static int launch_mf(const void* d_rx, int64_t B, int64_t Tn, int64_t ld_rx, con
 #define WF_MFT_CASE(SPS_, NF_, NT_, CPLX_, R_)                                                        \
   do {                                                                                                \
     using TL = MfTile<SPS_, NT_, R_>;                                                                 \
+    static_assert(2 * NF_ * NT_ <= kMfMaxTapEntries, "duplicated taps do not fit");                   \
+    for (int i = 0; i < NF_ * NT_; ++i) { /* (t, t) pairs: operands of the packed FFMA2 */            \
+      p.tap_re[2 * i] = p.tap_re[2 * i + 1] = (T)taps_re[i];                                          \
+      p.tap_im[2 * i] = p.tap_im[2 * i + 1] = taps_im ? (T)taps_im[i] : (T)0;                         \
+    }                                                                                                 \
     size_t sm = (size_t)TL::SLOTS * sizeof(float2);                                                   \
     const size_t so = (size_t)TL::SYM * n_out * sizeof(float2);                                       \
     if (so > sm) sm = so;                                                                             \
