@@ -187,13 +187,17 @@ constexpr int kL2Threads = 64;  // two warps; each warp owns its 32 frames and i
 template <typename T, bool DIFF, bool FULL>
 __global__ void __launch_bounds__(kL2Threads)
 viterbi_soqpsk_l2_kernel(const __grid_constant__ VitParams<T> p) {
-  using C = typename std::conditional<sizeof(T) == 4, float2, double2>::type;
+  // Everything is staged and read in 16-byte UNITS (two complex64 or one complex128): a chunk of
+  // CH calls is 12 units per frame for both types, rows sit 13 units apart (odd: the quarter-warp
+  // phases of LDS.128 are conflict free), one cp.async moves 16 bytes (half the LDGSTS count of an
+  // 8-byte copy -- the MIO queue, not HBM, was the limiter) and a float call pair is 3 LDS.128.
   constexpr int CH = VitChunk<T>::n;       // calls per chunk (divides 32)
-  constexpr int ROW = CH * 3;              // complex elements per frame per chunk
-  constexpr int PITCH = ROW + 1;           // odd pitch: the 32 lanes hit distinct banks
-  constexpr int ROWS_PER_STEP = 96 / ROW;  // e = lane + 32 j: every 3 j's the (row, column) pattern repeats
-  constexpr int STEPS = ROW / 3;
-  __align__(16) __shared__ C tile[2][kL2Threads * PITCH];
+  constexpr int ROWU = 12;                 // units per frame per chunk
+  constexpr int PITCHU = ROWU + 1;
+  constexpr int ROWS_PER_STEP = 8;         // unit e = lane + 32 r: every 3 r's the (row, column) pattern repeats 8 rows on
+  constexpr int STEPS = 4;
+  static_assert(CH * 3 * 2 * sizeof(T) == ROWU * 16, "chunk must be 12 units");
+  __align__(16) __shared__ uint4 tile[2][kL2Threads * PITCHU];
 
   const int lane = threadIdx.x & 31, wrow0 = threadIdx.x & ~31;
   const int64_t wframe0 = (int64_t)blockIdx.x * kL2Threads + wrow0;
@@ -207,30 +211,31 @@ viterbi_soqpsk_l2_kernel(const __grid_constant__ VitParams<T> p) {
   uint8_t* ob = (FULL && active && p.dec_bits) ? p.dec_bits + frame * p.n_calls : nullptr;
   int8_t* os = (FULL && active && p.dec_syms) ? p.dec_syms + frame * p.n_calls : nullptr;
 
-  // staging pattern of this lane: three (row, column) pairs, each repeated STEPS times ROWS_PER_STEP rows apart
-  const C* src[3];
-  int dst[3], col[3];
+  // staging pattern of this lane: three (row, unit) pairs, each repeated STEPS times ROWS_PER_STEP rows apart
+  const int64_t row_units = p.ld_z * (int64_t)(3 * 2 * sizeof(T)) / 16;  // ld_z * 24 (or 48) bytes / 16; ld_z is even for float
+  const uint4* src[3];
+  int dst[3], ucall[3];
 #pragma unroll
   for (int r = 0; r < 3; ++r) {
-    const int e = lane + 32 * r, f = e / ROW, k = e - f * ROW;
-    src[r] = reinterpret_cast<const C*>(p.z) + (wframe0 + f) * p.ld_z * 3 + k;
-    dst[r] = (wrow0 + f) * PITCH + k;
-    col[r] = k / 3;
+    const int e = lane + 32 * r, f = e / ROWU, k = e - f * ROWU;
+    src[r] = reinterpret_cast<const uint4*>(p.z) + (wframe0 + f) * row_units + k;
+    dst[r] = (wrow0 + f) * PITCHU + k;
+    ucall[r] = sizeof(T) == 4 ? (2 * k) / 3 : k / 3;  // call of the unit's first element
   }
-  const int64_t src_step = (int64_t)ROWS_PER_STEP * p.ld_z * 3;
+  const int64_t src_step = (int64_t)ROWS_PER_STEP * row_units;
   const int64_t last_row = p.B - 1 - wframe0;  // rows beyond it are clamped to it (valid memory, never used)
 
   auto stage = [&](int buf, int c0) {
     const bool whole = c0 + CH <= n_calls;
 #pragma unroll
     for (int r = 0; r < 3; ++r) {
-      const int f0 = (lane + 32 * r) / ROW;
+      const int f0 = (lane + 32 * r) / ROWU;
 #pragma unroll
       for (int m = 0; m < STEPS; ++m) {
         const int64_t rowi = f0 + m * ROWS_PER_STEP;
-        const int64_t back = rowi > last_row ? (rowi - last_row) * p.ld_z * 3 : 0;
-        if (whole || c0 + col[r] < n_calls)
-          cp_async<sizeof(C)>(&tile[buf][dst[r] + m * ROWS_PER_STEP * PITCH], src[r] + m * src_step - back + (int64_t)c0 * 3);
+        const int64_t back = rowi > last_row ? (rowi - last_row) * row_units : 0;
+        if (whole || c0 + ucall[r] < n_calls)
+          cp_async_cg16(&tile[buf][dst[r] + m * ROWS_PER_STEP * PITCHU], src[r] + m * src_step - back + (int64_t)(c0 / CH) * ROWU);
       }
     }
     cp_async_commit();
@@ -240,6 +245,8 @@ viterbi_soqpsk_l2_kernel(const __grid_constant__ VitParams<T> p) {
   T zpr[3] = {0, 0, 0}, zpi[3] = {0, 0, 0};
   uint32_t decw = 0, w_prev = 0;
   unsigned long long bit_err = 0, sym_err = 0;
+  const int n_words = (n_cmp + 31) >> 5;
+  uint32_t w_next = (txw != nullptr && n_words > 0) ? txw[0] : 0u;  // loaded one group ahead of its use
 
   // compare the 32 decisions of calls [g, g+32) with transmitted bits [g-2, g+30)
   auto count_group = [&](int g) {
@@ -247,7 +254,8 @@ viterbi_soqpsk_l2_kernel(const __grid_constant__ VitParams<T> p) {
     const int lo = max(g, 2), hi = min(g + 32, n_cmp + 2);  // valid call range
     if (hi > lo) {
       const int wi = g >> 5;
-      const uint32_t w_cur = (wi < (int)((n_cmp + 31) >> 5)) ? txw[wi] : 0u;
+      const uint32_t w_cur = w_next;
+      w_next = (wi + 1 < n_words) ? txw[wi + 1] : 0u;
       const uint32_t tx = (w_cur << 2) | (w_prev >> 30);
       uint32_t mask = 0xFFFFFFFFu;
       if (lo > g) mask &= 0xFFFFFFFFu << (lo - g);
@@ -268,12 +276,8 @@ viterbi_soqpsk_l2_kernel(const __grid_constant__ VitParams<T> p) {
       cp_async_wait<0>();
     }
     __syncwarp();
-    const C* row = &tile[c & 1][threadIdx.x * PITCH];
-    auto one_call = [&](int u, int par) {
-      const int i = c0 + u;
-      T zr[3], zi[3];
-#pragma unroll
-      for (int r = 0; r < 3; ++r) { const C v = row[u * 3 + r]; zr[r] = v.x; zi[r] = v.y; }
+    const uint4* row = &tile[c & 1][threadIdx.x * PITCHU];
+    auto decide = [&](int i, const T* zr, const T* zi, int par) {
       const uint32_t d = par ? detector_call_l2<T, 1, DIFF>(M, zpr, zpi, zr, zi)
                              : detector_call_l2<T, 0, DIFF>(M, zpr, zpi, zr, zi);
       decw |= (d & 1u) << (i & 31);
@@ -284,13 +288,33 @@ viterbi_soqpsk_l2_kernel(const __grid_constant__ VitParams<T> p) {
         if (txs && i >= 2 && i - 2 < n_cmp) sym_err += (sym != (int)txs[i - 2]) ? 1u : 0u;
       }
     };
-    if (c0 + CH <= n_calls) {  // whole chunk: one straight-line block, calls overlap in the schedule
+    const bool whole = c0 + CH <= n_calls;
+    if (sizeof(T) == 4) {
 #pragma unroll
-      for (int u = 0; u < CH; ++u) one_call(u, u & 1);
+      for (int u = 0; u < CH; u += 2) {  // a call pair is 3 units: (z0 z1) (z2 z0') (z1' z2')
+        if (whole || c0 + u < n_calls) {
+          const float4 q0 = *reinterpret_cast<const float4*>(row + 3 * (u / 2));
+          const float4 q1 = *reinterpret_cast<const float4*>(row + 3 * (u / 2) + 1);
+          const float4 q2 = *reinterpret_cast<const float4*>(row + 3 * (u / 2) + 2);
+          const T zr0[3] = {(T)q0.x, (T)q0.z, (T)q1.x}, zi0[3] = {(T)q0.y, (T)q0.w, (T)q1.y};
+          const T zr1[3] = {(T)q1.z, (T)q2.x, (T)q2.z}, zi1[3] = {(T)q1.w, (T)q2.y, (T)q2.w};
+          decide(c0 + u, zr0, zi0, 0);
+          if (whole || c0 + u + 1 < n_calls) decide(c0 + u + 1, zr1, zi1, 1);
+        }
+      }
     } else {
 #pragma unroll
-      for (int u = 0; u < CH; ++u)
-        if (c0 + u < n_calls) one_call(u, u & 1);
+      for (int u = 0; u < CH; ++u) {
+        if (whole || c0 + u < n_calls) {
+          T zr[3], zi[3];
+#pragma unroll
+          for (int r = 0; r < 3; ++r) {
+            const double2 v = *reinterpret_cast<const double2*>(row + 3 * u + r);
+            zr[r] = (T)v.x; zi[r] = (T)v.y;
+          }
+          decide(c0 + u, zr, zi, u & 1);
+        }
+      }
     }
     if (((c0 + CH) & 31) == 0) { count_group(c0 + CH - 32); decw = 0; }
     __syncwarp();  // all lanes are done with tile[c & 1] before chunk c+2 is staged into it
@@ -416,7 +440,9 @@ viterbi_soqpsk_any_kernel(const __grid_constant__ VitParams<T> p) {
 template <typename T>
 static int launch_viterbi(const VitParams<T>& p, int diff, cudaStream_t stream) {
   const unsigned grid = (unsigned)((p.B + kVitThreads - 1) / kVitThreads);
-  if (p.length == 2 && !p.state) {
+  // the length-2 kernel stages 16-byte units: rows must start on 16-byte boundaries
+  const bool rows16 = (reinterpret_cast<uintptr_t>(p.z) & 15) == 0 && (sizeof(T) == 8 || (p.ld_z & 1) == 0);
+  if (p.length == 2 && !p.state && rows16) {
     const unsigned g2 = (unsigned)((p.B + kL2Threads - 1) / kL2Threads);
     const bool full = p.dec_bits || p.dec_syms || p.tx_syms;
     if (diff && full) viterbi_soqpsk_l2_kernel<T, true, true><<<g2, kL2Threads, 0, stream>>>(p);
