@@ -358,17 +358,29 @@ cpm_modulate_f32s8_kernel(const __grid_constant__ ModParams<float> p) {
       if (tid < kFLB) { w_s[tid] = wv; f_s[tid] = fv; }
     }
     // ---- (a) scan the segment's symbols: w_k and F[k+1] for k in [k_lo, k_lo + kFSeg) ------
-    int sc = 0;
-    for (; sc < kFSeg && k_lo + sc < S; sc += kScanStep) {
-      const int k0 = k_lo + sc + 4 * tid;
-      int a[4];
+    // every step's packed symbol word is fetched up front: one exposed global latency per segment
+    constexpr int kSteps = kFSeg / kScanStep;
+    uint32_t sv[kSteps];
+#pragma unroll
+    for (int j = 0; j < kSteps; ++j) {
+      const int k0 = k_lo + j * kScanStep + 4 * tid;
+      sv[j] = 0u;
       if (sym_vec && k0 + 3 < S) {
-        const uint32_t v = *reinterpret_cast<const uint32_t*>(sy + k0);
-        a[0] = (int8_t)(v & 0xFF); a[1] = (int8_t)((v >> 8) & 0xFF); a[2] = (int8_t)((v >> 16) & 0xFF); a[3] = (int8_t)(v >> 24);
+        sv[j] = *reinterpret_cast<const uint32_t*>(sy + k0);
       } else {
 #pragma unroll
-        for (int i = 0; i < 4; ++i) a[i] = (k0 + i < S) ? (int)sy[k0 + i] : 0;
+        for (int i = 0; i < 4; ++i)
+          if (k0 + i < S) sv[j] |= (uint32_t)(uint8_t)sy[k0 + i] << (8 * i);
       }
+    }
+    int sc = 0;
+#pragma unroll
+    for (int j = 0; j < kSteps; ++j) {
+      if (k_lo + j * kScanStep >= S) break;  // block-uniform
+      sc = (j + 1) * kScanStep;
+      const int k0 = k_lo + j * kScanStep + 4 * tid;
+      const uint32_t v = sv[j];
+      const int a[4] = {(int8_t)(v & 0xFF), (int8_t)((v >> 8) & 0xFF), (int8_t)((v >> 16) & 0xFF), (int8_t)(v >> 24)};
       uint64_t inc[4], run = 0;
       float wv[4];
       if (one_h) {
@@ -403,7 +415,7 @@ cpm_modulate_f32s8_kernel(const __grid_constant__ ModParams<float> p) {
         if (i < wid) base += t;
         total += t;
       }
-      const int slot = kFLB + sc + 4 * tid;  // 16-byte aligned: one 128-bit store per array
+      const int slot = kFLB + j * kScanStep + 4 * tid;  // 16-byte aligned: one 128-bit store per array
       *reinterpret_cast<float4*>(w_s + slot) = make_float4(wv[0], wv[1], wv[2], wv[3]);
       *reinterpret_cast<uint4*>(f_s + slot) = make_uint4((uint32_t)((base + inc[0]) >> 32), (uint32_t)((base + inc[1]) >> 32),
                                                          (uint32_t)((base + inc[2]) >> 32), (uint32_t)((base + inc[3]) >> 32));
