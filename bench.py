@@ -27,8 +27,11 @@ sys.path.insert(0, ROOT)
 N_BITS, SPS, EBN0_DB, DETECTOR = 4096, 8, 6.0, "PAM"
 FRAMES_PER_GPU = 65536
 METRIC = "viterbi_decoded_bits_per_s_soqpsk_tg"
-# algorithmic bytes per decoded bit (complex64 = 8 B, sps = 8)
-ALGO_BYTES_PER_BIT = {"prbs_encode": 1.125, "modulate_awgn": 65.0, "mf_bank": 88.0, "viterbi_bert": 24.125}
+# algorithmic bytes per decoded bit (complex64 = 8 B, sps = 8).  The PAM link keeps the
+# bank's two raw filter outputs between bank and detector (16 B per call), so the
+# bank moves 64 + 16 and the detector 16 + 1/8 bytes per bit (SURVEY's reference-shaped [calls, 3]
+# array would be 64 + 24 and 24 + 1/8).
+ALGO_BYTES_PER_BIT = {"prbs_encode": 1.125, "modulate_awgn": 65.0, "mf_bank": 80.0, "viterbi_bert": 16.125}
 KERNELS = list(ALGO_BYTES_PER_BIT)
 
 
@@ -137,10 +140,18 @@ def main():
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
+    # stdout carries exactly ONE JSON line: anything a library writes to fd 1 on the way
+    # (NCCL prints its version banner there) is sent to stderr instead
+    sys.stdout.flush()
+    json_fd = os.dup(1)
+    os.dup2(2, 1)
+
+    def emit(obj):
+        os.write(json_fd, (json.dumps(obj) + "\n").encode())
 
     if args.impl == "reference":
         if rank == 0:
-            print(json.dumps(cpu_reference_line(args, as_main=True)), flush=True)
+            emit(cpu_reference_line(args, as_main=True))
         return
 
     # the CPU baseline forks worker processes: take it BEFORE this process owns a CUDA context
@@ -248,7 +259,7 @@ def main():
         }
         if cpu_line is not None:
             line["cpu_baseline"] = cpu_line
-        print(json.dumps(line), flush=True)
+        emit(line)
     if world > 1:
         dist.barrier(device_ids=[local_rank])
         dist.destroy_process_group()

@@ -175,6 +175,20 @@ WF_API int wf_viterbi_soqpsk(const void* d_z, int dtype, int64_t B, int64_t n_ca
                       const int8_t* d_tx_syms, int64_t S,
                       const int32_t* d_point, int64_t* d_counters, void* d_state, void* stream);
 
+/* Counter-only variant fed by the bank's RAW filter outputs (the PAM bank of
+ * examples/soqpsk_detection.py:158-173 has n_in = 2 real filters):
+ * d_y complex[B][ld_y][n_in]; the detector forms z_r = sum_f combine[r][f] y_f (r = 0..2,
+ * HOST float64[3][n_in], the conj(pseudo-symbol) matrix of :165-173) itself, with the same
+ * sequence of fused operations as wf_mf_bank's combine stage, and then runs
+ * SOQPSKTrellisDetector(length=2, differantial_encoding=diff) + the error count exactly as
+ * wf_viterbi_soqpsk does.  Counters are bit-identical to wf_mf_bank(.., combine, ..) +
+ * wf_viterbi_soqpsk(..); the intermediate array is n_in/3 of the size.  Rows must start on
+ * 16-byte boundaries. */
+WF_API int wf_viterbi_soqpsk_combined(const void* d_y, int dtype, int64_t B, int64_t n_calls, int64_t ld_y,
+                               int n_in, const double* combine_re, const double* combine_im, int diff,
+                               const uint32_t* d_tx_packed, int64_t ld_words, int64_t S,
+                               const int32_t* d_point, int64_t* d_counters, void* stream);
+
 /* stand-alone error count of unpacked decisions (soqpsk_detection.py:200-209):
  * drops the first `skip` decisions of each frame, compares n_cmp of them. */
 WF_API int wf_bert(const uint8_t* d_dec_bits, const int8_t* d_dec_syms, int64_t ld_dec,

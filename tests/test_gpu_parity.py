@@ -388,6 +388,19 @@ def test_link_noiseless_round_trip_full_batch():
         assert (be, n) == (0, 2048 * 4093), det
 
 
+def test_raw_bank_detection_equals_combined_bank_detection():
+    """PAM link, two data paths: the bank stores z[.., 3] and wf_viterbi_soqpsk reads it, or the bank
+    stores its two raw outputs and wf_viterbi_soqpsk_combined applies the pseudo-symbol combine.
+    Counters must be identical at every Eb/N0 point (same fused operations, same order)."""
+    eb = [0.0, 4.0, 8.0]
+    a = LinkSimulator(LinkConfig(detector="PAM", n_bits=2048), device=DEV, max_batch=96)
+    b = LinkSimulator(LinkConfig(detector="PAM", n_bits=2048, extra={"combine_in_bank": True}), device=DEV, max_batch=96)
+    assert a.raw_bank and not b.raw_bank and a.z.shape[-1] == 2 and b.z.shape[-1] == 3
+    ca, cb = a.run(eb, 200, first_frame=77), b.run(eb, 200, first_frame=77)
+    assert np.array_equal(ca, cb), (ca, cb)
+    assert ca[:, 2].min() == 200 * 2045 and ca[0, 0] > ca[2, 0] > 0
+
+
 def test_link_matches_oracle_chain_with_philox_noise():
     """Same Philox noise through the CUDA chain and through the float64 oracle chain."""
     cfg = LinkConfig(n_bits=1024, detector="PAM")

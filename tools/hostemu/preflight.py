@@ -376,6 +376,41 @@ def t_lean():
         assert np.array_equal(cnt, want), (B, n_calls, S, dtype, cnt, want)
 
 
+def t_rawbank():
+    """bank without combine + wf_viterbi_soqpsk_combined == bank with combine + wf_viterbi_soqpsk"""
+    from waveforms_b200 import mfbank as _mf
+    rng = np.random.default_rng(9)
+    sps = 8
+    taps, comb = _mf.pam_taps(o.pulse_soqpsk_tg(sps), 0.25, sps)
+    taps, comb = np.asarray(taps), np.asarray(comb)
+    for B, S, dtype in ((37, 300, 0), (3, 77, 0), (34, 129, 1)):
+        T = (S + 1) * sps
+        first, n_calls = _mf.symbol_instants(T, sps, 0, 2)
+        rx = (rng.normal(size=(B, T)) + 1j * rng.normal(size=(B, T)))
+        ld = (n_calls + 3) & ~3
+        cdt = np.complex64 if dtype == 0 else np.complex128
+        rx = np.ascontiguousarray(rx.astype(cdt))
+        tr, trp = darr(taps.real.ravel())
+        cr, crp = darr(comb.real.ravel())
+        ci, cip = darr(comb.imag.ravel())
+        z = np.zeros((B, ld, 3), cdt)
+        y = np.zeros((B, ld, 2), cdt)
+        c = (taps.shape[1] - 1) // 2
+        ok(L.wf_mf_bank(ptr(rx), dtype, B, T, T, trp, None, 2, taps.shape[1], c, crp, cip, 3, sps, first, n_calls, ptr(z), ld, None))
+        ok(L.wf_mf_bank(ptr(rx), dtype, B, T, T, trp, None, 2, taps.shape[1], c, None, None, 2, sps, first, n_calls, ptr(y), ld, None))
+        tx = rng.integers(0, 2, size=(B, S)).astype(np.uint8)
+        pk = np.packbits(tx, axis=1, bitorder="little")
+        pk = np.ascontiguousarray(np.concatenate((pk, np.zeros((B, (-pk.shape[1]) % 4), np.uint8)), axis=1)).view(np.uint32)
+        pts = (np.arange(B) % 2).astype(np.int32)
+        ca, cb = np.zeros((2, 3), np.int64), np.zeros((2, 3), np.int64)
+        ok(L.wf_viterbi_soqpsk(ptr(z), dtype, B, n_calls, ld, 1, 2, None, None, ptr(pk), pk.shape[1], None, S, ptr(pts), ptr(ca),
+                               None, None))
+        ok(L.wf_viterbi_soqpsk_combined(ptr(y), dtype, B, n_calls, ld, 2, crp, cip, 1, ptr(pk), pk.shape[1], S, ptr(pts),
+                                        ptr(cb), None))
+        print(f"  raw bank B={B} S={S} dtype={dtype}: counters {ca.tolist()} vs {cb.tolist()}")
+        assert np.array_equal(ca, cb) and ca[:, 2].sum() == B * max(0, min(S, n_calls - 2))
+
+
 def t_cpm():
     """generic CPM detector (PCM/FM, multi-h) vs oracle/cpm_generic.py, bank + trellis"""
     from oracle.cpm_generic import CpmTrellis
@@ -414,7 +449,7 @@ def t_cpm():
                 assert nd <= 2
 
 
-TESTS = {"lfsr": t_lfsr, "prbs": t_prbs, "mod": t_mod, "mf": t_mf, "vit": t_vit, "noise": t_noise, "stream": t_stream, "lean": t_lean, "cpm": t_cpm}
+TESTS = {"lfsr": t_lfsr, "prbs": t_prbs, "mod": t_mod, "mf": t_mf, "vit": t_vit, "noise": t_noise, "stream": t_stream, "lean": t_lean, "rawbank": t_rawbank, "cpm": t_cpm}
 
 if __name__ == "__main__":
     names = sys.argv[1:] or list(TESTS)

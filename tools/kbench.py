@@ -19,7 +19,7 @@ import torch  # noqa: E402
 
 from waveforms_b200.linksim import LinkConfig, LinkSimulator  # noqa: E402
 
-BYTES = {"prbs_encode": 1.125, "modulate_awgn": 65.0, "mf_bank": 88.0, "viterbi_bert": 24.125}
+BYTES = {"prbs_encode": 1.125, "modulate_awgn": 65.0, "mf_bank": 80.0, "viterbi_bert": 16.125}  # PAM raw-bank link (bench.py)
 
 
 def measure(sim, B, reps, cfg):

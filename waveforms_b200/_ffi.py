@@ -36,6 +36,8 @@ PROTOTYPES = {
                           _vp, _i64, _vp]),
     "wf_viterbi_soqpsk": (_i32, [_vp, _i32, _i64, _i64, _i64, _i32, _i32, _vp, _vp, _vp, _i64, _vp, _i64, _vp, _vp, _vp,
                                  _vp]),
+    "wf_viterbi_soqpsk_combined": (_i32, [_vp, _i32, _i64, _i64, _i64, _i32, _vp, _vp, _i32, _vp, _i64, _i64, _vp, _vp,
+                                          _vp]),
     "wf_viterbi_cpm": (_i32, [_vp, _i32, _i64, _i64, _i64, _i32, _i32, _i32, _vp, _i32, _i32, _vp, _vp, _i64, _i64, _i64,
                               _vp, _vp, _vp]),
     "wf_bert": (_i32, [_vp, _vp, _i64, _vp, _vp, _i64, _i64, _i64, _i64, _vp, _vp, _vp]),

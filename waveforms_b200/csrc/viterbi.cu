@@ -56,6 +56,10 @@ struct VitParams {
   void* state;  // T[B][1 + 4 + 8*length]: call parity, carried metrics, increment history (streaming)
   int64_t B, n_calls, ld_z, ld_words, S;
   int length;
+  // n_in = 2: `z` holds the bank's two raw filter outputs y_f per call and the detector forms
+  // z_r = sum_f comb[r][f] y_f itself (same fused operations as the bank's combine stage)
+  int n_in;
+  T comb_re[6], comb_im[6];
 };
 
 // one ACS stage over column parity C: prev[4] -> next[4], sel bit per state
@@ -184,19 +188,22 @@ constexpr int kL2Threads = 64;  // two warps; each warp owns its 32 frames and i
 // FULL = decisions and/or symbol errors requested (API path); otherwise only packed bit
 // errors are counted: decisions are collected 32 calls at a time and compared with the
 // transmitted bits by funnel-shift (the 2-call decision delay) + XOR + popcount.
-template <typename T, bool DIFF, bool FULL>
+template <typename T, bool DIFF, bool FULL, int NIN>
 __global__ void __launch_bounds__(kL2Threads)
 viterbi_soqpsk_l2_kernel(const __grid_constant__ VitParams<T> p) {
   // Everything is staged and read in 16-byte UNITS (two complex64 or one complex128): a chunk of
   // CH calls is 12 units per frame for both types, rows sit 13 units apart (odd: the quarter-warp
   // phases of LDS.128 are conflict free), one cp.async moves 16 bytes (half the LDGSTS count of an
   // 8-byte copy -- the MIO queue, not HBM, was the limiter) and a float call pair is 3 LDS.128.
+  // NIN = 3: rows hold the three combined outputs z_r (24 bytes per call); NIN = 2: the two raw
+  // filter outputs (16 bytes per call) and the 3x2 combine runs here, off the metric recursion.
   constexpr int CH = VitChunk<T>::n;       // calls per chunk (divides 32)
-  constexpr int ROWU = 12;                 // units per frame per chunk
+  constexpr int ROWU = CH * NIN * 2 * (int)sizeof(T) / 16;  // units per frame per chunk: 12 or 8
   constexpr int PITCHU = ROWU + 1;
-  constexpr int ROWS_PER_STEP = 8;         // unit e = lane + 32 r: every 3 r's the (row, column) pattern repeats 8 rows on
-  constexpr int STEPS = 4;
-  static_assert(CH * 3 * 2 * sizeof(T) == ROWU * 16, "chunk must be 12 units");
+  constexpr int NPAT = ROWU == 12 ? 3 : 1;            // unit e = lane + 32 r: the (row, column) pattern repeats
+  constexpr int ROWS_PER_STEP = 32 * NPAT / ROWU;     // every NPAT r's, this many rows further on
+  constexpr int STEPS = 32 / ROWS_PER_STEP;
+  static_assert(ROWU == 12 || ROWU == 8, "chunk must be 12 or 8 units");
   __align__(16) __shared__ uint4 tile[2][kL2Threads * PITCHU];
 
   const int lane = threadIdx.x & 31, wrow0 = threadIdx.x & ~31;
@@ -212,15 +219,15 @@ viterbi_soqpsk_l2_kernel(const __grid_constant__ VitParams<T> p) {
   int8_t* os = (FULL && active && p.dec_syms) ? p.dec_syms + frame * p.n_calls : nullptr;
 
   // staging pattern of this lane: three (row, unit) pairs, each repeated STEPS times ROWS_PER_STEP rows apart
-  const int64_t row_units = p.ld_z * (int64_t)(3 * 2 * sizeof(T)) / 16;  // ld_z * 24 (or 48) bytes / 16; ld_z is even for float
-  const uint4* src[3];
-  int dst[3], ucall[3];
+  const int64_t row_units = p.ld_z * (int64_t)(NIN * 2 * sizeof(T)) / 16;  // row bytes / 16 (a whole number here)
+  const uint4* src[NPAT];
+  int dst[NPAT], ucall[NPAT];
 #pragma unroll
-  for (int r = 0; r < 3; ++r) {
+  for (int r = 0; r < NPAT; ++r) {
     const int e = lane + 32 * r, f = e / ROWU, k = e - f * ROWU;
     src[r] = reinterpret_cast<const uint4*>(p.z) + (wframe0 + f) * row_units + k;
     dst[r] = (wrow0 + f) * PITCHU + k;
-    ucall[r] = sizeof(T) == 4 ? (2 * k) / 3 : k / 3;  // call of the unit's first element
+    ucall[r] = sizeof(T) == 4 ? (2 * k) / NIN : k / NIN;  // call of the unit's first element
   }
   const int64_t src_step = (int64_t)ROWS_PER_STEP * row_units;
   const int64_t last_row = p.B - 1 - wframe0;  // rows beyond it are clamped to it (valid memory, never used)
@@ -228,7 +235,7 @@ viterbi_soqpsk_l2_kernel(const __grid_constant__ VitParams<T> p) {
   auto stage = [&](int buf, int c0) {
     const bool whole = c0 + CH <= n_calls;
 #pragma unroll
-    for (int r = 0; r < 3; ++r) {
+    for (int r = 0; r < NPAT; ++r) {
       const int f0 = (lane + 32 * r) / ROWU;
 #pragma unroll
       for (int m = 0; m < STEPS; ++m) {
@@ -289,7 +296,34 @@ viterbi_soqpsk_l2_kernel(const __grid_constant__ VitParams<T> p) {
       }
     };
     const bool whole = c0 + CH <= n_calls;
-    if (sizeof(T) == 4) {
+    if (NIN == 2) {
+#pragma unroll
+      for (int u = 0; u < CH; ++u) {
+        if (whole || c0 + u < n_calls) {
+          T yr[2], yi[2];
+          if (sizeof(T) == 4) {
+            const float4 q = *reinterpret_cast<const float4*>(row + u);
+            yr[0] = (T)q.x; yi[0] = (T)q.y; yr[1] = (T)q.z; yi[1] = (T)q.w;
+          } else {
+            const double2 a = *reinterpret_cast<const double2*>(row + 2 * u), b = *reinterpret_cast<const double2*>(row + 2 * u + 1);
+            yr[0] = (T)a.x; yi[0] = (T)a.y; yr[1] = (T)b.x; yi[1] = (T)b.y;
+          }
+          T zr[3], zi[3];
+#pragma unroll
+          for (int r = 0; r < 3; ++r) {  // operation for operation the bank's combine stage (mfbank.cu)
+            T ar = 0, ai = 0;
+#pragma unroll
+            for (int f = 0; f < 2; ++f) {
+              const T cr = p.comb_re[r * 2 + f], ci = p.comb_im[r * 2 + f];
+              ar = fma(cr, yr[f], ar); ar = fma(-ci, yi[f], ar);
+              ai = fma(cr, yi[f], ai); ai = fma(ci, yr[f], ai);
+            }
+            zr[r] = ar; zi[r] = ai;
+          }
+          decide(c0 + u, zr, zi, u & 1);
+        }
+      }
+    } else if (sizeof(T) == 4) {
 #pragma unroll
       for (int u = 0; u < CH; u += 2) {  // a call pair is 3 units: (z0 z1) (z2 z0') (z1' z2')
         if (whole || c0 + u < n_calls) {
@@ -441,14 +475,20 @@ template <typename T>
 static int launch_viterbi(const VitParams<T>& p, int diff, cudaStream_t stream) {
   const unsigned grid = (unsigned)((p.B + kVitThreads - 1) / kVitThreads);
   // the length-2 kernel stages 16-byte units: rows must start on 16-byte boundaries
-  const bool rows16 = (reinterpret_cast<uintptr_t>(p.z) & 15) == 0 && (sizeof(T) == 8 || (p.ld_z & 1) == 0);
+  const bool rows16 = (reinterpret_cast<uintptr_t>(p.z) & 15) == 0 && (sizeof(T) == 8 || p.n_in == 2 || (p.ld_z & 1) == 0);
   if (p.length == 2 && !p.state && rows16) {
     const unsigned g2 = (unsigned)((p.B + kL2Threads - 1) / kL2Threads);
     const bool full = p.dec_bits || p.dec_syms || p.tx_syms;
-    if (diff && full) viterbi_soqpsk_l2_kernel<T, true, true><<<g2, kL2Threads, 0, stream>>>(p);
-    else if (diff) viterbi_soqpsk_l2_kernel<T, true, false><<<g2, kL2Threads, 0, stream>>>(p);
-    else if (full) viterbi_soqpsk_l2_kernel<T, false, true><<<g2, kL2Threads, 0, stream>>>(p);
-    else viterbi_soqpsk_l2_kernel<T, false, false><<<g2, kL2Threads, 0, stream>>>(p);
+    if (p.n_in == 2) {
+      if (diff) viterbi_soqpsk_l2_kernel<T, true, false, 2><<<g2, kL2Threads, 0, stream>>>(p);
+      else viterbi_soqpsk_l2_kernel<T, false, false, 2><<<g2, kL2Threads, 0, stream>>>(p);
+    }
+    else if (diff && full) viterbi_soqpsk_l2_kernel<T, true, true, 3><<<g2, kL2Threads, 0, stream>>>(p);
+    else if (diff) viterbi_soqpsk_l2_kernel<T, true, false, 3><<<g2, kL2Threads, 0, stream>>>(p);
+    else if (full) viterbi_soqpsk_l2_kernel<T, false, true, 3><<<g2, kL2Threads, 0, stream>>>(p);
+    else viterbi_soqpsk_l2_kernel<T, false, false, 3><<<g2, kL2Threads, 0, stream>>>(p);
+  } else if (p.n_in == 2) {
+    return fail(WF_ERR_ARG, "combined-input detection needs length 2, no streaming state and 16-byte aligned rows");
   } else {
     if (diff) viterbi_soqpsk_any_kernel<T, true><<<grid, kVitThreads, 0, stream>>>(p);
     else viterbi_soqpsk_any_kernel<T, false><<<grid, kVitThreads, 0, stream>>>(p);
@@ -482,6 +522,7 @@ int wf_viterbi_soqpsk(const void* d_z, int dtype, int64_t B, int64_t n_calls, in
     p.z = d_z; p.dec_bits = d_dec_bits; p.dec_syms = d_dec_syms; p.tx_packed = d_tx_packed; p.tx_syms = d_tx_syms;
     p.point = d_point; p.counters = reinterpret_cast<unsigned long long*>(d_counters);
     p.B = B; p.n_calls = n_calls; p.ld_z = ld_z; p.ld_words = ld_words; p.S = S; p.length = length; p.state = d_state;
+    p.n_in = 3;
     return launch_viterbi<float>(p, diff, as_stream(stream));
   }
   VitParams<double> p;
@@ -489,6 +530,42 @@ int wf_viterbi_soqpsk(const void* d_z, int dtype, int64_t B, int64_t n_calls, in
   p.z = d_z; p.dec_bits = d_dec_bits; p.dec_syms = d_dec_syms; p.tx_packed = d_tx_packed; p.tx_syms = d_tx_syms;
   p.point = d_point; p.counters = reinterpret_cast<unsigned long long*>(d_counters);
   p.B = B; p.n_calls = n_calls; p.ld_z = ld_z; p.ld_words = ld_words; p.S = S; p.length = length; p.state = d_state;
+  p.n_in = 3;
+  return launch_viterbi<double>(p, diff, as_stream(stream));
+}
+
+// Counter-only detection straight from the bank's RAW filter outputs (n_in = 2, the PAM bank):
+// y is [B][ld_y][2] and z_r = sum_f comb[r][f] y_f (r = 0..2) is formed inside the detector with the
+// bank's own sequence of fused operations, so the counters equal those of
+// wf_mf_bank(.., combine, ..) followed by wf_viterbi_soqpsk(..) bit for bit, while the array between
+// the two kernels is 16 instead of 24 bytes per call.  comb_* are HOST float64[3][2].
+int wf_viterbi_soqpsk_combined(const void* d_y, int dtype, int64_t B, int64_t n_calls, int64_t ld_y, int n_in,
+                               const double* comb_re, const double* comb_im, int diff, const uint32_t* d_tx_packed,
+                               int64_t ld_words, int64_t S, const int32_t* d_point, int64_t* d_counters, void* stream) {
+  using namespace wf;
+  WF_REQUIRE(B >= 0 && n_calls >= 0, "negative shape");
+  WF_REQUIRE(dtype == WF_F32 || dtype == WF_F64, "dtype must be WF_F32 or WF_F64");
+  WF_REQUIRE(n_in == 2 && comb_re, "n_in must be 2 with a 3x2 combine matrix");
+  WF_REQUIRE(ld_y >= n_calls, "ld_y smaller than n_calls");
+  WF_REQUIRE(!d_tx_packed || ld_words >= (S + 31) / 32, "ld_words too small for S");
+  WF_REQUIRE(!d_tx_packed || d_counters, "error counting needs d_counters");
+  int rc;
+  if ((rc = require_device())) return rc;
+  if (B == 0) return WF_OK;
+  WF_REQUIRE(d_y || n_calls == 0, "d_y is NULL");
+  if (dtype == WF_F32) {
+    VitParams<float> p;
+    memset(&p, 0, sizeof(p));
+    p.z = d_y; p.tx_packed = d_tx_packed; p.point = d_point; p.counters = reinterpret_cast<unsigned long long*>(d_counters);
+    p.B = B; p.n_calls = n_calls; p.ld_z = ld_y; p.ld_words = ld_words; p.S = S; p.length = 2; p.n_in = 2;
+    for (int i = 0; i < 6; ++i) { p.comb_re[i] = (float)comb_re[i]; p.comb_im[i] = comb_im ? (float)comb_im[i] : 0.f; }
+    return launch_viterbi<float>(p, diff, as_stream(stream));
+  }
+  VitParams<double> p;
+  memset(&p, 0, sizeof(p));
+  p.z = d_y; p.tx_packed = d_tx_packed; p.point = d_point; p.counters = reinterpret_cast<unsigned long long*>(d_counters);
+  p.B = B; p.n_calls = n_calls; p.ld_z = ld_y; p.ld_words = ld_words; p.S = S; p.length = 2; p.n_in = 2;
+  for (int i = 0; i < 6; ++i) { p.comb_re[i] = comb_re[i]; p.comb_im[i] = comb_im ? comb_im[i] : 0.0; }
   return launch_viterbi<double>(p, diff, as_stream(stream));
 }
 

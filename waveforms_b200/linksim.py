@@ -91,6 +91,14 @@ class LinkSimulator:
         self._comb_re = None if comb is None else _dev.host_f64(np.asarray(comb).real.ravel())
         self._comb_im = None if comb is None else _dev.host_f64(np.asarray(comb).imag.ravel())
         self._n_out = 3
+        # PAM bank + length-2 detector: the bank stores its two raw filter outputs (16 B per call)
+        # and the detector applies the 3x2 pseudo-symbol combine itself (wf_viterbi_soqpsk_combined):
+        # same counters bit for bit, a third less traffic between the two kernels.
+        # extra["combine_in_bank"] = True keeps the reference-shaped [B, calls, 3] array instead.
+        self.raw_bank = (comb is not None and cfg.length == 2 and self._taps.shape[0] == 2
+                         and not bool(cfg.extra.get("combine_in_bank", False)))
+        if self.raw_bank:
+            self._n_out = 2
         self.max_batch = 0
         self._alloc(int(max_batch))
         self.launches = 0  # kernels launched so far (4 per run_batch)
@@ -147,6 +155,8 @@ class LinkSimulator:
         st = _dev.stream_ptr(dev)
         dt = _dev.COMPLEX[cfg.dtype]
         seed = cfg.seed & (2**64 - 1)
+        raw = self.soqpsk and self.raw_bank
+
         def mark():
             if events is not None:
                 e = torch.cuda.Event(enable_timing=True)
@@ -168,8 +178,8 @@ class LinkSimulator:
                                       None if self._tap_im is None else _dev.f64_ptr(self._tap_im),
                                       self._taps.shape[0], self._taps.shape[1],
                                       (self._taps.shape[1] - 1) // 2 if self.soqpsk else cfg.sps - 1,
-                                      None if self._comb_re is None else _dev.f64_ptr(self._comb_re),
-                                      None if self._comb_im is None else _dev.f64_ptr(self._comb_im), self._n_out,
+                                      None if (self._comb_re is None or raw) else _dev.f64_ptr(self._comb_re),
+                                      None if (self._comb_im is None or raw) else _dev.f64_ptr(self._comb_im), self._n_out,
                                       cfg.sps, self.first_instant, self.n_calls, _dev.ptr(self.z), self.ld_z, st))
             mark()
             if not self.soqpsk:
@@ -177,6 +187,14 @@ class LinkSimulator:
                 _ffi.check(lib.wf_viterbi_cpm(_dev.ptr(self.z), dt, B, self.n_calls, self.ld_z, d.M, d.Lp, d.p,
                                               d.h_num.ctypes.data, d.n_h, d.depth, None, _dev.ptr(self.syms), self.n_sym,
                                               self.skip, self.skip, _dev.ptr(point), _dev.ptr(counters), st))
+                mark()
+                self.launches += 4
+                return
+            if raw:
+                _ffi.check(lib.wf_viterbi_soqpsk_combined(_dev.ptr(self.z), dt, B, self.n_calls, self.ld_z, 2,
+                                                          _dev.f64_ptr(self._comb_re), _dev.f64_ptr(self._comb_im),
+                                                          int(cfg.differential), _dev.ptr(self.packed), self.ld_words,
+                                                          self.n_sym, _dev.ptr(point), _dev.ptr(counters), st))
                 mark()
                 self.launches += 4
                 return
