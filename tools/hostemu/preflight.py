@@ -305,6 +305,7 @@ def t_noise():
              ("multih", 4, 2048, [4 / 16, 5 / 16], o.pulse_multih(8), 8, 0, (-3, -1, 1, 3)),
              ("mil", 4, 3000, [0.25], o.pulse_soqpsk_mil(8), 8, 0, (-2, 0, 2)),
              ("tg long", 2, 11001, [0.25], o.pulse_soqpsk_tg(8), 8, 0, (-2, 0, 2)),
+             ("three-h", 2, 2051, [4 / 16, 5 / 16, 7 / 16], o.pulse_multih(8), 8, 0, (-3, -1, 1, 3)),
              ("tg sps10", 2, 3001, [0.25], o.pulse_soqpsk_tg(10), 10, 0, (-2, 0, 2)),
              ("tg f64", 2, 3001, [0.25], o.pulse_soqpsk_tg(8), 8, 1, (-2, 0, 2))]
     for lab, B, S, h, pulse, sps, dtype, alpha in cases:

@@ -174,6 +174,16 @@ __device__ __forceinline__ void noise_pair(uint32_t wa, uint32_t wb, int half, c
   g0 = box_muller16(wa, la, nc);
   g1 = box_muller16(wb, lb, nc);
 }
+// c + sum of the four signed-byte products of a and b (IDP.4A)
+__device__ __forceinline__ int dp4a_s8(uint32_t a, uint32_t b, int c) {
+#ifdef WF_HOSTEMU
+  for (int i = 0; i < 4; ++i) c += (int)(int8_t)(a >> (8 * i)) * (int)(int8_t)(b >> (8 * i));
+  return c;
+#else
+  return __dp4a((int)a, (int)b, c);
+#endif
+}
+
 // packed FP32 FMA (Blackwell FFMA2): one issue slot for two independent fused multiply-adds
 __device__ __forceinline__ float2 ffma2(float2 a, float2 b, float2 c) {
 #ifdef WF_HOSTEMU

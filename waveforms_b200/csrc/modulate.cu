@@ -309,20 +309,21 @@ cpm_modulate_f32s8_kernel(const __grid_constant__ ModParams<float> p) {
 
   if (tid == 0) {
     // per-frame constant folded into the prefix sum: initial phase minus the frame-start
-    // truncation of "same" convolution, sum_k w_k Q[clip(off-(k+1)8, 0, K)] / 8  (turns)
-    double c0 = 0.0;
+    // truncation of "same" convolution, sum_k w_k Q[clip(off-(k+1)8, 0, K)] / 8  (turns).
+    // At most off/8 terms; float is ample (a constant phase error of 1e-7 turns).  No barrier
+    // here: the value is published by the first barrier of the scan, so the other warps are
+    // already fetching symbols while this lane works.
+    float c0 = 0.f;
     for (int k = 0; k < S && (k + 1) * 8 < off; ++k) {
       int idx = off - (k + 1) * 8;
       if (idx > p.K) idx = p.K;
-      c0 += (double)sy[k] * (double)p.hw[k % p.n_h] * (double)p.q[idx];
+      c0 = fmaf((float)sy[k] * p.hw[k % p.n_h], p.q[idx], c0);
     }
-    double t = (double)p.phase0_turns - c0 * 0.125;
-    t -= rint(t);                                                  // [-1/2, 1/2]
-    base_s = (uint64_t)(int64_t)llrint(t * 9223372036854775808.0 * 0.5) << 2;  // t 2^64 without overflowing
+    float t = fmaf(c0, -0.125f, p.phase0_turns);
+    t -= rintf(t);                                                 // [-1/2, 1/2]
+    base_s = (uint64_t)(int64_t)llrintf(t * 4611686018427387904.0f) << 2;  // t 2^64 without overflowing
   }
-  __syncthreads();
-  uint64_t carry = base_s;  // F[scanned] (+ the constant)
-  if (tid < kFLB) { w_s[tid] = 0.f; f_s[tid] = (uint32_t)(carry >> 32); }  // symbols k < 0, F[k <= 0]
+  uint64_t carry = 0;  // F[scanned] (+ the constant), valid after the first scan barrier
 
   NoiseCoef ncoef = noise_coef(0.f);
   u32x4 ctr;
@@ -340,12 +341,6 @@ cpm_modulate_f32s8_kernel(const __grid_constant__ ModParams<float> p) {
   const int sub = tid & 3, grp = tid >> 2;
   const int rho = 2 * sub;
   const int e = ((sub - (off >> 1)) >> 2) & 1;
-  float qa[JT], qb[JT];
-#pragma unroll
-  for (int j = 0; j < JT; ++j) {
-    qa[j] = p.q[rho + 1 + 8 * j] * 0.78539816339744831f;  // Q * 2 pi / sps  (radians per unit w)
-    qb[j] = p.q[rho + 2 + 8 * j] * 0.78539816339744831f;
-  }
   const int A_last = (Ti - 1 + off) >> 3;
   const bool one_h = (p.n_h == 1);
 
@@ -357,77 +352,99 @@ cpm_modulate_f32s8_kernel(const __grid_constant__ ModParams<float> p) {
       __syncthreads();
       if (tid < kFLB) { w_s[tid] = wv; f_s[tid] = fv; }
     }
-    // ---- (a) scan the segment's symbols: w_k and F[k+1] for k in [k_lo, k_lo + kFSeg) ------
-    // every step's packed symbol word is fetched up front: one exposed global latency per segment
-    constexpr int kSteps = kFSeg / kScanStep;
-    uint32_t sv[kSteps];
+    // ---- (a) one-pass scan: w_k and F[k+1] for k in [k_lo, k_lo + kFSeg) -------------------
+    // Thread t owns kPer = 20 consecutive symbols (five packed words): local total -> one block
+    // scan of the 256 totals (two barriers per segment) -> second local pass from the thread's
+    // base writes w and F with 128-bit stores (thread stride 20 words: conflict free).
+    constexpr int kPer = kFSeg / kModThreads;
+    static_assert(kPer % 4 == 0, "whole packed words per thread");
+    const int k0 = k_lo + kPer * tid;
+    uint32_t sv[kPer / 4];
 #pragma unroll
-    for (int j = 0; j < kSteps; ++j) {
-      const int k0 = k_lo + j * kScanStep + 4 * tid;
+    for (int j = 0; j < kPer / 4; ++j) {
+      const int kk = k0 + 4 * j;
       sv[j] = 0u;
-      if (sym_vec && k0 + 3 < S) {
-        sv[j] = *reinterpret_cast<const uint32_t*>(sy + k0);
+      if (sym_vec && kk + 3 < S) {
+        sv[j] = *reinterpret_cast<const uint32_t*>(sy + kk);
       } else {
 #pragma unroll
         for (int i = 0; i < 4; ++i)
-          if (k0 + i < S) sv[j] |= (uint32_t)(uint8_t)sy[k0 + i] << (8 * i);
+          if (kk + i < S) sv[j] |= (uint32_t)(uint8_t)sy[kk + i] << (8 * i);
       }
     }
-    int sc = 0;
+    const int hi0 = one_h ? 0 : k0 % p.n_h;
+    // thread total: byte sums by IDP.4A (even / odd positions apart for two-h patterns), one or two
+    // 64-bit multiplies -- deliberately NOT the per-symbol products of the second pass
+    uint64_t run = 0;
+    if (p.n_h <= 2) {
+      int se = 0, so = 0;
 #pragma unroll
-    for (int j = 0; j < kSteps; ++j) {
-      if (k_lo + j * kScanStep >= S) break;  // block-uniform
-      sc = (j + 1) * kScanStep;
-      const int k0 = k_lo + j * kScanStep + 4 * tid;
-      const uint32_t v = sv[j];
-      const int a[4] = {(int8_t)(v & 0xFF), (int8_t)((v >> 8) & 0xFF), (int8_t)((v >> 16) & 0xFF), (int8_t)(v >> 24)};
-      uint64_t inc[4], run = 0;
-      float wv[4];
-      if (one_h) {
+      for (int j = 0; j < kPer / 4; ++j) { se = dp4a_s8(sv[j], 0x00010001u, se); so = dp4a_s8(sv[j], 0x01000100u, so); }
+      run = one_h ? (uint64_t)((int64_t)(se + so)) * p.hfix[0]
+                  : (uint64_t)((int64_t)se) * p.hfix[hi0] + (uint64_t)((int64_t)so) * p.hfix[hi0 ^ 1];
+    } else {
+      int hi = hi0;
+#pragma unroll 1
+      for (int i = 0; i < kPer; ++i) {
+        const int a = (int8_t)((sv[0] >> (8 * (i & 3))) & 0xFF);
+        run += (uint64_t)((int64_t)a) * p.hfix[hi];
+        if (++hi == p.n_h) hi = 0;
+        if ((i & 3) == 3) {  // rotate the packed words so the loop indexes only sv[0]
+          const uint32_t t0 = sv[0];
 #pragma unroll
-        for (int i = 0; i < 4; ++i) {
-          wv[i] = (float)a[i] * p.hw[0];
-          run += (uint64_t)((int64_t)a[i]) * p.hfix[0];
-          inc[i] = run;
-        }
-      } else {
-        int hi = k0 % p.n_h;
-#pragma unroll
-        for (int i = 0; i < 4; ++i) {
-          wv[i] = (float)a[i] * p.hw[hi];
-          run += (uint64_t)((int64_t)a[i]) * p.hfix[hi];
-          inc[i] = run;
-          if (++hi == p.n_h) hi = 0;
+          for (int j = 0; j + 1 < kPer / 4; ++j) sv[j] = sv[j + 1];
+          sv[kPer / 4 - 1] = t0;
         }
       }
-      uint64_t incl = run;
-#pragma unroll
-      for (int s = 1; s < 32; s <<= 1) {
-        const uint64_t t = __shfl_up_sync(0xFFFFFFFFu, incl, s);
-        if (lane >= s) incl += t;
-      }
-      if (lane == 31) warp_tot[wid] = incl;
-      __syncthreads();
-      uint64_t base = carry + (incl - run), total = 0;
-#pragma unroll
-      for (int i = 0; i < kModThreads / 32; ++i) {
-        const uint64_t t = warp_tot[i];
-        if (i < wid) base += t;
-        total += t;
-      }
-      const int slot = kFLB + j * kScanStep + 4 * tid;  // 16-byte aligned: one 128-bit store per array
-      *reinterpret_cast<float4*>(w_s + slot) = make_float4(wv[0], wv[1], wv[2], wv[3]);
-      *reinterpret_cast<uint4*>(f_s + slot) = make_uint4((uint32_t)((base + inc[0]) >> 32), (uint32_t)((base + inc[1]) >> 32),
-                                                         (uint32_t)((base + inc[2]) >> 32), (uint32_t)((base + inc[3]) >> 32));
-      carry += total;
-      __syncthreads();  // warp_tot is reused by the next step; the last one publishes the ring
     }
-    // the intervals just past the last symbol (A <= S + off/8) read w = 0, F = F[S] up to kFLB slots
-    // beyond the scanned range (only when S ends exactly on a scan step; otherwise the step zero-filled them)
-    if (sc < kFSeg && tid < kFLB) { w_s[kFLB + sc + tid] = 0.f; f_s[kFLB + sc + tid] = (uint32_t)(carry >> 32); }
-    __syncthreads();
+    uint64_t incl = run;
+#pragma unroll
+    for (int s = 1; s < 32; s <<= 1) {
+      const uint64_t t = __shfl_up_sync(0xFFFFFFFFu, incl, s);
+      if (lane >= s) incl += t;
+    }
+    if (lane == 31) warp_tot[wid] = incl;
+    __syncthreads();  // also publishes base_s (first segment) / the look-back copy (later ones)
+    if (k_lo == 0) {
+      carry = base_s;
+      if (tid < kFLB) { w_s[tid] = 0.f; f_s[tid] = (uint32_t)(carry >> 32); }  // symbols k < 0, F[k <= 0]
+    }
+    uint64_t base = carry + (incl - run), total = 0;
+#pragma unroll
+    for (int i = 0; i < kModThreads / 32; ++i) {
+      const uint64_t t = warp_tot[i];
+      if (i < wid) base += t;
+      total += t;
+    }
+    {
+      int hi = hi0;
+#pragma unroll
+      for (int j = 0; j < kPer / 4; ++j) {
+        float wv[4];
+        uint32_t fv[4];
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+          const int a = (int8_t)((sv[j] >> (8 * i)) & 0xFF);
+          wv[i] = (float)a * p.hw[hi];
+          base += (uint64_t)((int64_t)a) * p.hfix[hi];
+          fv[i] = (uint32_t)(base >> 32);  // F[k + 1]
+          if (!one_h && ++hi == p.n_h) hi = 0;
+        }
+        const int slot = kFLB + kPer * tid + 4 * j;  // 16-byte aligned
+        *reinterpret_cast<float4*>(w_s + slot) = make_float4(wv[0], wv[1], wv[2], wv[3]);
+        *reinterpret_cast<uint4*>(f_s + slot) = make_uint4(fv[0], fv[1], fv[2], fv[3]);
+      }
+    }
+    carry += total;
+    __syncthreads();  // the segment is published; warp_tot is free for the next one
 
     // ---- (b) RUN consecutive intervals per thread, barrier free ---------------------------
+    float qa[JT], qb[JT];  // (re)built per segment so that they are not live across the scan
+#pragma unroll
+    for (int j = 0; j < JT; ++j) {
+      qa[j] = p.q[rho + 1 + 8 * j] * 0.78539816339744831f;  // Q * 2 pi / sps  (radians per unit w)
+      qb[j] = p.q[rho + 2 + 8 * j] * 0.78539816339744831f;
+    }
     for (int cs = 0; cs < kFSeg && k_lo + cs <= A_last; cs += kFChunk) {
       const int r0 = cs + grp * RUN + e;             // first interval of this run, relative to k_lo
       if (k_lo + r0 > A_last) break;                 // this run (and every later one of the thread) is past the frame
