@@ -29,3 +29,9 @@ $NCU_CMD > $OUT/ncu_plain2.log 2>&1 &&
 timeout 900 ncu --set full --clock-control none --import-source on -k regex:'cpm_modulate|mf_bank|viterbi|encode_frames' -s 12 -c 4 -o $OUT/prof $NCU_CMD > $OUT/ncu_full.log 2>&1
 echo "ncu full exit $?"
 ls -la $OUT
+
+# configs[1] / configs[2] of BASELINE.json (PCM/FM and ARTM multi-h, 65536 frames): per-kernel timings
+for wf in pcmfm multih soqpsk-tg; do
+  timeout 300 python tools/kbench.py --frames 65536 --reps 3 --waveform $wf >> $OUT/kbench_waveforms.log 2>&1
+done
+cat $OUT/kbench_waveforms.log

@@ -143,6 +143,7 @@ static inline void emu_sincosf(float a, float* s, float* c) { *s = sinf(a); *c =
 static inline float emu_log2f(float x) { return log2f(x); }
 #define __sincosf emu_sincosf
 #define __log2f emu_log2f
+static inline void sincospif(float a, float* s, float* c) { *s = (float)sin(M_PI * (double)a); *c = (float)cos(M_PI * (double)a); }
 static inline void sincospi(double a, double* s, double* c) { *s = sin(M_PI * a); *c = cos(M_PI * a); }
 static inline unsigned long long atomicAdd(unsigned long long* p, unsigned long long v) {
   return __atomic_fetch_add(p, v, __ATOMIC_RELAXED);

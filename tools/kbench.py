@@ -24,7 +24,7 @@ BYTES = {"prbs_encode": 1.125, "modulate_awgn": 65.0, "mf_bank": 80.0, "viterbi_
 
 def measure(sim, B, reps, cfg):
     dev = sim.device
-    sigma = (cfg.sps / (2.0 * 10.0 ** 0.6)) ** 0.5  # 6 dB, 1 bit/symbol
+    sigma = (cfg.sps / (2.0 * sim.bits_per_symbol * 10.0 ** 0.6)) ** 0.5  # 6 dB
     sg = torch.full((B,), sigma, dtype=torch.float32, device=dev)
     counters = torch.zeros((1, 3), dtype=torch.int64, device=dev)
     for _ in range(2):
@@ -42,7 +42,9 @@ def measure(sim, B, reps, cfg):
     for name, ms in tot.items():
         ms /= reps
         out[name] = {"ms": round(ms, 4), "algo_gbs": round(BYTES[name] * bits / ms / 1e6, 1)}
-    out["total_ms"] = round(sum(v["ms"] for v in out.values()), 4)
+    out["waveform"] = cfg.waveform
+    out["frames"] = B
+    out["total_ms"] = round(sum(v["ms"] for v in out.values() if isinstance(v, dict)), 4)
     out["bits_per_s"] = round(bits / out["total_ms"] * 1e3, 1)
     return out
 
@@ -52,9 +54,10 @@ def main():
     ap.add_argument("--frames", type=int, default=16384)
     ap.add_argument("--reps", type=int, default=5)
     ap.add_argument("--detector", default="PAM")
+    ap.add_argument("--waveform", default="soqpsk-tg", help="LinkConfig.waveform (algo_gbs figures are SOQPSK/PAM bytes)")
     ap.add_argument("--env", default=None)
     a = ap.parse_args()
-    cfg = LinkConfig(n_bits=4096, detector=a.detector)
+    cfg = LinkConfig(n_bits=4096, detector=a.detector, waveform=a.waveform)
     sim = LinkSimulator(cfg, device=torch.device("cuda", 0), max_batch=a.frames)
     if a.env:
         name, vals = a.env.split("=")
