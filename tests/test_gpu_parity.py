@@ -180,6 +180,28 @@ def test_modulator_long_frames_batch():
         assert np.max(np.abs(s[k].cpu().numpy() - ref)) < 1e-5
 
 
+@pytest.mark.parametrize("lab", ["tg", "multih", "mil"])
+def test_modulator_degenerate_and_segment_boundary_lengths(lab):
+    """The sps-8 fast path scans a frame in segments of 5120 symbol intervals, 20 symbols per thread:
+    one-symbol frames, lengths around the per-thread, per-step and per-segment boundaries, with the
+    fused noise equal to the stand-alone AWGN kernel's on every length."""
+    rng = np.random.default_rng(21)
+    tre, h, pf = _MOD[lab]
+    alpha = (-3, -1, 1, 3) if lab == "multih" else (-2, 0, 2)
+    pulse = pf(8)
+    for S in (1, 2, 7, 8, 9, 20, 21, 1023, 1025, 5099, 5116, 5119, 5120, 5121, 10241):
+        B = 3 if S < 2000 else 1
+        sy = rng.choice(np.array(alpha, np.int8), size=(B, S)).astype(np.int8)
+        clean = wmod.modulate_frames(cu(sy), h, pulse, 8).contiguous()
+        for b in range(B):
+            ref = o.cpm_modulate_closed_form(sy[b], h, pulse, 8)
+            assert np.max(np.abs(clean[b].cpu().numpy() - ref)) < 1e-5, (lab, S, b)
+        sig = torch.full((B,), 0.8, dtype=torch.float32, device=DEV)
+        sep = add_awgn(clean.clone(), sig, PhiloxRNG(5), first_frame=9)
+        fused = wmod.modulate_frames(cu(sy), h, pulse, 8, sigma=sig, seed=5, first_frame=9)
+        assert torch.max(torch.abs(sep - fused)).item() < 2e-6, (lab, S)
+
+
 def test_frequency_and_phase_modulate():
     rng = np.random.default_rng(3)
     f = rng.normal(size=3000) * 0.3

@@ -153,6 +153,28 @@ def t_mod():
             assert err < tol
 
 
+def t_modedge():
+    """sps-8 fast modulator at degenerate and boundary frame lengths (segment = 5120 intervals)"""
+    rng = np.random.default_rng(21)
+    for lab, h, pulse, alpha in (("tg", [0.25], o.pulse_soqpsk_tg(8), (-2, 0, 2)),
+                                 ("multih", [4 / 16, 5 / 16], o.pulse_multih(8), (-3, -1, 1, 3)),
+                                 ("mil", [0.25], o.pulse_soqpsk_mil(8), (-2, 0, 2))):
+        for S in (1, 2, 3, 7, 8, 9, 19, 20, 21, 1023, 1024, 1025, 5099, 5115, 5116, 5119, 5120, 5121, 5140, 10241):
+            B = 3 if S < 2000 else 1
+            sy = rng.choice(np.array(alpha, np.int8), size=(B, S)).astype(np.int8)
+            got = modulate(sy, h, pulse, 8, 0)
+            sg = np.full(B, 0.8, np.float32)
+            buf = np.ascontiguousarray(got.copy())
+            ok(L.wf_awgn_add(ptr(buf), 0, B, got.shape[1], got.shape[1], ptr(sg), None, 5, 9, None))
+            fused = modulate(sy, h, pulse, 8, 0, sigma=sg, seed=5, first=9)
+            for b in range(B):
+                ref = o.cpm_modulate_closed_form(sy[b], h if len(h) > 1 else h[0], pulse, 8)
+                err = np.max(np.abs(got[b] - ref))
+                assert err < 1e-5, (lab, S, b, err)
+            assert np.max(np.abs(buf - fused)) < 2e-6, (lab, S)
+        print(f"  {lab}: all lengths ok")
+
+
 def mf(rx, taps, comb, sps, n_calls, dtype, first=0):
     B, T = rx.shape
     ld = T
@@ -450,7 +472,7 @@ def t_cpm():
                 assert nd <= 2
 
 
-TESTS = {"lfsr": t_lfsr, "prbs": t_prbs, "mod": t_mod, "mf": t_mf, "vit": t_vit, "noise": t_noise, "stream": t_stream, "lean": t_lean, "rawbank": t_rawbank, "cpm": t_cpm}
+TESTS = {"lfsr": t_lfsr, "prbs": t_prbs, "mod": t_mod, "modedge": t_modedge, "mf": t_mf, "vit": t_vit, "noise": t_noise, "stream": t_stream, "lean": t_lean, "rawbank": t_rawbank, "cpm": t_cpm}
 
 if __name__ == "__main__":
     names = sys.argv[1:] or list(TESTS)
