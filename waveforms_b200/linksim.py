@@ -205,7 +205,7 @@ class LinkSimulator:
         self.launches += 4
 
     # ------------------------------------------------------------------ host-facing calls
-    def run(self, ebn0_db, n_frames: int, first_frame: int = 0) -> np.ndarray:
+    def run(self, ebn0_db, n_frames: int, first_frame: int = 0, active=None) -> np.ndarray:
         """End-to-end call with HOST inputs and outputs: ``ebn0_db`` is a host sequence of P
         Eb/N0 points; every point is simulated on frames first_frame .. first_frame+n_frames-1.
         Per-frame sigma / point tables are staged through pinned memory; returns int64[P, 3] =
@@ -215,6 +215,8 @@ class LinkSimulator:
         sig = sigma_from_ebn0_db(eb, self.cfg.sps, self.bits_per_symbol).astype(np.float32)
         counters = torch.zeros((P, 3), dtype=torch.int64, device=self.device)
         for p in range(P):
+            if active is not None and not active[p]:
+                continue  # the point keeps its row and its noise stream id, it just gets no frames
             for f0 in range(0, n_frames, self.max_batch):
                 B = min(self.max_batch, n_frames - f0)
                 h_sigma = torch.full((B,), float(sig[p]), dtype=torch.float32).pin_memory()
@@ -224,7 +226,7 @@ class LinkSimulator:
                 self.run_batch(first_frame + f0, d_sigma, d_point, counters)
         return counters.cpu().numpy()
 
-    def sweep(self, ebn0_db, n_frames: int, first_frame: int = 0, group=None) -> np.ndarray:
+    def sweep(self, ebn0_db, n_frames: int, first_frame: int = 0, group=None, active=None) -> np.ndarray:
         """Multi-GPU ``run``: this rank simulates its contiguous share of the n_frames of every
         point, then the counters are all-reduced (NCCL, SUM, int64[P,3] -- the only traffic that
         crosses NVLink).  Without an initialised process group it equals ``run``."""
@@ -232,11 +234,39 @@ class LinkSimulator:
 
         eb = np.atleast_1d(np.asarray(ebn0_db, dtype=np.float64))
         if not (dist.is_available() and dist.is_initialized()):
-            return self.run(eb, n_frames, first_frame)
+            return self.run(eb, n_frames, first_frame, active) if active is not None else self.run(eb, n_frames, first_frame)
         rank, world = dist.get_rank(group), dist.get_world_size(group)
         lo, hi = shard_range(n_frames, rank, world)
-        local = self.run(eb, hi - lo, first_frame + lo) if hi > lo else np.zeros((eb.size, 3), dtype=np.int64)
+        if hi > lo:
+            local = self.run(eb, hi - lo, first_frame + lo, active) if active is not None else self.run(eb, hi - lo, first_frame + lo)
+        else:
+            local = np.zeros((eb.size, 3), dtype=np.int64)
         return allreduce_counters(local, self.device, group)
+
+    def waterfall(self, ebn0_db, min_errors: int = 100, max_bits: float = 1e11, chunk_frames: int | None = None,
+                  first_frame: int = 0, group=None) -> np.ndarray:
+        """BER waterfall with a stop rule (BASELINE configs[3]): every Eb/N0 point is
+        simulated in chunks of ``chunk_frames`` frames (default: one full batch per rank) until it
+        has collected ``min_errors`` bit errors or ``max_bits`` compared bits.  Chunks are sharded
+        over the ranks of ``group`` exactly like ``sweep``; the counter all-reduce after each chunk
+        gives every rank the same global view, so all ranks retire a point at the same time.  Frame
+        ids advance by ``chunk_frames`` per chunk for every point, and a point's noise stream is
+        keyed by its index in ``ebn0_db``, so the result does not depend on the number of GPUs."""
+        import torch.distributed as dist
+
+        eb = np.atleast_1d(np.asarray(ebn0_db, dtype=np.float64))
+        world = dist.get_world_size(group) if (dist.is_available() and dist.is_initialized()) else 1
+        chunk = int(chunk_frames) if chunk_frames else world * self.max_batch
+        if chunk <= 0 or self.n_compared <= 0:
+            raise ValueError("chunk_frames and the compared bits per frame must be positive")
+        total = np.zeros((eb.size, 3), dtype=np.int64)
+        active = np.ones(eb.size, dtype=bool)
+        frame = int(first_frame)
+        while active.any():
+            total += self.sweep(eb, chunk, frame, group, active)
+            frame += chunk
+            active = (total[:, 0] < min_errors) & (total[:, 2] < max_bits)
+        return total
 
 
 def allreduce_counters(local: np.ndarray, device, group=None) -> np.ndarray:
