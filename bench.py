@@ -33,6 +33,11 @@ METRIC = "viterbi_decoded_bits_per_s_soqpsk_tg"
 # array would be 64 + 24 and 24 + 1/8).
 ALGO_BYTES_PER_BIT = {"prbs_encode": 1.125, "modulate_awgn": 65.0, "mf_bank": 80.0, "viterbi_bert": 16.125}
 KERNELS = list(ALGO_BYTES_PER_BIT)
+# what ncu shows each stage is limited by (profiles/*_ncu_full_summary.csv)
+BOUND = {"prbs_encode": "alu pipe (integer LFSR / precoder work, ~1 B/bit of HBM)",
+         "modulate_awgn": "xu pipe + issue (12 MUFU per sample pair: sin/cos of the signal, Box-Muller); HBM write 62 %",
+         "mf_bank": "hbm",
+         "viterbi_bert": "issue / alu pipe (add-compare-select recursion, one thread per frame)"}
 
 
 def workload_config(frames, n_gpus):
@@ -233,13 +238,18 @@ def main():
         name = KERNELS[dom]
         algo_bytes = ALGO_BYTES_PER_BIT[name] * B * N_BITS
         achieved = algo_bytes / (per_kernel_ms[dom] * 1e-3) / 1e9
-        traffic = None
+        # measured DRAM bytes per launch (ncu --set full, tools/ncu_summary.py), scaled to this batch
         tpath = os.path.join(ROOT, "profiles", "traffic.json")
+        tj_all = {}
         if os.path.exists(tpath):
             with open(tpath) as f:
-                tj = json.load(f).get(name)
-            if tj and tj.get("frames"):
-                traffic = tj["dram_bytes_per_launch"] * (B / tj["frames"])
+                tj_all = json.load(f)
+
+        def traffic_of(stage):
+            tj = tj_all.get(stage)
+            return tj["dram_bytes_per_launch"] * (B / tj["frames"]) if tj and tj.get("frames") else None
+
+        traffic = traffic_of(name)
         line = {
             "metric": METRIC, "value": value, "unit": "bits/s", "n_gpus": world, "steps": K, "warmup": W,
             "ms_per_step": elapsed_ms / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
@@ -252,6 +262,9 @@ def main():
                          "algorithmic_bytes_per_bit": ALGO_BYTES_PER_BIT[name]},
             "kernels": {KERNELS[k]: {"ms": per_kernel_ms[k],
                                      "algo_gbs": ALGO_BYTES_PER_BIT[KERNELS[k]] * B * N_BITS / (per_kernel_ms[k] * 1e-3) / 1e9,
+                                     "hbm_frac": ALGO_BYTES_PER_BIT[KERNELS[k]] * B * N_BITS / (per_kernel_ms[k] * 1e-3) / 1e9 / peak,
+                                     "algorithmic_bytes": ALGO_BYTES_PER_BIT[KERNELS[k]] * B * N_BITS,
+                                     "traffic": traffic_of(KERNELS[k]), "bound": BOUND[KERNELS[k]],
                                      "share": per_kernel_ms[k] / sum(per_kernel_ms)} for k in range(4)},
             "clocks": clocks,
             "ber": {"ebn0_db": EBN0_DB, "bit_errors": bit_err, "compared": compared,
