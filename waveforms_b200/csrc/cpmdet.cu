@@ -35,6 +35,8 @@ struct CpmParams {
   int delta[kCpmMaxH][16];  // (K_h * alphabet[x]) mod 2p
 };
 
+struct CpmRot { float c[64], s[64]; };  // cos / sin(pi v / p), v in Z_2p (float32 of the double values)
+
 template <typename T>
 __global__ void __launch_bounds__(kCpmWarps * 32)
 viterbi_cpm_kernel(const __grid_constant__ CpmParams p) {
@@ -151,6 +153,97 @@ viterbi_cpm_kernel(const __grid_constant__ CpmParams p) {
   }
 }
 
+// ---------------------------------------------------------------------------
+// Binary, memory-2, single-h shape (IRIG PCM/FM: M = 2, Lp = 2, h = K/p): the same recursion with
+// one THREAD per frame.  The 2 * P2 path metrics live in registers (old and new generation), every
+// predecessor index, filter index and rotation is a compile-time constant (rotations are
+// constant-bank operands), and only the 64-bit survivor words ping-pong through shared memory,
+// laid out [state][thread] so a warp's LDS.64 / STS.64 are conflict free.  Per frame-step this is
+// ~25 instructions instead of the ~400 of the lane-per-state kernel (which spends a whole warp, two
+// shuffle reductions and run-time index arithmetic on one frame).  Semantics are identical: strict
+// '>' keeps x = 0 on ties, the best state is the LOWEST index with the maximum metric, metrics
+// are normalised by the maximum, the oldest survivor symbol of the best state is emitted.
+// ---------------------------------------------------------------------------
+constexpr int kM2Threads = 64;
+
+template <int P2, int D0, int D1>
+__global__ void __launch_bounds__(kM2Threads)
+viterbi_cpm_m2l2_kernel(const __grid_constant__ CpmParams p, const __grid_constant__ CpmRot rot) {
+  constexpr int NS = 2 * P2;
+  __shared__ unsigned long long sv_s[2][NS][kM2Threads];
+  const int tid = threadIdx.x;
+  const int64_t frame = (int64_t)blockIdx.x * kM2Threads + tid;
+  if (frame >= p.B) return;  // no barriers in this kernel: every thread is autonomous
+
+  const int D = p.depth;
+  const unsigned long long hmask = (D >= 64) ? ~0ull : ((1ull << D) - 1ull);
+  const float4* zrow = reinterpret_cast<const float4*>(p.z) + frame * p.ld_z * 2;  // 4 complex64 = 2 float4 per step
+  const int8_t* tx = p.tx_syms ? p.tx_syms + frame * p.S : nullptr;
+  int8_t* out = p.dec_syms ? p.dec_syms + frame * p.n_steps : nullptr;
+  const int64_t n_steps = p.n_steps;
+  const int64_t cmp_lo = p.skip_head, cmp_hi = min(p.S, n_steps) - p.skip_tail;
+
+  float pm[NS], pn[NS];
+#pragma unroll
+  for (int s = 0; s < NS; ++s) { pm[s] = 0.f; sv_s[0][s][tid] = 0ull; }
+
+  unsigned long long sym_err = 0, compared = 0;
+  auto emit = [&](int64_t idx, unsigned v) {
+    if (out) out[idx] = (int8_t)(2 * (int)v - 1);
+    if (tx && idx >= cmp_lo && idx < cmp_hi) {
+      const unsigned t = (unsigned)(((int)tx[idx] + 1) >> 1);
+      sym_err += (t != v) ? 1u : 0u;
+      ++compared;
+    }
+  };
+
+  int cur = 0;
+  float4 za = n_steps > 0 ? zrow[0] : make_float4(0.f, 0.f, 0.f, 0.f);
+  float4 zb = n_steps > 0 ? zrow[1] : make_float4(0.f, 0.f, 0.f, 0.f);
+  for (int64_t i = 0; i < n_steps; ++i) {
+    const float zx[4] = {za.x, za.z, zb.x, zb.z}, zy[4] = {za.y, za.w, zb.y, zb.w};
+    if (i + 1 < n_steps) { za = zrow[2 * (i + 1)]; zb = zrow[2 * (i + 1) + 1]; }  // next step's sector, a step ahead
+    const unsigned long long(*ho)[kM2Threads] = sv_s[cur];
+    unsigned long long(*hn)[kM2Threads] = sv_s[cur ^ 1];
+#pragma unroll
+    for (int s = 0; s < NS; ++s) {
+      constexpr int dummy = 0; (void)dummy;
+      const int vnew = s >> 1, hnew = s & 1;
+      const int vp0 = (vnew - D0 + 2 * P2) % P2, vp1 = (vnew - D1 + 2 * P2) % P2;
+      const int pred0 = vp0 * 2, pred1 = vp1 * 2 + 1;
+      const int f0 = hnew * 2, f1 = hnew * 2 + 1;
+      // pm + Re{e^{-j pi v/p} z} = pm + (cos * zr + sin * zi), evaluated in this order (as in the generic kernel)
+      const float c0 = pm[pred0] + (rot.c[vp0] * zx[f0] + rot.s[vp0] * zy[f0]);
+      const float c1 = pm[pred1] + (rot.c[vp1] * zx[f1] + rot.s[vp1] * zy[f1]);
+      const bool win1 = c1 > c0;
+      pn[s] = win1 ? c1 : c0;
+      const unsigned long long h = win1 ? ho[pred1][tid] : ho[pred0][tid];
+      hn[s][tid] = ((h << 1) | (unsigned long long)hnew) & hmask;
+    }
+    float wmax = pn[0];
+#pragma unroll
+    for (int s = 1; s < NS; ++s) wmax = pn[s] > wmax ? pn[s] : wmax;
+    int best_s = NS - 1;
+#pragma unroll
+    for (int s = NS - 2; s >= 0; --s) best_s = (pn[s] == wmax) ? s : best_s;  // lowest index wins
+    if (pn[NS - 1] != wmax && best_s == NS - 1) best_s = 0;                    // unreachable (wmax is one of them)
+#pragma unroll
+    for (int s = 0; s < NS; ++s) pm[s] = pn[s] - wmax;
+    cur ^= 1;
+    if (i >= D - 1) emit(i - D + 1, (unsigned)((sv_s[cur][best_s][tid] >> (D - 1)) & 1ull));
+    if (i == n_steps - 1) {  // flush the tail from the best final survivor
+      const unsigned long long h = sv_s[cur][best_s][tid];
+      for (int d = 0; d < D - 1 && d < n_steps; ++d) emit(n_steps - 1 - d, (unsigned)((h >> d) & 1ull));
+    }
+  }
+  if (p.counters) {
+    const int64_t pt = p.point ? p.point[frame] : 0;
+    atomicAdd(&p.counters[3 * pt + 0], sym_err);  // binary alphabet: bit errors = symbol errors
+    atomicAdd(&p.counters[3 * pt + 1], sym_err);
+    atomicAdd(&p.counters[3 * pt + 2], compared);
+  }
+}
+
 }  // namespace wf
 
 extern "C" int wf_viterbi_cpm(const void* d_z, int dtype, int64_t B, int64_t n_steps, int64_t ld_z, int M, int Lp,
@@ -192,6 +285,19 @@ extern "C" int wf_viterbi_cpm(const void* d_z, int dtype, int64_t B, int64_t n_s
   q.z = d_z; q.dec_syms = d_dec_syms; q.tx_syms = d_tx_syms; q.point = d_point;
   q.counters = reinterpret_cast<unsigned long long*>(d_counters);
   q.B = B; q.n_steps = n_steps; q.ld_z = ld_z; q.S = S; q.skip_head = skip_head; q.skip_tail = skip_tail;
+  // IRIG PCM/FM shape (binary, memory 2, h = 7/10, 4-complex rows on 16-byte boundaries): thread-per-frame kernel
+  if (dtype == WF_F32 && M == 2 && Lp == 2 && n_h == 1 && p == 10 && q.delta[0][0] == 13 && q.delta[0][1] == 7 &&
+      (reinterpret_cast<uintptr_t>(d_z) & 15) == 0) {
+    CpmRot rot;
+    for (int v = 0; v < 2 * p; ++v) {
+      rot.c[v] = (float)cos(M_PI * (double)v / (double)p);
+      rot.s[v] = (float)sin(M_PI * (double)v / (double)p);
+    }
+    const unsigned g = (unsigned)((B + kM2Threads - 1) / kM2Threads);
+    viterbi_cpm_m2l2_kernel<20, 13, 7><<<g, kM2Threads, 0, as_stream(stream)>>>(q, rot);
+    WF_LAUNCH_CHECK("viterbi_cpm_m2l2_kernel");
+    return WF_OK;
+  }
   const unsigned grid = (unsigned)((B + kCpmWarps - 1) / kCpmWarps);
   if (dtype == WF_F32) viterbi_cpm_kernel<float><<<grid, kCpmWarps * 32, 0, as_stream(stream)>>>(q);
   else viterbi_cpm_kernel<double><<<grid, kCpmWarps * 32, 0, as_stream(stream)>>>(q);
