@@ -244,6 +244,163 @@ viterbi_cpm_m2l2_kernel(const __grid_constant__ CpmParams p, const __grid_consta
   }
 }
 
+// ---------------------------------------------------------------------------
+// Memory-2 trellises with 2p = 32 phase states (ARTM multi-h: M = 4, h = {4, 5}/16 -> 128 states):
+// one WARP per frame, lane = phase state v, the M history states of a lane in REGISTERS.
+// For Lp = 2 the predecessor of (v, h_new) through oldest symbol x is (v - delta[x], x): the same
+// lane and register for every h_new, so a step needs only M metric shuffles and M survivor
+// shuffles (lane-varying source = v - delta[x]); rotations and source lanes are per-lane registers
+// for each modulation-index parity, the step's M^2 bank outputs come from a 4-deep cp.async ring
+// read by broadcast LDS.128.  No shared-memory metric/survivor ping-pong, no run-time index
+// arithmetic, transmitted symbols fetched 32 at a time.  Same semantics as viterbi_cpm_kernel.
+// ---------------------------------------------------------------------------
+constexpr int kLvWarps = 4;
+constexpr int kLvRing = 4;
+
+template <int M, int NHH>
+__global__ void __launch_bounds__(kLvWarps * 32)
+viterbi_cpm_lanev_kernel(const __grid_constant__ CpmParams p, const __grid_constant__ CpmRot rot) {
+  constexpr int NF = M * M;                 // bank outputs per step and parity
+  constexpr int BITS = M == 2 ? 1 : (M == 4 ? 2 : (M == 8 ? 3 : 4));
+  __align__(16) __shared__ float2 z_s[kLvWarps][kLvRing][NF];
+  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+  const int64_t frame = (int64_t)blockIdx.x * kLvWarps + wid;
+  if (frame >= p.B) return;  // whole warp; only warp-level synchronisation below
+
+  const int D = p.depth;
+  const unsigned long long hmask = (D * BITS >= 64) ? ~0ull : ((1ull << (D * BITS)) - 1ull);
+  const float2* zrow = reinterpret_cast<const float2*>(p.z) + frame * p.ld_z * p.n_cols;
+  const int8_t* tx = p.tx_syms ? p.tx_syms + frame * p.S : nullptr;
+  int8_t* out = p.dec_syms ? p.dec_syms + frame * p.n_steps : nullptr;
+  const int64_t n_steps = p.n_steps;
+  const int64_t cmp_lo = p.skip_head, cmp_hi = min(p.S, n_steps) - p.skip_tail;
+
+  // per-lane transition tables for each modulation-index parity
+  int src[NHH][M];
+  float rc[NHH][M], rs[NHH][M];
+#pragma unroll
+  for (int h = 0; h < NHH; ++h)
+#pragma unroll
+    for (int x = 0; x < M; ++x) {
+      src[h][x] = (lane - p.delta[h][x]) & 31;
+      rc[h][x] = rot.c[src[h][x]];
+      rs[h][x] = rot.s[src[h][x]];
+#ifndef WF_HOSTEMU
+      // pin the values in registers: left alone, the compiler re-reads rot.c[src] in the loop, a
+      // lane-divergent constant-bank access that serialises 32 ways (13 stall cycles per issue in ncu)
+      asm volatile("" : "+r"(src[h][x]), "+f"(rc[h][x]), "+f"(rs[h][x]));
+#endif
+    }
+
+  float pm[M];
+  unsigned long long sv[M];
+#pragma unroll
+  for (int h = 0; h < M; ++h) { pm[h] = 0.f; sv[h] = 0ull; }
+
+  unsigned long long sym_err = 0, bit_err = 0, compared = 0;  // lane 0
+  int tx_reg = 0;                                              // tx[32 g + lane] of the current group g
+  auto emit = [&](int64_t idx, unsigned v) {                   // executed by every lane (shuffle inside); lane 0 counts
+    if ((idx & 31) == 0 || idx == cmp_lo) {                    // (re)load the group of 32 transmitted symbols
+      const int64_t k = (idx & ~(int64_t)31) + lane;
+      tx_reg = (tx && k < p.S) ? (int)tx[k] : 0;
+    }
+    const int t_sym = __shfl_sync(0xFFFFFFFFu, tx_reg, (int)(idx & 31));
+    if (lane == 0) {
+      if (out) out[idx] = (int8_t)(2 * (int)v - (M - 1));
+      if (tx && idx >= cmp_lo && idx < cmp_hi) {
+        const unsigned t = (unsigned)((t_sym + (M - 1)) >> 1);
+        sym_err += (t != v) ? 1u : 0u;
+        bit_err += __popc((t ^ v) & (unsigned)(M - 1));
+        ++compared;
+      }
+    }
+  };
+
+  auto stage = [&](int64_t i) {  // 16 bytes per lane: NF complex64 = NF/2 lanes
+    if (i < n_steps && lane < NF / 2) {
+      const int par = (int)(i % NHH);
+      cp_async_cg16(&z_s[wid][i % kLvRing][2 * lane], zrow + i * p.n_cols + par * NF + 2 * lane);
+    }
+    cp_async_commit();
+  };
+  for (int k = 0; k < kLvRing - 1; ++k) stage(k);
+
+  bool tx_loaded = false;
+  for (int64_t i0 = 0; i0 < n_steps; i0 += NHH) {
+#pragma unroll
+    for (int hp = 0; hp < NHH; ++hp) {
+      const int64_t i = i0 + hp;
+      if (i >= n_steps) break;
+      // parity of the filters is i % NHH = hp (i0 is a multiple of NHH); of the transition (i - Lp + 1) % NHH
+      constexpr int dummy = 0; (void)dummy;
+      const int lp = (hp + NHH - 1) % NHH;
+      __syncwarp();              // every lane has finished reading the slot that is staged next
+      stage(i + kLvRing - 1);
+      cp_async_wait<kLvRing - 1>();
+      __syncwarp();              // the step's bank outputs are visible to all lanes
+      const float4* zq = reinterpret_cast<const float4*>(z_s[wid][i % kLvRing]);
+      float pmx[M];
+      unsigned long long svx[M];
+#pragma unroll
+      for (int x = 0; x < M; ++x) {
+        pmx[x] = __shfl_sync(0xFFFFFFFFu, pm[x], src[lp][x]);
+        svx[x] = __shfl_sync(0xFFFFFFFFu, sv[x], src[lp][x]);
+      }
+      float lmax = -3.0e38f;
+#pragma unroll
+      for (int hn = 0; hn < M; ++hn) {
+        float best = 0.f;
+        unsigned long long bsv = 0ull;
+#pragma unroll
+        for (int x = 0; x < M; x += 2) {
+          const float4 q = zq[(hn * M + x) / 2];  // two complex outputs: f = hn M + x, f + 1
+          // pm + Re{e^{-j pi v/p} z} = pm + (cos * zr + sin * zi), evaluated in this order
+          const float ca = pmx[x] + (rc[lp][x] * q.x + rs[lp][x] * q.y);
+          const float cb = pmx[x + 1] + (rc[lp][x + 1] * q.z + rs[lp][x + 1] * q.w);
+          if (x == 0 || ca > best) { best = ca; bsv = svx[x]; }
+          if (cb > best) { best = cb; bsv = svx[x + 1]; }
+        }
+        pm[hn] = best;
+        sv[hn] = ((bsv << BITS) | (unsigned long long)hn) & hmask;
+        lmax = best > lmax ? best : lmax;
+      }
+      float wmax = lmax;
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) {
+        const float t = __shfl_xor_sync(0xFFFFFFFFu, wmax, o);
+        wmax = t > wmax ? t : wmax;
+      }
+      int best_s = 0x7FFFFFFF;  // lowest state index v M + h with the maximum metric
+      unsigned long long my_sv = 0ull;
+#pragma unroll
+      for (int hn = M - 1; hn >= 0; --hn) {
+        if (pm[hn] == wmax) { best_s = lane * M + hn; my_sv = sv[hn]; }
+        pm[hn] -= wmax;
+      }
+      int wbest = best_s;
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) {
+        const int t = __shfl_xor_sync(0xFFFFFFFFu, wbest, o);
+        wbest = t < wbest ? t : wbest;
+      }
+      if (i >= D - 1 || i == n_steps - 1) {
+        const unsigned long long h = __shfl_sync(0xFFFFFFFFu, my_sv, wbest / M);  // the best lane's lowest-h survivor
+        if (i >= D - 1) emit(i - D + 1, (unsigned)((h >> ((D - 1) * BITS)) & (unsigned)(M - 1)));
+        if (i == n_steps - 1)  // flush the tail from the best final survivor
+          for (int d = D - 2 < n_steps - 1 ? D - 2 : (int)(n_steps - 1); d >= 0; --d)
+            emit(n_steps - 1 - d, (unsigned)((h >> (d * BITS)) & (unsigned)(M - 1)));
+      }
+    }
+  }
+  (void)tx_loaded;
+  if (lane == 0 && p.counters) {
+    const int64_t pt = p.point ? p.point[frame] : 0;
+    atomicAdd(&p.counters[3 * pt + 0], bit_err);
+    atomicAdd(&p.counters[3 * pt + 1], sym_err);
+    atomicAdd(&p.counters[3 * pt + 2], compared);
+  }
+}
+
 }  // namespace wf
 
 extern "C" int wf_viterbi_cpm(const void* d_z, int dtype, int64_t B, int64_t n_steps, int64_t ld_z, int M, int Lp,
@@ -296,6 +453,19 @@ extern "C" int wf_viterbi_cpm(const void* d_z, int dtype, int64_t B, int64_t n_s
     const unsigned g = (unsigned)((B + kM2Threads - 1) / kM2Threads);
     viterbi_cpm_m2l2_kernel<20, 13, 7><<<g, kM2Threads, 0, as_stream(stream)>>>(q, rot);
     WF_LAUNCH_CHECK("viterbi_cpm_m2l2_kernel");
+    return WF_OK;
+  }
+  // memory-2 trellis with 32 phase states (ARTM multi-h): lane-per-phase-state register kernel
+  if (dtype == WF_F32 && M == 4 && Lp == 2 && p == 16 && n_h == 2 && q.depth * q.bits <= 64 &&
+      (reinterpret_cast<uintptr_t>(d_z) & 15) == 0) {
+    CpmRot rot;
+    for (int v = 0; v < 2 * p; ++v) {
+      rot.c[v] = (float)cos(M_PI * (double)v / (double)p);
+      rot.s[v] = (float)sin(M_PI * (double)v / (double)p);
+    }
+    const unsigned g = (unsigned)((B + kLvWarps - 1) / kLvWarps);
+    viterbi_cpm_lanev_kernel<4, 2><<<g, kLvWarps * 32, 0, as_stream(stream)>>>(q, rot);
+    WF_LAUNCH_CHECK("viterbi_cpm_lanev_kernel");
     return WF_OK;
   }
   const unsigned grid = (unsigned)((B + kCpmWarps - 1) / kCpmWarps);
