@@ -180,14 +180,14 @@ def test_modulator_long_frames_batch():
         assert np.max(np.abs(s[k].cpu().numpy() - ref)) < 1e-5
 
 
-@pytest.mark.parametrize("lab", ["tg", "multih", "mil"])
+@pytest.mark.parametrize("lab", ["tg", "multih", "mil", "pcmfm"])
 def test_modulator_degenerate_and_segment_boundary_lengths(lab):
     """The sps-8 fast path scans a frame in segments of 5120 symbol intervals, 20 symbols per thread:
     one-symbol frames, lengths around the per-thread, per-step and per-segment boundaries, with the
     fused noise equal to the stand-alone AWGN kernel's on every length."""
     rng = np.random.default_rng(21)
     tre, h, pf = _MOD[lab]
-    alpha = (-3, -1, 1, 3) if lab == "multih" else (-2, 0, 2)
+    alpha = {"multih": (-3, -1, 1, 3), "pcmfm": (-1, 1)}.get(lab, (-2, 0, 2))
     pulse = pf(8)
     for S in (1, 2, 7, 8, 9, 20, 21, 1023, 1025, 5099, 5116, 5119, 5120, 5121, 10241):
         B = 3 if S < 2000 else 1

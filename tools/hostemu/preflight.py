@@ -158,7 +158,8 @@ def t_modedge():
     rng = np.random.default_rng(21)
     for lab, h, pulse, alpha in (("tg", [0.25], o.pulse_soqpsk_tg(8), (-2, 0, 2)),
                                  ("multih", [4 / 16, 5 / 16], o.pulse_multih(8), (-3, -1, 1, 3)),
-                                 ("mil", [0.25], o.pulse_soqpsk_mil(8), (-2, 0, 2))):
+                                 ("mil", [0.25], o.pulse_soqpsk_mil(8), (-2, 0, 2)),
+                                 ("pcmfm", [0.7], o.pulse_pcmfm(8, 4), (-1, 1))):
         for S in (1, 2, 3, 7, 8, 9, 19, 20, 21, 1023, 1024, 1025, 5099, 5115, 5116, 5119, 5120, 5121, 5140, 10241):
             B = 3 if S < 2000 else 1
             sy = rng.choice(np.array(alpha, np.int8), size=(B, S)).astype(np.int8)
@@ -326,6 +327,7 @@ def t_noise():
     cases = [("tg", 4, 4096, [0.25], o.pulse_soqpsk_tg(8), 8, 0, (-2, 0, 2)),
              ("multih", 4, 2048, [4 / 16, 5 / 16], o.pulse_multih(8), 8, 0, (-3, -1, 1, 3)),
              ("mil", 4, 3000, [0.25], o.pulse_soqpsk_mil(8), 8, 0, (-2, 0, 2)),
+             ("pcmfm", 4, 4096, [0.7], o.pulse_pcmfm(8, 4), 8, 0, (-1, 1)),
              ("tg long", 2, 11001, [0.25], o.pulse_soqpsk_tg(8), 8, 0, (-2, 0, 2)),
              ("three-h", 2, 2051, [4 / 16, 5 / 16, 7 / 16], o.pulse_multih(8), 8, 0, (-3, -1, 1, 3)),
              ("tg sps10", 2, 3001, [0.25], o.pulse_soqpsk_tg(10), 10, 0, (-2, 0, 2)),

@@ -264,21 +264,21 @@ constexpr size_t kFSmemBytes = (size_t)kFSlots * 8;
 
 // Rare path (p = 2^-15 per pair): one pair again, this time with the tail refinement of the
 // radius uniform.  Kept out of line so the unrolled main loop stays branch free.
-// wwin = w_s + slot(A - JT) (symbols A-JT .. A-1), f_old = F[A - JT].
+// Sample a: window wa (symbols A-JT .. A-1 of ITS interval), fa = F[A - JT], Q index qa0 + 8 j;
+// sample b likewise (the two differ only for an odd "same" offset, see ODD in the kernel).
 template <int JT>
-static __device__ __noinline__ float4 mod_f32s8_slow_pair(const ModParams<float>& p, const float* wwin, uint32_t f_old, int rho,
-                                                          u32x4 ctr, int half, NoiseCoef ncoef) {
+static __device__ __noinline__ float4 mod_f32s8_slow_pair(const ModParams<float>& p, const float* wa, const float* wb, uint32_t fa,
+                                                          uint32_t fb, int qa0, int qb0, u32x4 ctr, int half, NoiseCoef ncoef) {
   float acc0 = 0.f, acc1 = 0.f;
 #pragma unroll
   for (int j = 0; j < JT; ++j) {
-    const float wj = wwin[JT - 1 - j];
-    acc0 = fmaf(wj, p.q[rho + 1 + 8 * j] * 0.78539816339744831f, acc0);
-    acc1 = fmaf(wj, p.q[rho + 2 + 8 * j] * 0.78539816339744831f, acc1);
+    acc0 = fmaf(wa[JT - 1 - j], p.q[qa0 + 8 * j] * 0.78539816339744831f, acc0);
+    acc1 = fmaf(wb[JT - 1 - j], p.q[qb0 + 8 * j] * 0.78539816339744831f, acc1);
   }
-  const float old = (float)(int32_t)f_old * 1.4629180792671596e-09f;
+  const float olda = (float)(int32_t)fa * 1.4629180792671596e-09f, oldb = (float)(int32_t)fb * 1.4629180792671596e-09f;
   float c0f, s0f, c1f, s1f;
-  __sincosf(acc0 + old, &s0f, &c0f);
-  __sincosf(acc1 + old, &s1f, &c1f);
+  __sincosf(acc0 + olda, &s0f, &c0f);
+  __sincosf(acc1 + oldb, &s1f, &c1f);
   const uint32_t k0 = (uint32_t)p.seed, k1 = (uint32_t)(p.seed >> 32);
   const u32x4 r = philox4x32_10(ctr, k0, k1);
   float2 g0, g1;
@@ -286,7 +286,11 @@ static __device__ __noinline__ float4 mod_f32s8_slow_pair(const ModParams<float>
   return make_float4(c0f + g0.x, s0f + g0.y, c1f + g1.x, s1f + g1.y);
 }
 
-template <int JT, bool NOISE, int RUN, int MINB>
+// ODD: the "same"-mode offset off = (K-1)/2 is odd (PCM/FM, K = 24).  Sample n = a - off is then
+// even for ODD a, so a thread's pair is a = 8 A + 2 sub - 1, 8 A + 2 sub; for sub = 0 the first of
+// the two is the LAST sample (rho = 7) of interval A - 1: one symbol further back in the window and
+// in F.  The pair then runs on two scalar FFMA chains instead of one packed FFMA2 chain.
+template <int JT, bool NOISE, int RUN, int MINB, bool ODD>
 __global__ void __launch_bounds__(kModThreads, MINB)
 cpm_modulate_f32s8_kernel(const __grid_constant__ ModParams<float> p) {
   constexpr int kFChunk = RUN * (kModThreads / 4);
@@ -339,8 +343,10 @@ cpm_modulate_f32s8_kernel(const __grid_constant__ ModParams<float> p) {
   // Its pair index at interval A is 4 A + sub - off/2; e makes (pair >> 2) even at the first
   // interval of every run, so iterations (2m, 2m+1) share Philox call c0 + 4m.
   const int sub = tid & 3, grp = tid >> 2;
-  const int rho = 2 * sub;
-  const int e = ((sub - (off >> 1)) >> 2) & 1;
+  const int rho = 2 * sub - (ODD ? 1 : 0);          // a of the pair's first sample (-1: rho 7 of the interval before)
+  const bool sha = ODD && sub == 0;
+  const int qa0 = sha ? 8 : rho + 1, qb0 = rho + 2;  // Q index of the newest symbol's tap for samples a, b
+  const int e = ((sub - ((off + 1) >> 1)) >> 2) & 1;
   const int A_last = (Ti - 1 + off) >> 3;
   const bool one_h = (p.n_h == 1);
 
@@ -442,17 +448,27 @@ cpm_modulate_f32s8_kernel(const __grid_constant__ ModParams<float> p) {
     float qa[JT], qb[JT];  // (re)built per segment so that they are not live across the scan
 #pragma unroll
     for (int j = 0; j < JT; ++j) {
-      qa[j] = p.q[rho + 1 + 8 * j] * 0.78539816339744831f;  // Q * 2 pi / sps  (radians per unit w)
-      qb[j] = p.q[rho + 2 + 8 * j] * 0.78539816339744831f;
+      qa[j] = p.q[qa0 + 8 * j] * 0.78539816339744831f;  // Q * 2 pi / sps  (radians per unit w)
+      qb[j] = p.q[qb0 + 8 * j] * 0.78539816339744831f;
     }
     for (int cs = 0; cs < kFSeg && k_lo + cs <= A_last; cs += kFChunk) {
       const int r0 = cs + grp * RUN + e;             // first interval of this run, relative to k_lo
       if (k_lo + r0 > A_last) break;                 // this run (and every later one of the thread) is past the frame
       const float* wp = w_s + (r0 - JT + kFLB);      // symbols A0-JT .. A0+RUN-2
       const uint32_t* fp = f_s + (r0 - JT - 1 + kFLB);  // F[A0-JT ..]
-      float w[JT + RUN - 1];
+      float w[JT + RUN - 1];   // sample b's window (and sample a's unless it sits one interval back)
+      float wa[ODD ? JT + RUN - 1 : 1];
+      uint32_t fa[ODD ? RUN : 1];
 #pragma unroll
       for (int j = 0; j < JT + RUN - 1; ++j) w[j] = wp[j];
+      if (ODD) {
+        const float* wq = sha ? wp - 1 : wp;
+        const uint32_t* fq = sha ? fp - 1 : fp;
+#pragma unroll
+        for (int j = 0; j < JT + RUN - 1; ++j) wa[j] = wq[j];
+#pragma unroll
+        for (int j = 0; j < RUN; ++j) fa[j] = fq[j];
+      }
       const int n0 = 8 * (k_lo + r0) + rho - off;    // first sample of the first pair (< 0 before the frame starts)
       float4* o = out + (n0 >> 1);
 #ifndef WF_HOSTEMU
@@ -466,6 +482,13 @@ cpm_modulate_f32s8_kernel(const __grid_constant__ ModParams<float> p) {
 #pragma unroll
       for (int i = 0; i < RUN; ++i) {
         float acc0 = 0.f, acc1 = 0.f;
+        if (ODD) {
+#pragma unroll
+          for (int j = 0; j < JT; ++j) {
+            acc0 = fmaf(wa[i + JT - 1 - j], qa[j], acc0);
+            acc1 = fmaf(w[i + JT - 1 - j], qb[j], acc1);
+          }
+        } else {
 #if WF_MOD_FFMA2
         float2 acc = make_float2(0.f, 0.f);
 #pragma unroll
@@ -482,9 +505,11 @@ cpm_modulate_f32s8_kernel(const __grid_constant__ ModParams<float> p) {
           acc1 = fmaf(wj, qb[j], acc1);
         }
 #endif
+        }
         const float old = (float)(int32_t)fp[i] * 1.4629180792671596e-09f;  // F[A-JT] in radians, [-pi, pi)
+        const float olda = ODD ? (float)(int32_t)fa[i] * 1.4629180792671596e-09f : old;
         float c0f, s0f, c1f, s1f;
-        __sincosf(acc0 + old, &s0f, &c0f);
+        __sincosf(acc0 + olda, &s0f, &c0f);
         __sincosf(acc1 + old, &s1f, &c1f);
         if (NOISE) {
           if ((i & 1) == 0) {
@@ -505,7 +530,8 @@ cpm_modulate_f32s8_kernel(const __grid_constant__ ModParams<float> p) {
           const u32x4 rr = philox4x32_10_rk(ctr, p.rk);
           const uint32_t wa = (i & 1) ? rr.z : rr.x, wb = (i & 1) ? rr.w : rr.y;
           if (((wa & 0xFFFFu) == 0u || (wb & 0xFFFFu) == 0u) && (unsigned)(n0 + 8 * i) < (unsigned)Ti)
-            o[4 * i] = mod_f32s8_slow_pair<JT>(p, wp + i, fp[i], rho, ctr, i & 1, ncoef);
+            o[4 * i] = mod_f32s8_slow_pair<JT>(p, (sha ? wp - 1 : wp) + i, wp + i, (sha ? fp - 1 : fp)[i], fp[i], qa0, qb0, ctr,
+                                               i & 1, ncoef);
         }
       }
     }
@@ -657,24 +683,26 @@ static int launch_modulate(const int8_t* d_syms, int64_t B, int64_t S, const dou
   const bool noise = d_sigma != nullptr;
   const dim3 grid((unsigned)B), block(kModThreads);
   const bool fast8 = (sps == 8) && (p.off % 2 == 0);
+  const bool fast8_odd = (sps == 8) && (p.off % 2 == 1) && p.J == 3;  // PCM/FM (K = 24)
 #define WF_MOD_LAUNCH(SPS_, JT_)                                                            \
   do {                                                                                      \
     if (noise) cpm_modulate_kernel<T, SPS_, JT_, true><<<grid, block, 0, stream>>>(p);     \
     else cpm_modulate_kernel<T, SPS_, JT_, false><<<grid, block, 0, stream>>>(p);          \
   } while (0)
-  if (sizeof(T) == 4 && fast8 && (p.J == 8 || p.J == 3 || p.J == 1) && (ld_out & 1) == 0 &&
+  if (sizeof(T) == 4 && ((fast8 && (p.J == 8 || p.J == 3 || p.J == 1)) || fast8_odd) && (ld_out & 1) == 0 &&
       (reinterpret_cast<uintptr_t>(d_out) & 15) == 0 && p.Tn < 0x7FFFF000) {
     const ModParams<float>& pf = reinterpret_cast<const ModParams<float>&>(p);  // T == float on this branch
-#define WF_MODF_LAUNCH(JT_, RUN_, MINB_)                                                                  \
-  do {                                                                                                   \
-    if (noise) cpm_modulate_f32s8_kernel<JT_, true, RUN_, MINB_><<<grid, block, kFSmemBytes, stream>>>(pf);  \
-    else cpm_modulate_f32s8_kernel<JT_, false, RUN_, MINB_><<<grid, block, kFSmemBytes, stream>>>(pf);       \
+#define WF_MODF_LAUNCH(JT_, RUN_, MINB_, ODD_)                                                                   \
+  do {                                                                                                          \
+    if (noise) cpm_modulate_f32s8_kernel<JT_, true, RUN_, MINB_, ODD_><<<grid, block, kFSmemBytes, stream>>>(pf);  \
+    else cpm_modulate_f32s8_kernel<JT_, false, RUN_, MINB_, ODD_><<<grid, block, kFSmemBytes, stream>>>(pf);       \
   } while (0)
     // RUN = 8 intervals per thread at 4 resident blocks/SM (64 registers) measured fastest on B200
     // among RUN in {4, 8, 16} x blocks/SM in {3, 4, 5} (profiles/r1f_kbench_mod_variants.log)
-    if (p.J == 8) WF_MODF_LAUNCH(8, 8, 4);
-    else if (p.J == 3) WF_MODF_LAUNCH(3, 8, 4);
-    else WF_MODF_LAUNCH(1, 8, 4);
+    if (fast8_odd) WF_MODF_LAUNCH(3, 8, 4, true);
+    else if (p.J == 8) WF_MODF_LAUNCH(8, 8, 4, false);
+    else if (p.J == 3) WF_MODF_LAUNCH(3, 8, 4, false);
+    else WF_MODF_LAUNCH(1, 8, 4, false);
 #undef WF_MODF_LAUNCH
     WF_LAUNCH_CHECK("cpm_modulate_f32s8_kernel");
     return WF_OK;
