@@ -203,7 +203,7 @@ WF_API int wf_bert(const uint8_t* d_dec_bits, const int8_t* d_dec_syms, int64_t 
 /* d_z complex[B][ld_z][n_h * M^Lp]: per detection step the bank outputs for every symbol
  * hypothesis (newest symbol most significant), one block of M^Lp per step parity i % n_h.
  * h = h_num[k % n_h] / p.  State count 2p * M^(Lp-1) <= 256; register-exchange survivors of
- * `depth` symbols (0 -> 64 / log2 M).  Outputs: d_dec_syms int8[B][n_steps] (alphabet values,
+ * `depth` symbols (0 -> min(32, 64 / log2 M)).  Outputs: d_dec_syms int8[B][n_steps] (alphabet values,
  * may be NULL) and, when d_tx_syms int8[B][S] is given, counters[point][3] += (bit errors,
  * symbol errors, compared symbols) over symbols [skip_head, min(S, n_steps) - skip_tail). */
 WF_API int wf_viterbi_cpm(const void* d_z, int dtype, int64_t B, int64_t n_steps, int64_t ld_z,

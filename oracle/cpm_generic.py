@@ -82,7 +82,7 @@ class CpmTrellis:
         flushed from the best final state.  All states start equal (unknown start)."""
         M, Lp, p2 = self.M, self.Lp, 2 * self.p
         bits = max(1, (M - 1).bit_length())
-        D = depth or (64 // bits)
+        D = depth or min(32, 64 // bits)
         n_steps = z.shape[0]
         NS, NH = self.n_states, self.n_hist
         pm = np.zeros(NS)

@@ -533,6 +533,32 @@ def test_generic_cpm_detector_vs_oracle(name, memory, pn15_stream):
     assert int(np.sum(dec32 != dec)) <= 2
 
 
+@pytest.mark.parametrize("depth", [5, 32, 33, 64])
+def test_pcmfm_detector_survivor_depths(depth, pn15_stream):
+    """The PCM/FM thread-per-frame kernel keeps 32-bit survivor words up to depth 32 and 64-bit words beyond:
+    both, and the float64 generic kernel, against the float64 statement at the same depth."""
+    from oracle.cpm_generic import CpmTrellis
+    from waveforms_b200.viterbi.cpm import CPMTrellisDetector
+
+    pf, hnum, p, M, mapper = _GEN["pcmfm"]
+    pulse = pf()
+    bits = cu(np.stack([pn15_stream[k * 700:k * 700 + 600] for k in range(3)]))
+    syms = mapper()(bits)
+    sg = torch.full((3,), float(o.sigma_from_ebn0_db(3.0, 8, 1)), dtype=torch.float32, device=DEV)
+    rx = wmod.modulate_frames(syms, np.array(hnum) / p, pulse, 8, dtype=torch.complex128, derotate=-np.pi / 4,
+                              sigma=sg, seed=11, first_frame=0)
+    det = CPMTrellisDetector(pulse, hnum, p, M, 8, memory=2, depth=depth)
+    S = syms.shape[1]
+    z = det.bank(rx, S)
+    dec64 = det.detect(z).cpu().numpy()
+    dec32 = det.detect(det.bank(rx.to(torch.complex64), S)).cpu().numpy()
+    tr = CpmTrellis(pulse, hnum, p, M, 8, 2)
+    for b in range(3):
+        ref = 2 * tr.detect(tr.bank(rx[b].cpu().numpy(), S), depth=depth).astype(np.int64) - 1
+        assert np.array_equal(dec64[b], ref), (depth, b)
+    assert int(np.sum(dec32 != dec64)) <= 2
+
+
 @pytest.mark.parametrize("name", ["pcmfm", "multih"])
 def test_generic_link_round_trip_and_waterfall(name):
     """BASELINE configs[1]/[2] at N = 4096: noiseless frames decode without error; BER falls

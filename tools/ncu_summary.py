@@ -49,6 +49,7 @@ def main():
     ap.add_argument("report")
     ap.add_argument("--tag", required=True)
     ap.add_argument("--frames", type=int, required=True, help="frames per launch in the captured run")
+    ap.add_argument("--no-traffic", action="store_true", help="summary only: leave profiles/traffic.json (the bench workload's) alone")
     a = ap.parse_args()
     raw = subprocess.run(["ncu", "-i", a.report, "--page", "raw", "--csv"], check=True, capture_output=True, text=True).stdout
     rows = list(csv.reader(io.StringIO(raw)))
@@ -72,8 +73,9 @@ def main():
                     tot += float(r[ix[m]]) * UNIT_SCALE[units[ix[m]]]
                 traffic[stage] = {"kernel": name.split("(")[0], "frames": a.frames, "dram_bytes_per_launch": tot,
                                   "source": f"profiles/{a.tag}_ncu_full_summary.csv (ncu --set full, one launch)"}
-    with open(os.path.join(ROOT, "profiles", "traffic.json"), "w") as f:
-        json.dump(traffic, f, indent=1)
+    if not a.no_traffic:
+        with open(os.path.join(ROOT, "profiles", "traffic.json"), "w") as f:
+            json.dump(traffic, f, indent=1)
     print(out)
     print(json.dumps(traffic, indent=1))
 

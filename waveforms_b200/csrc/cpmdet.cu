@@ -166,17 +166,19 @@ viterbi_cpm_kernel(const __grid_constant__ CpmParams p) {
 // ---------------------------------------------------------------------------
 constexpr int kM2Threads = 64;
 
-template <int P2, int D0, int D1>
-__global__ void __launch_bounds__(kM2Threads)
+// SV: survivor word, uint32_t when depth <= 32 (the default: half the shared memory -- 7 blocks per SM, so the
+// 1024 blocks of a 65 536-frame batch are ONE wave instead of 1.4 -- and half the select / shift work)
+template <int P2, int D0, int D1, typename SV>
+__global__ void __launch_bounds__(kM2Threads, sizeof(SV) == 4 ? 7 : 5)
 viterbi_cpm_m2l2_kernel(const __grid_constant__ CpmParams p, const __grid_constant__ CpmRot rot) {
   constexpr int NS = 2 * P2;
-  __shared__ unsigned long long sv_s[2][NS][kM2Threads];
+  __shared__ SV sv_s[2][NS][kM2Threads];
   const int tid = threadIdx.x;
   const int64_t frame = (int64_t)blockIdx.x * kM2Threads + tid;
   if (frame >= p.B) return;  // no barriers in this kernel: every thread is autonomous
 
   const int D = p.depth;
-  const unsigned long long hmask = (D >= 64) ? ~0ull : ((1ull << D) - 1ull);
+  const SV hmask = (D >= (int)(8 * sizeof(SV))) ? (SV)~(SV)0 : (SV)(((SV)1 << D) - (SV)1);
   const float4* zrow = reinterpret_cast<const float4*>(p.z) + frame * p.ld_z * 2;  // 4 complex64 = 2 float4 per step
   const int8_t* tx = p.tx_syms ? p.tx_syms + frame * p.S : nullptr;
   int8_t* out = p.dec_syms ? p.dec_syms + frame * p.n_steps : nullptr;
@@ -185,7 +187,7 @@ viterbi_cpm_m2l2_kernel(const __grid_constant__ CpmParams p, const __grid_consta
 
   float pm[NS], pn[NS];
 #pragma unroll
-  for (int s = 0; s < NS; ++s) { pm[s] = 0.f; sv_s[0][s][tid] = 0ull; }
+  for (int s = 0; s < NS; ++s) { pm[s] = 0.f; sv_s[0][s][tid] = (SV)0; }
 
   unsigned long long sym_err = 0, compared = 0;
   auto emit = [&](int64_t idx, unsigned v) {
@@ -203,8 +205,8 @@ viterbi_cpm_m2l2_kernel(const __grid_constant__ CpmParams p, const __grid_consta
   for (int64_t i = 0; i < n_steps; ++i) {
     const float zx[4] = {za.x, za.z, zb.x, zb.z}, zy[4] = {za.y, za.w, zb.y, zb.w};
     if (i + 1 < n_steps) { za = zrow[2 * (i + 1)]; zb = zrow[2 * (i + 1) + 1]; }  // next step's sector, a step ahead
-    const unsigned long long(*ho)[kM2Threads] = sv_s[cur];
-    unsigned long long(*hn)[kM2Threads] = sv_s[cur ^ 1];
+    const SV(*ho)[kM2Threads] = sv_s[cur];
+    SV(*hn)[kM2Threads] = sv_s[cur ^ 1];
 #pragma unroll
     for (int s = 0; s < NS; ++s) {
       constexpr int dummy = 0; (void)dummy;
@@ -217,8 +219,8 @@ viterbi_cpm_m2l2_kernel(const __grid_constant__ CpmParams p, const __grid_consta
       const float c1 = pm[pred1] + (rot.c[vp1] * zx[f1] + rot.s[vp1] * zy[f1]);
       const bool win1 = c1 > c0;
       pn[s] = win1 ? c1 : c0;
-      const unsigned long long h = win1 ? ho[pred1][tid] : ho[pred0][tid];
-      hn[s][tid] = ((h << 1) | (unsigned long long)hnew) & hmask;
+      const SV h = win1 ? ho[pred1][tid] : ho[pred0][tid];
+      hn[s][tid] = (SV)(((SV)(h << 1) | (SV)hnew) & hmask);
     }
     float wmax = pn[0];
 #pragma unroll
@@ -230,10 +232,10 @@ viterbi_cpm_m2l2_kernel(const __grid_constant__ CpmParams p, const __grid_consta
 #pragma unroll
     for (int s = 0; s < NS; ++s) pm[s] = pn[s] - wmax;
     cur ^= 1;
-    if (i >= D - 1) emit(i - D + 1, (unsigned)((sv_s[cur][best_s][tid] >> (D - 1)) & 1ull));
+    if (i >= D - 1) emit(i - D + 1, (unsigned)((sv_s[cur][best_s][tid] >> (D - 1)) & (SV)1));
     if (i == n_steps - 1) {  // flush the tail from the best final survivor
-      const unsigned long long h = sv_s[cur][best_s][tid];
-      for (int d = 0; d < D - 1 && d < n_steps; ++d) emit(n_steps - 1 - d, (unsigned)((h >> d) & 1ull));
+      const SV h = sv_s[cur][best_s][tid];
+      for (int d = 0; d < D - 1 && d < n_steps; ++d) emit(n_steps - 1 - d, (unsigned)((h >> d) & (SV)1));
     }
   }
   if (p.counters) {
@@ -425,7 +427,7 @@ extern "C" int wf_viterbi_cpm(const void* d_z, int dtype, int64_t B, int64_t n_s
   q.n_cols = n_h * q.n_filt;
   WF_REQUIRE(q.n_states <= kCpmMaxStates, "trellis has %d states (max %d)", q.n_states, kCpmMaxStates);
   WF_REQUIRE(q.n_cols <= kCpmMaxCols, "bank has %d outputs per step (max %d)", q.n_cols, kCpmMaxCols);
-  q.depth = depth > 0 ? depth : 64 / q.bits;
+  q.depth = depth > 0 ? depth : (64 / q.bits < 32 ? 64 / q.bits : 32);  // default: 32 symbols
   WF_REQUIRE(q.depth >= 1 && q.depth * q.bits <= 64, "survivor depth x bits/symbol exceeds 64");
   WF_REQUIRE(skip_head >= 0 && skip_tail >= 0, "negative skip");
   WF_REQUIRE(!d_tx_syms || d_counters, "error counting needs d_counters");
@@ -451,7 +453,8 @@ extern "C" int wf_viterbi_cpm(const void* d_z, int dtype, int64_t B, int64_t n_s
       rot.s[v] = (float)sin(M_PI * (double)v / (double)p);
     }
     const unsigned g = (unsigned)((B + kM2Threads - 1) / kM2Threads);
-    viterbi_cpm_m2l2_kernel<20, 13, 7><<<g, kM2Threads, 0, as_stream(stream)>>>(q, rot);
+    if (q.depth <= 32) viterbi_cpm_m2l2_kernel<20, 13, 7, uint32_t><<<g, kM2Threads, 0, as_stream(stream)>>>(q, rot);
+    else viterbi_cpm_m2l2_kernel<20, 13, 7, unsigned long long><<<g, kM2Threads, 0, as_stream(stream)>>>(q, rot);
     WF_LAUNCH_CHECK("viterbi_cpm_m2l2_kernel");
     return WF_OK;
   }

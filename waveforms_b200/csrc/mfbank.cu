@@ -185,6 +185,9 @@ mf_bank_kernel(const __grid_constant__ MfParams<T> p) {
   __syncthreads();  // every thread is done reading the rx tile; reuse it for the output
 
   // ---- combine + stage the output tile [SYM][n_out] ----------------------------------
+  // rows are `po` elements apart, po odd: a thread writes one row, so with an even n_out (32 for the
+  // multi-h bank: 256-byte thread stride) every lane of a store would land in the same bank pair
+  const int po = n_out | 1;
 #pragma unroll
   for (int e = 0; e < R; ++e) {
     const int s = R * tid + e;
@@ -200,19 +203,25 @@ mf_bank_kernel(const __grid_constant__ MfParams<T> p) {
           }
         }
         C z; z.x = zr; z.y = zi;
-        tile[s * n_out + r] = z;
+        tile[s * po + r] = z;
       }
     } else {
 #pragma unroll
       for (int f = 0; f < NFM; ++f) {
-        if (f < nf) { C z; z.x = yr[e][f]; z.y = yi[e][f]; tile[s * n_out + f] = z; }
+        if (f < nf) { C z; z.x = yr[e][f]; z.y = yi[e][f]; tile[s * po + f] = z; }
       }
     }
   }
   __syncthreads();
   C* out = reinterpret_cast<C*>(p.out) + (frame * p.ld_out + i0) * n_out;
   const int n_el = n_sym * n_out;
-  for (int k = tid; k < n_el; k += kMfThreads) out[k] = tile[k];
+  int row = tid / n_out, col = tid - row * n_out;
+  const int dr = kMfThreads / n_out, dc = kMfThreads - dr * n_out;
+  for (int k = tid; k < n_el; k += kMfThreads) {
+    out[k] = tile[row * po + col];
+    row += dr; col += dc;
+    if (col >= n_out) { col -= n_out; ++row; }
+  }
 }
 
 // ---------------------------------------------------------------------------
@@ -381,7 +390,7 @@ static size_t mf_smem_bytes(int sps, int nt, int R, int n_out, int& qs) {
   const int SYM = R * kMfThreads;
   qs = mf_qs(sps, nt, R);
   size_t in_bytes = (size_t)sps * R * qs * 2 * sizeof(T);
-  size_t out_bytes = (size_t)SYM * n_out * 2 * sizeof(T);
+  size_t out_bytes = (size_t)SYM * (n_out | 1) * 2 * sizeof(T);  // odd row pitch, see the kernel
   return in_bytes > out_bytes ? in_bytes : out_bytes;
 }
 
