@@ -246,6 +246,32 @@ viterbi_cpm_m2l2_kernel(const __grid_constant__ CpmParams p, const __grid_consta
   }
 }
 
+// warp-wide max / min in one instruction (CREDUX; sm_100a has the f32 form)
+__device__ __forceinline__ float warp_max_f32(float v) {
+#ifdef WF_HOSTEMU
+  for (int o = 16; o > 0; o >>= 1) {
+    const float t = __shfl_xor_sync(0xFFFFFFFFu, v, o);
+    v = t > v ? t : v;
+  }
+  return v;
+#else
+  float r;
+  asm volatile("redux.sync.max.f32 %0, %1, 0xffffffff;" : "=f"(r) : "f"(v));
+  return r;
+#endif
+}
+__device__ __forceinline__ int warp_min_s32(int v) {
+#ifdef WF_HOSTEMU
+  for (int o = 16; o > 0; o >>= 1) {
+    const int t = __shfl_xor_sync(0xFFFFFFFFu, v, o);
+    v = t < v ? t : v;
+  }
+  return v;
+#else
+  return __reduce_min_sync(0xFFFFFFFFu, v);
+#endif
+}
+
 // ---------------------------------------------------------------------------
 // Memory-2 trellises with 2p = 32 phase states (ARTM multi-h: M = 4, h = {4, 5}/16 -> 128 states):
 // one WARP per frame, lane = phase state v, the M history states of a lane in REGISTERS.
@@ -271,11 +297,12 @@ viterbi_cpm_lanev_kernel(const __grid_constant__ CpmParams p, const __grid_const
 
   const int D = p.depth;
   const unsigned long long hmask = (D * BITS >= 64) ? ~0ull : ((1ull << (D * BITS)) - 1ull);
-  const float2* zrow = reinterpret_cast<const float2*>(p.z) + frame * p.ld_z * p.n_cols;
+  const int n_cols = p.n_cols;
   const int8_t* tx = p.tx_syms ? p.tx_syms + frame * p.S : nullptr;
   int8_t* out = p.dec_syms ? p.dec_syms + frame * p.n_steps : nullptr;
-  const int64_t n_steps = p.n_steps;
-  const int64_t cmp_lo = p.skip_head, cmp_hi = min(p.S, n_steps) - p.skip_tail;
+  const int n_steps = (int)p.n_steps, S = (int)p.S;  // < 2^31 (checked by the launcher): 32-bit index arithmetic
+  const int cmp_lo = (int)p.skip_head, cmp_hi = min(S, n_steps) - (int)p.skip_tail;
+  const int sh_old = (D - 1) * BITS;  // position of the oldest symbol of a survivor word
 
   // per-lane transition tables for each modulation-index parity
   int src[NHH][M];
@@ -299,48 +326,55 @@ viterbi_cpm_lanev_kernel(const __grid_constant__ CpmParams p, const __grid_const
 #pragma unroll
   for (int h = 0; h < M; ++h) { pm[h] = 0.f; sv[h] = 0ull; }
 
-  unsigned long long sym_err = 0, bit_err = 0, compared = 0;  // lane 0
-  int tx_reg = 0;                                              // tx[32 g + lane] of the current group g
-  auto emit = [&](int64_t idx, unsigned v) {                   // executed by every lane (shuffle inside); lane 0 counts
-    if ((idx & 31) == 0 || idx == cmp_lo) {                    // (re)load the group of 32 transmitted symbols
-      const int64_t k = (idx & ~(int64_t)31) + lane;
-      tx_reg = (tx && k < p.S) ? (int)tx[k] : 0;
-    }
-    const int t_sym = __shfl_sync(0xFFFFFFFFu, tx_reg, (int)(idx & 31));
-    if (lane == 0) {
-      if (out) out[idx] = (int8_t)(2 * (int)v - (M - 1));
-      if (tx && idx >= cmp_lo && idx < cmp_hi) {
-        const unsigned t = (unsigned)((t_sym + (M - 1)) >> 1);
-        sym_err += (t != v) ? 1u : 0u;
-        bit_err += __popc((t ^ v) & (unsigned)(M - 1));
+  // Decisions come out in ascending order, one per step: lane (idx mod 32) keeps decision idx, and once
+  // a group of 32 is complete every lane stores / compares ITS symbol (one coalesced 32-byte store and
+  // one 32-byte load per 32 steps; no per-step divergent branch, byte store or shuffle).
+  unsigned sym_err = 0, bit_err = 0, compared = 0;  // per lane, reduced at the end
+  unsigned dec_reg = 0;
+  auto flush_group = [&](int last_idx) {  // decisions (last_idx & ~31) .. last_idx are in the lanes' dec_reg
+    const int k = (last_idx & ~31) + lane;
+    if (k <= last_idx) {
+      if (out) out[k] = (int8_t)(2 * (int)dec_reg - (M - 1));
+      if (tx && k >= cmp_lo && k < cmp_hi) {
+        const unsigned t = (unsigned)(((int)tx[k] + (M - 1)) >> 1);
+        sym_err += (t != dec_reg) ? 1u : 0u;
+        bit_err += __popc((t ^ dec_reg) & (unsigned)(M - 1));
         ++compared;
       }
     }
   };
-
-  auto stage = [&](int64_t i) {  // 16 bytes per lane: NF complex64 = NF/2 lanes
-    if (i < n_steps && lane < NF / 2) {
-      const int par = (int)(i % NHH);
-      cp_async_cg16(&z_s[wid][i % kLvRing][2 * lane], zrow + i * p.n_cols + par * NF + 2 * lane);
-    }
-    cp_async_commit();
+  auto emit = [&](int idx, unsigned v) {  // executed by every lane with the same (idx, v)
+    dec_reg = (lane == (idx & 31)) ? v : dec_reg;
+    if ((idx & 31) == 31 || idx == n_steps - 1) flush_group(idx);
   };
-  for (int k = 0; k < kLvRing - 1; ++k) stage(k);
 
-  bool tx_loaded = false;
-  for (int64_t i0 = 0; i0 < n_steps; i0 += NHH) {
+  // bank outputs of step j: NF complex64 at column (j mod NHH) NF of row j; 16 bytes per lane, NF/2 lanes
+  const float2* zst = reinterpret_cast<const float2*>(p.z) + frame * p.ld_z * n_cols + 2 * lane;
+  float2* zdst = &z_s[wid][0][2 * lane];
+  int st_j = 0;  // next step to stage
+  auto stage = [&](int par) {
+    if (st_j < n_steps && lane < NF / 2) cp_async_cg16(zdst + (st_j & (kLvRing - 1)) * NF, zst + par * NF);
+    cp_async_commit();
+    zst += n_cols;
+    ++st_j;
+  };
+  static_assert((kLvRing & (kLvRing - 1)) == 0 && kLvRing % NHH == 0, "ring slots: power of two, multiple of the h period");
+#pragma unroll
+  for (int k = 0; k < kLvRing - 1; ++k) stage(k % NHH);
+
+  for (int i0 = 0; i0 < n_steps; i0 += NHH) {
 #pragma unroll
     for (int hp = 0; hp < NHH; ++hp) {
-      const int64_t i = i0 + hp;
+      const int i = i0 + hp;
       if (i >= n_steps) break;
       // parity of the filters is i % NHH = hp (i0 is a multiple of NHH); of the transition (i - Lp + 1) % NHH
       constexpr int dummy = 0; (void)dummy;
       const int lp = (hp + NHH - 1) % NHH;
       __syncwarp();              // every lane has finished reading the slot that is staged next
-      stage(i + kLvRing - 1);
+      stage((hp + kLvRing - 1) % NHH);
       cp_async_wait<kLvRing - 1>();
       __syncwarp();              // the step's bank outputs are visible to all lanes
-      const float4* zq = reinterpret_cast<const float4*>(z_s[wid][i % kLvRing]);
+      const float4* zq = reinterpret_cast<const float4*>(z_s[wid][i & (kLvRing - 1)]);
       float pmx[M];
       unsigned long long svx[M];
 #pragma unroll
@@ -366,12 +400,7 @@ viterbi_cpm_lanev_kernel(const __grid_constant__ CpmParams p, const __grid_const
         sv[hn] = ((bsv << BITS) | (unsigned long long)hn) & hmask;
         lmax = best > lmax ? best : lmax;
       }
-      float wmax = lmax;
-#pragma unroll
-      for (int o = 16; o > 0; o >>= 1) {
-        const float t = __shfl_xor_sync(0xFFFFFFFFu, wmax, o);
-        wmax = t > wmax ? t : wmax;
-      }
+      const float wmax = warp_max_f32(lmax);
       int best_s = 0x7FFFFFFF;  // lowest state index v M + h with the maximum metric
       unsigned long long my_sv = 0ull;
 #pragma unroll
@@ -379,27 +408,28 @@ viterbi_cpm_lanev_kernel(const __grid_constant__ CpmParams p, const __grid_const
         if (pm[hn] == wmax) { best_s = lane * M + hn; my_sv = sv[hn]; }
         pm[hn] -= wmax;
       }
-      int wbest = best_s;
-#pragma unroll
-      for (int o = 16; o > 0; o >>= 1) {
-        const int t = __shfl_xor_sync(0xFFFFFFFFu, wbest, o);
-        wbest = t < wbest ? t : wbest;
-      }
+      const int wbest = warp_min_s32(best_s);
       if (i >= D - 1 || i == n_steps - 1) {
         const unsigned long long h = __shfl_sync(0xFFFFFFFFu, my_sv, wbest / M);  // the best lane's lowest-h survivor
-        if (i >= D - 1) emit(i - D + 1, (unsigned)((h >> ((D - 1) * BITS)) & (unsigned)(M - 1)));
+        if (i >= D - 1) emit(i - D + 1, (unsigned)(h >> sh_old) & (unsigned)(M - 1));
         if (i == n_steps - 1)  // flush the tail from the best final survivor
-          for (int d = D - 2 < n_steps - 1 ? D - 2 : (int)(n_steps - 1); d >= 0; --d)
-            emit(n_steps - 1 - d, (unsigned)((h >> (d * BITS)) & (unsigned)(M - 1)));
+          for (int d = D - 2 < n_steps - 1 ? D - 2 : n_steps - 1; d >= 0; --d)
+            emit(n_steps - 1 - d, (unsigned)(h >> (d * BITS)) & (unsigned)(M - 1));
       }
     }
   }
-  (void)tx_loaded;
+  // per-lane counts -> lane 0
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    sym_err += __shfl_xor_sync(0xFFFFFFFFu, sym_err, o);
+    bit_err += __shfl_xor_sync(0xFFFFFFFFu, bit_err, o);
+    compared += __shfl_xor_sync(0xFFFFFFFFu, compared, o);
+  }
   if (lane == 0 && p.counters) {
     const int64_t pt = p.point ? p.point[frame] : 0;
-    atomicAdd(&p.counters[3 * pt + 0], bit_err);
-    atomicAdd(&p.counters[3 * pt + 1], sym_err);
-    atomicAdd(&p.counters[3 * pt + 2], compared);
+    atomicAdd(&p.counters[3 * pt + 0], (unsigned long long)bit_err);
+    atomicAdd(&p.counters[3 * pt + 1], (unsigned long long)sym_err);
+    atomicAdd(&p.counters[3 * pt + 2], (unsigned long long)compared);
   }
 }
 
@@ -459,7 +489,7 @@ extern "C" int wf_viterbi_cpm(const void* d_z, int dtype, int64_t B, int64_t n_s
     return WF_OK;
   }
   // memory-2 trellis with 32 phase states (ARTM multi-h): lane-per-phase-state register kernel
-  if (dtype == WF_F32 && M == 4 && Lp == 2 && p == 16 && n_h == 2 && q.depth * q.bits <= 64 &&
+  if (dtype == WF_F32 && M == 4 && Lp == 2 && p == 16 && n_h == 2 && q.depth * q.bits <= 64 && n_steps < 0x7FFFFF00 && S < 0x7FFFFF00 &&
       (reinterpret_cast<uintptr_t>(d_z) & 15) == 0) {
     CpmRot rot;
     for (int v = 0; v < 2 * p; ++v) {
