@@ -464,6 +464,25 @@ static int launch_mf(const void* d_rx, int64_t B, int64_t Tn, int64_t ld_rx, con
       else if (sps == 10 && n_filt == 3 && n_taps == 11 && !real_taps) WF_MFT_CASE(10, 3, 11, true, 4);
       else if (sps == 8 && n_filt == 4 && n_taps == 8 && !real_taps && !comb_re) WF_MFT_CASE(8, 4, 8, true, 4);  // PCM/FM, Lp = 2
     }
+    // Odd tile origin (IRIG PCM/FM: first instant -1): one zero tap in front of every filter moves the origin
+    // one sample back to an even index -- same sums, 9/8 of the FFMAs, but the 16-byte cp.async staging applies.
+    const bool odd_ok = (((first_instant + center - n_taps) & 1) == 0) && ((ld_rx & 1) == 0) &&
+                        ((reinterpret_cast<uintptr_t>(d_rx) & 15) == 0) && Tn < 0x7FFFFFF0 && n_calls < 0x7FFFFFF0 &&
+                        first_instant < 0x7FFFFFF0;
+    if (odd_ok && sps == 8 && n_filt == 4 && n_taps == 8 && !real_taps && !comb_re) {
+      double pad_re[4 * 9], pad_im[4 * 9];
+      for (int f = 0; f < 4; ++f)
+        for (int t = 0; t < 9; ++t) {  // tap index NT-1 multiplies the OLDEST sample of the window
+          pad_re[f * 9 + t] = t < 8 ? taps_re[f * 8 + t] : 0.0;
+          pad_im[f * 9 + t] = t < 8 ? taps_im[f * 8 + t] : 0.0;
+        }
+      {
+        const double* taps_re = pad_re;  // the macro reads these names
+        const double* taps_im = pad_im;
+        p.n_taps = 9;
+        WF_MFT_CASE(8, 4, 9, true, 4);
+      }
+    }
 #undef WF_MFT_CASE
   }
   if (sps == 8 && n_filt == 2 && n_taps == 73 && real_taps) WF_MF_CASE(8, 2, 73, false, 2);       // PAM bank, TG
