@@ -31,12 +31,16 @@ METRIC = "viterbi_decoded_bits_per_s_soqpsk_tg"
 # bank's two raw filter outputs between bank and detector (16 B per call), so the
 # bank moves 64 + 16 and the detector 16 + 1/8 bytes per bit (SURVEY's reference-shaped [calls, 3]
 # array would be 64 + 24 and 24 + 1/8).
-ALGO_BYTES_PER_BIT = {"prbs_encode": 1.125, "modulate_awgn": 65.0, "mf_bank": 80.0, "viterbi_bert": 16.125}
-KERNELS = list(ALGO_BYTES_PER_BIT)
+# The fused modulate+AWGN+bank kernel (wf_cpm_modulate_bank, the default link) reads 1 B and writes the
+# 16 B of raw bank outputs per bit: the 64 B/bit baseband stays in shared memory.
+ALGO_BYTES_PER_BIT = {"prbs_encode": 1.125, "modulate_awgn": 65.0, "mf_bank": 80.0, "viterbi_bert": 16.125,
+                      "modulate_awgn_bank": 17.0}
 # what ncu shows each stage is limited by (profiles/*_ncu_full_summary.csv)
 BOUND = {"prbs_encode": "alu pipe (integer LFSR / precoder work, ~1 B/bit of HBM)",
          "modulate_awgn": "xu pipe + issue (12 MUFU per sample pair: sin/cos of the signal, Box-Muller); HBM write 62 %",
          "mf_bank": "hbm",
+         "modulate_awgn_bank": "xu pipe + issue (the modulator's MUFU / Philox work plus the bank's FFMA2 loop from shared "
+                               "memory); HBM traffic is 17 B/bit, far from the HBM roof by construction",
          "viterbi_bert": "issue / alu pipe (add-compare-select recursion, one thread per frame)"}
 
 
@@ -45,7 +49,8 @@ def workload_config(frames, n_gpus):
                         f"Eb/N0 {EBN0_DB} dB, {DETECTOR} bank, length-2 trellis detector (BASELINE configs[4])",
             "frames_per_gpu": frames, "n_bits": N_BITS, "sps": SPS, "ebn0_db": EBN0_DB, "detector": DETECTOR,
             "parallelism": f"frames sharded over {n_gpus} GPU(s), counter all-reduce only",
-            "l2_policy": "per-step working set (rx+z, ~24 GB at 65536 frames) is far larger than the 126 MB L2"}
+            "l2_policy": "per-step working set (z + symbols, ~4.6 GB at 65536 frames; ~24 GB with --unfused) is far larger "
+                         "than the 126 MB L2"}
 
 
 def peaks():
@@ -142,6 +147,7 @@ def main():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--frames", type=int, default=FRAMES_PER_GPU, help="frames per GPU per step")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--fused", action="store_true", help="fused modulate+AWGN+bank kernel (baseband stays in shared memory) instead of the four-kernel link")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -183,7 +189,10 @@ def main():
         torch.cuda.synchronize(dev)
 
     B, K, W = args.frames, args.steps, max(args.warmup, 3)
-    sim = LinkSimulator(LinkConfig(n_bits=N_BITS, sps=SPS, detector=DETECTOR), device=dev, max_batch=B)
+    sim = LinkSimulator(LinkConfig(n_bits=N_BITS, sps=SPS, detector=DETECTOR, extra={"fused": args.fused}),
+                        device=dev, max_batch=B)
+    KERNELS = list(sim.stage_names)
+    NK = len(KERNELS)
     sigma = torch.full((B,), float(sigma_from_ebn0_db(EBN0_DB, SPS)), dtype=torch.float32, device=dev)
     point = torch.zeros((B,), dtype=torch.int32, device=dev)
     counters = torch.zeros((1, 3), dtype=torch.int64, device=dev)
@@ -213,8 +222,8 @@ def main():
         dist.all_reduce(counters, op=dist.ReduceOp.SUM)  # the path's one collective
     elapsed_ms = float(t.item())
     bit_err, _, compared = counters[0].tolist()
-    per_kernel_ms = [statistics.fmean(events[5 * s + k].elapsed_time(events[5 * s + k + 1]) for s in range(K))
-                     for k in range(4)]
+    per_kernel_ms = [statistics.fmean(events[(NK + 1) * s + k].elapsed_time(events[(NK + 1) * s + k + 1]) for s in range(K))
+                     for k in range(NK)]
 
     # ---------------- end-to-end loop through the public host call: `e2e` ---------------------
     for s in range(2):
@@ -234,7 +243,7 @@ def main():
         bits_per_step = world * B * N_BITS
         value = bits_per_step * K / (elapsed_ms * 1e-3)
         peak, peak_src = peaks()
-        dom = max(range(4), key=lambda k: per_kernel_ms[k])
+        dom = max(range(NK), key=lambda k: per_kernel_ms[k])
         name = KERNELS[dom]
         algo_bytes = ALGO_BYTES_PER_BIT[name] * B * N_BITS
         achieved = algo_bytes / (per_kernel_ms[dom] * 1e-3) / 1e9
@@ -259,13 +268,14 @@ def main():
                     "d2h_bytes_per_step": int(host_counts.nbytes)},
             "roofline": {"bound": "hbm", "kernel": name, "achieved": achieved, "peak": peak, "unit": "GB/s",
                          "frac": achieved / peak, "traffic": traffic, "peak_source": peak_src,
-                         "algorithmic_bytes_per_bit": ALGO_BYTES_PER_BIT[name]},
+                         "algorithmic_bytes_per_bit": ALGO_BYTES_PER_BIT[name], "binding_resource": BOUND[name]},
+            "link": "fused (prbs | modulate+awgn+bank | viterbi+bert)" if sim.fused else "four kernels",
             "kernels": {KERNELS[k]: {"ms": per_kernel_ms[k],
                                      "algo_gbs": ALGO_BYTES_PER_BIT[KERNELS[k]] * B * N_BITS / (per_kernel_ms[k] * 1e-3) / 1e9,
                                      "hbm_frac": ALGO_BYTES_PER_BIT[KERNELS[k]] * B * N_BITS / (per_kernel_ms[k] * 1e-3) / 1e9 / peak,
                                      "algorithmic_bytes": ALGO_BYTES_PER_BIT[KERNELS[k]] * B * N_BITS,
                                      "traffic": traffic_of(KERNELS[k]), "bound": BOUND[KERNELS[k]],
-                                     "share": per_kernel_ms[k] / sum(per_kernel_ms)} for k in range(4)},
+                                     "share": per_kernel_ms[k] / sum(per_kernel_ms)} for k in range(NK)},
             "clocks": clocks,
             "ber": {"ebn0_db": EBN0_DB, "bit_errors": bit_err, "compared": compared,
                     "ber": bit_err / compared if compared else None},

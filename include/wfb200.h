@@ -117,6 +117,25 @@ WF_API int wf_cpm_modulate(const int8_t* d_syms, int64_t B, int64_t S,
                     const float* d_sigma, const int32_t* d_point,
                     uint64_t seed, uint64_t first_frame, void* stream);
 
+/* Fused cpm_modulate -> + AWGN -> decimated real-tap bank (examples/soqpsk_detection.py:78-90 followed by
+ * the PAM bank of :158-173) in ONE kernel: the noisy baseband stays in shared memory, only the bank's
+ * raw filter outputs d_z complex64[B][ld_z][n_filt] reach HBM (same values, bit for bit, as
+ * wf_cpm_modulate(.., WF_F32, ..) followed by wf_mf_bank(.., combine = NULL, ..) on the same arguments).
+ * Built for the SOQPSK-TG shape only: sps 8, pulse with ceil((K-1)/8) == 8 and ((K-1)/2) % 8 == 0,
+ * n_filt == 2 real filters of n_taps == 73; wf_cpm_modulate_bank_supported() says whether a shape is
+ * covered (1) or not (0); uncovered shapes return WF_ERR_UNSUPPORTED and the caller runs the two calls. */
+WF_API int wf_cpm_modulate_bank_supported(int K, int sps, int n_filt, int n_taps, int center,
+                                          int64_t first_instant, int64_t S, int64_t n_calls);
+WF_API int wf_cpm_modulate_bank(const int8_t* d_syms, int64_t B, int64_t S,
+                    const double* mod_index, int n_h,
+                    const double* pulse, int K, int sps,
+                    double initial_phase, double derotate,
+                    const float* d_sigma, const int32_t* d_point,
+                    uint64_t seed, uint64_t first_frame,
+                    const double* taps_re, int n_filt, int n_taps, int center,
+                    int64_t first_instant, int64_t n_calls,
+                    void* d_z, int64_t ld_z, void* stream);
+
 /* frequency_modulate(freq_pulses, sps, initial_phase) (cpm/modulate.py:28-54) for B rows
  * of arbitrary per-sample frequency pulses d_freq double[B][ld_in]:
  * out[n] = exp(j(((sum_{m<=n} f[m]) mod sps) * 2pi/sps + initial_phase)). */

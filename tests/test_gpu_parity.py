@@ -423,6 +423,49 @@ def test_raw_bank_detection_equals_combined_bank_detection():
     assert ca[:, 2].min() == 200 * 2045 and ca[0, 0] > ca[2, 0] > 0
 
 
+@pytest.mark.parametrize("n_bits", [4096, 1024, 511, 520, 96, 5117, 7000, 10240])
+def test_fused_modulate_bank_is_bit_identical_to_the_two_kernel_path(n_bits):
+    """wf_cpm_modulate_bank keeps the noisy baseband in shared memory; its bank outputs must equal
+    wf_cpm_modulate + wf_mf_bank bit for bit (same samples, same FFMA2 order), at frame lengths that end
+    inside a chunk, on a chunk boundary, and in a second scan segment (> 5120 symbols), with per-frame
+    noise levels from 0 (noiseless) to 0 dB.  Counters then agree trivially."""
+    B = 24
+    a = LinkSimulator(LinkConfig(detector="PAM", n_bits=n_bits, extra={"fused": True}), device=DEV, max_batch=B)
+    b = LinkSimulator(LinkConfig(detector="PAM", n_bits=n_bits, extra={"fused": False}), device=DEV, max_batch=B)
+    assert a.fused and a.rx is None and not b.fused and len(a.stage_names) == 3
+    sg = torch.linspace(0.0, 2.0, B, dtype=torch.float32, device=DEV)
+    sg[0] = 0.0
+    pt = torch.zeros(B, dtype=torch.int32, device=DEV)
+    ca = torch.zeros((1, 3), dtype=torch.int64, device=DEV)
+    cb = torch.zeros((1, 3), dtype=torch.int64, device=DEV)
+    a.z.fill_(float("nan")); b.z.fill_(float("nan"))
+    a.run_batch(12345, sg, pt, ca)
+    b.run_batch(12345, sg, pt, cb)
+    za = torch.view_as_real(a.z[:, :a.n_calls]).contiguous().view(torch.int32)
+    zb = torch.view_as_real(b.z[:, :b.n_calls]).contiguous().view(torch.int32)
+    assert a.n_calls == b.n_calls and torch.equal(za, zb), int((za != zb).sum())
+    assert torch.equal(ca, cb) and int(ca[0, 2]) == B * a.n_compared
+
+
+def test_fused_link_covers_soqpsk_tg_and_other_shapes_fall_back_to_four_kernels():
+    assert LinkSimulator(LinkConfig(extra={"fused": True}), device=DEV, max_batch=4).fused
+    assert not LinkSimulator(LinkConfig(), device=DEV, max_batch=4).fused
+    for kw in ({"waveform": "soqpsk-mil"}, {"detector": "PT"}, {"sps": 10}, {"timing_offset": 3},
+               {"waveform": "pcmfm"}, {"extra": {"combine_in_bank": True}}):
+        kw = {**kw, "extra": {**kw.get("extra", {}), "fused": True}}
+        sim = LinkSimulator(LinkConfig(n_bits=256, **kw), device=DEV, max_batch=4)
+        if sim.fused:  # a covered shape must still equal the two-kernel path
+            ref = LinkSimulator(LinkConfig(n_bits=256, **{**kw, "extra": {**kw["extra"], "fused": False}}), device=DEV,
+                                max_batch=4)
+            e = [3.0]
+            assert np.array_equal(sim.run(e, 4), ref.run(e, 4)), kw
+        else:
+            assert len(sim.stage_names) == 4, kw
+    rc = _ffi.lib().wf_cpm_modulate_bank(None, 1, 16, None, 1, None, 9, 8, 0.0, 0.0, None, None, 0, 0, None, 2, 73, 36, 0,
+                                         15, None, 16, None)
+    assert rc < 0  # bad arguments are refused, not run
+
+
 def test_link_matches_oracle_chain_with_philox_noise():
     """Same Philox noise through the CUDA chain and through the float64 oracle chain."""
     cfg = LinkConfig(n_bits=1024, detector="PAM")

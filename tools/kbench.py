@@ -19,7 +19,8 @@ import torch  # noqa: E402
 
 from waveforms_b200.linksim import LinkConfig, LinkSimulator  # noqa: E402
 
-BYTES = {"prbs_encode": 1.125, "modulate_awgn": 65.0, "mf_bank": 80.0, "viterbi_bert": 16.125}  # PAM raw-bank link (bench.py)
+BYTES = {"prbs_encode": 1.125, "modulate_awgn": 65.0, "mf_bank": 80.0, "viterbi_bert": 16.125,  # PAM raw-bank link (bench.py)
+         "modulate_awgn_bank": 17.0}
 
 
 def measure(sim, B, reps, cfg):
@@ -30,12 +31,12 @@ def measure(sim, B, reps, cfg):
     for _ in range(2):
         sim.run_batch(0, sg, None, counters)
     torch.cuda.synchronize(dev)
-    tot = dict.fromkeys(BYTES, 0.0)
+    tot = dict.fromkeys(sim.stage_names, 0.0)
     for r in range(reps):
         ev = []
         sim.run_batch(r * B, sg, None, counters, events=ev)
         torch.cuda.synchronize(dev)
-        for k, name in enumerate(BYTES):
+        for k, name in enumerate(sim.stage_names):
             tot[name] += ev[k].elapsed_time(ev[k + 1])
     bits = B * cfg.n_bits
     out = {}
@@ -56,8 +57,9 @@ def main():
     ap.add_argument("--detector", default="PAM")
     ap.add_argument("--waveform", default="soqpsk-tg", help="LinkConfig.waveform (algo_gbs figures are SOQPSK/PAM bytes)")
     ap.add_argument("--env", default=None)
+    ap.add_argument("--fused", action="store_true")
     a = ap.parse_args()
-    cfg = LinkConfig(n_bits=4096, detector=a.detector, waveform=a.waveform)
+    cfg = LinkConfig(n_bits=4096, detector=a.detector, waveform=a.waveform, extra={"fused": a.fused})
     sim = LinkSimulator(cfg, device=torch.device("cuda", 0), max_batch=a.frames)
     if a.env:
         name, vals = a.env.split("=")

@@ -28,6 +28,9 @@ PROTOTYPES = {
     "wf_trellis_encode": (_i32, [_vp, _i64, _i64, _vp, _vp, _i32, _i32, _i32, _vp, _vp, _vp]),
     "wf_cpm_modulate": (_i32, [_vp, _i64, _i64, _vp, _i32, _vp, _i32, _i32, _dbl, _dbl, _i32, _vp, _i64,
                                _vp, _vp, _u64, _u64, _vp]),
+    "wf_cpm_modulate_bank_supported": (_i32, [_i32, _i32, _i32, _i32, _i32, _i64, _i64, _i64]),
+    "wf_cpm_modulate_bank": (_i32, [_vp, _i64, _i64, _vp, _i32, _vp, _i32, _i32, _dbl, _dbl, _vp, _vp, _u64, _u64,
+                                    _vp, _i32, _i32, _i32, _i64, _i64, _vp, _i64, _vp]),
     "wf_frequency_modulate": (_i32, [_vp, _i64, _i64, _i64, _i32, _dbl, _i32, _vp, _i64, _vp]),
     "wf_phase_modulate": (_i32, [_vp, _i64, _dbl, _i32, _vp, _vp]),
     "wf_awgn_add": (_i32, [_vp, _i32, _i64, _i64, _i64, _vp, _vp, _u64, _u64, _vp]),

@@ -48,6 +48,17 @@ def _fingerprint() -> str:
     return h.hexdigest()
 
 
+def _object_fingerprint(src: str) -> str:
+    h = hashlib.sha256()
+    h.update(" ".join(NVCC_FLAGS).encode())
+    headers = [os.path.join(CSRC, n) for n in sorted(os.listdir(CSRC)) if n.endswith((".cuh", ".h"))]
+    for path in [src, *headers, os.path.join(HERE, "..", "include", "wfb200.h")]:
+        h.update(os.path.basename(path).encode())
+        with open(path, "rb") as f:
+            h.update(f.read())
+    return h.hexdigest()
+
+
 def sources() -> list[str]:
     return [os.path.join(CSRC, s) for s in SOURCES if os.path.exists(os.path.join(CSRC, s))]
 
@@ -61,15 +72,24 @@ def build(force: bool = False, verbose: bool = False) -> str:
     nvcc = _nvcc()
     objs = []
     procs = []
+    stamps = []
     for src in sources():
         obj = os.path.join(OUT_DIR, os.path.basename(src)[:-3] + ".o")
+        objs.append(obj)
+        # per-object stamp: a source is recompiled only when it, a header or the flags changed
+        ofp = _object_fingerprint(src)
+        ostamp = obj + ".stamp"
+        if not force and os.path.exists(obj) and os.path.exists(ostamp) and open(ostamp).read().strip() == ofp:
+            continue
+        if os.path.exists(ostamp):
+            os.remove(ostamp)
+        stamps.append((ostamp, ofp))
         cmd = [nvcc, *NVCC_FLAGS, "-c", src, "-o", obj]
         if verbose:
             cmd.insert(1, "-Xptxas")
             cmd.insert(2, "-v")
             print(" ".join(cmd), file=sys.stderr)
         procs.append((src, subprocess.Popen(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)))
-        objs.append(obj)
     failed = False
     for src, pr in procs:
         out, _ = pr.communicate()
@@ -80,6 +100,9 @@ def build(force: bool = False, verbose: bool = False) -> str:
             sys.stderr.write(out)
     if failed:
         raise RuntimeError("nvcc compilation failed")
+    for ostamp, ofp in stamps:
+        with open(ostamp, "w") as f:
+            f.write(ofp)
     cmd = [nvcc, "-shared", "-cudart", "static", "-gencode", "arch=compute_100a,code=sm_100a", "-o", LIB, *objs]
     r = subprocess.run(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)
     if r.returncode != 0:

@@ -14,6 +14,8 @@
 #include "common.cuh"
 #include <math.h>
 #include <string.h>
+#include <stdlib.h>
+#include <type_traits>
 
 #ifndef WF_MOD_FFMA2
 #define WF_MOD_FFMA2 1
@@ -262,6 +264,120 @@ constexpr int kFLB = 16;                      // look-back slots in front of a s
 constexpr int kFSlots = kFLB + kFSeg + 8;     // + spill of the lanes that start one interval late
 constexpr size_t kFSmemBytes = (size_t)kFSlots * 8;
 
+// ---------------------------------------------------------------------------
+// Fused modulate -> AWGN -> PAM bank (wf_cpm_modulate_bank): the fast kernel below with FUSE = true
+// never writes the noisy baseband to HBM.  A chunk of 512 symbol intervals (4096 samples) lands in a
+// shared-memory tile laid out exactly like mf_bank_f32_kernel's (mfbank.cu: natural sample order, one
+// 16-byte pad after every 32 samples, so the bank's per-thread 128-bit loads are conflict free), one
+// barrier, warps 0-3 then run the bank's R = 4 calls-per-thread FFMA2 loop over the tile -- SAME
+// operation order as mf_bank_f32_kernel, so the filter outputs are bit-identical to the two-kernel
+// path -- and store 16 bytes per call (two raw PAM filter outputs); warps 4-7 carry the newest LB
+// samples to the front of the tile for the next chunk.  Chunk j' (intervals 512 j' ..) completes calls
+// [512 j' - CB, 512 (j'+1) - CB); the tile origin is the first sample of call 512 j' - CB's window.
+// HBM per bit: 1 B in + 16 B out instead of 65 + 80.
+// ---------------------------------------------------------------------------
+constexpr int kFzNT = 73, kFzNF = 2, kFzR = 4;   // PAM bank of SOQPSK-TG at sps 8 (mfbank.cu WF_MFT_CASE(8, 2, 73, false, 4))
+constexpr int kFzThreads = 128;                   // threads that run the bank phase: 4 x 128 = 512 calls per chunk
+constexpr int kFzChunk = kFzR * kFzThreads;       // calls per chunk == intervals per chunk
+constexpr int kFzLBMax = 96;                      // look-back samples kept from the previous chunk
+constexpr int kFzSlots = 4464;                    // pos(8 * kFzChunk + kFzLBMax) rounded up
+constexpr size_t fz_smem_bytes(int fseg) { return (size_t)(kFLB + fseg + 8) * 8 + (size_t)kFzSlots * 8; }
+__host__ __device__ constexpr int fz_pos(int m) { return m + 2 * (m >> 5); }
+
+struct FuseParams {
+  float2* z;            // [B][ld_z][2] raw outputs of the two real-tap filters
+  int64_t ld_z;
+  int n_calls, CB, LB;
+  int n_sm, stagger;    // first-wave blocks of residency slot k = (blockIdx / n_sm) & 3 start k * stagger cycles late
+  alignas(16) float tap2[2 * kFzNF * kFzNT];  // (t, t) pairs, filter-major: 64-bit uniform operands of the packed FFMA2
+};
+struct FuseNone { int unused; };
+
+// R = 4 consecutive calls of thread t, BOTH filters (warps 0-3 only); mirrors mf_bank_f32_kernel<8, 2, 73, false, 4>.
+static __device__ __forceinline__ void fz_bank_phase2(const FuseParams& fz, const float2* tile, int t, int cbase, float2* zrow) {
+  const int c0 = cbase + kFzR * t;
+  if (c0 + kFzR - 1 < 0 || c0 >= fz.n_calls) return;
+  constexpr int NV = (kFzR - 1) * 8 + kFzNT;
+  const float2* tap2 = reinterpret_cast<const float2*>(fz.tap2);
+  float2 y[kFzR][kFzNF];
+#pragma unroll
+  for (int e = 0; e < kFzR; ++e)
+#pragma unroll
+    for (int f = 0; f < kFzNF; ++f) y[e][f] = make_float2(0.f, 0.f);
+  const float2* seg = tile + t * (kFzR * 8 + 2);
+#pragma unroll
+  for (int v = 0; v < NV; v += 2) {
+    float4 xx;
+    if (v + 1 < NV) {
+      xx = *reinterpret_cast<const float4*>(seg + fz_pos(v));
+    } else {
+      const float2 x1 = seg[fz_pos(v)];
+      xx = make_float4(x1.x, x1.y, 0.f, 0.f);
+    }
+#pragma unroll
+    for (int s = 0; s < 2; ++s) {
+      if (v + s < NV) {
+        const float2 x = s ? make_float2(xx.z, xx.w) : make_float2(xx.x, xx.y);
+#pragma unroll
+        for (int e = 0; e < kFzR; ++e) {
+          const int u = v + s - e * 8;
+          if (u >= 0 && u < kFzNT) {
+#pragma unroll
+            for (int f = 0; f < kFzNF; ++f) y[e][f] = ffma2(x, tap2[f * kFzNT + kFzNT - 1 - u], y[e][f]);
+          }
+        }
+      }
+    }
+  }
+#pragma unroll
+  for (int e = 0; e < kFzR; ++e) {
+    const int c = c0 + e;
+    if ((unsigned)c < (unsigned)fz.n_calls)
+      *reinterpret_cast<float4*>(zrow + 2 * (int64_t)c) = make_float4(y[e][0].x, y[e][0].y, y[e][1].x, y[e][1].y);
+  }
+}
+
+// R = 4 consecutive calls of thread t, filter F, from the tile; per (call, filter) the same FFMA2 sequence as
+// mf_bank_f32_kernel<8, 2, 73, false, 4> (oldest sample first), so the sums are bit-identical.  Warps 0-3 run
+// F = 0 and warps 4-7 F = 1 over the same 512 calls: all eight warps of the block share the bank phase.
+template <int F>
+static __device__ __forceinline__ void fz_bank_phase(const FuseParams& fz, const float2* tile, int t, int cbase, float2* zrow) {
+  const int c0 = cbase + kFzR * t;
+  if (c0 + kFzR - 1 < 0 || c0 >= fz.n_calls) return;
+  constexpr int NV = (kFzR - 1) * 8 + kFzNT;
+  const float2* tap2 = reinterpret_cast<const float2*>(fz.tap2) + F * kFzNT;
+  float2 y[kFzR];
+#pragma unroll
+  for (int e = 0; e < kFzR; ++e) y[e] = make_float2(0.f, 0.f);
+  const float2* seg = tile + t * (kFzR * 8 + 2);
+#pragma unroll
+  for (int v = 0; v < NV; v += 2) {
+    float4 xx;
+    if (v + 1 < NV) {
+      xx = *reinterpret_cast<const float4*>(seg + fz_pos(v));
+    } else {
+      const float2 x1 = seg[fz_pos(v)];
+      xx = make_float4(x1.x, x1.y, 0.f, 0.f);
+    }
+#pragma unroll
+    for (int s = 0; s < 2; ++s) {
+      if (v + s < NV) {
+        const float2 x = s ? make_float2(xx.z, xx.w) : make_float2(xx.x, xx.y);
+#pragma unroll
+        for (int e = 0; e < kFzR; ++e) {
+          const int u = v + s - e * 8;
+          if (u >= 0 && u < kFzNT) y[e] = ffma2(x, tap2[kFzNT - 1 - u], y[e]);
+        }
+      }
+    }
+  }
+#pragma unroll
+  for (int e = 0; e < kFzR; ++e) {
+    const int c = c0 + e;
+    if ((unsigned)c < (unsigned)fz.n_calls) zrow[2 * (int64_t)c + F] = y[e];
+  }
+}
+
 // Rare path (p = 2^-15 per pair): one pair again, this time with the tail refinement of the
 // radius uniform.  Kept out of line so the unrolled main loop stays branch free.
 // Sample a: window wa (symbols A-JT .. A-1 of ITS interval), fa = F[A - JT], Q index qa0 + 8 j;
@@ -290,10 +406,15 @@ static __device__ __noinline__ float4 mod_f32s8_slow_pair(const ModParams<float>
 // even for ODD a, so a thread's pair is a = 8 A + 2 sub - 1, 8 A + 2 sub; for sub = 0 the first of
 // the two is the LAST sample (rho = 7) of interval A - 1: one symbol further back in the window and
 // in F.  The pair then runs on two scalar FFMA chains instead of one packed FFMA2 chain.
-template <int JT, bool NOISE, int RUN, int MINB, bool ODD>
+template <int JT, bool NOISE, int RUN, int MINB, bool ODD, bool FUSE = false, int FSEG = kFSeg, bool KSPLIT = true>
 __global__ void __launch_bounds__(kModThreads, MINB)
-cpm_modulate_f32s8_kernel(const __grid_constant__ ModParams<float> p) {
+cpm_modulate_f32s8_kernel(const __grid_constant__ ModParams<float> p,
+                          const __grid_constant__ typename std::conditional<FUSE, FuseParams, FuseNone>::type fz) {
   constexpr int kFChunk = RUN * (kModThreads / 4);
+  constexpr int kFSeg = FSEG;                    // shadows the namespace constant: segment length of THIS instance
+  constexpr int kFSlots = kFLB + FSEG + 8;
+  constexpr size_t kFSmemBytes = (size_t)kFSlots * 8;
+  static_assert(!FUSE || (!ODD && kFChunk == kFzChunk), "the fused bank wants 512-interval chunks and an even offset");
   constexpr int kScanStep = 4 * kModThreads;
   static_assert(kFSeg % kFChunk == 0 && kFSeg % kScanStep == 0, "segment = whole chunks and whole scan steps");
   static_assert(JT + 2 <= kFLB && (RUN % 2) == 0, "look-back too short / odd run");
@@ -305,6 +426,20 @@ cpm_modulate_f32s8_kernel(const __grid_constant__ ModParams<float> p) {
 
   const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
   const int64_t frame = blockIdx.x;
+  float2* tile = reinterpret_cast<float2*>(smem_raw + kFSmemBytes);  // FUSE only
+  if constexpr (FUSE) {  // samples before the frame are zero; published by the scan's barriers
+    if (tid < kFzLBMax / 2 + 8) *reinterpret_cast<float4*>(tile + fz_pos(2 * tid)) = make_float4(0.f, 0.f, 0.f, 0.f);
+#ifndef WF_HOSTEMU
+    // Blocks that start together on an SM would run their produce (XU-bound) and bank (FMA-bound) phases in
+    // lockstep, all in the same phase at the same time.  The first wave is therefore started a fraction of a chunk
+    // period apart per residency slot; later blocks inherit the offset (each starts when its predecessor ends).
+    if (fz.stagger > 0 && blockIdx.x < 4u * (unsigned)fz.n_sm) {
+      const long long wait = (long long)((blockIdx.x / (unsigned)fz.n_sm) & 3u) * fz.stagger;
+      const long long t0 = clock64();
+      while (clock64() - t0 < wait) {}
+    }
+#endif
+  }
   const int off = p.off;
   const int S = (int)p.S, Ti = (int)p.Tn;
   const int8_t* sy = p.syms + frame * (int64_t)S;
@@ -453,7 +588,11 @@ cpm_modulate_f32s8_kernel(const __grid_constant__ ModParams<float> p) {
     }
     for (int cs = 0; cs < kFSeg && k_lo + cs <= A_last; cs += kFChunk) {
       const int r0 = cs + grp * RUN + e;             // first interval of this run, relative to k_lo
-      if (k_lo + r0 > A_last) break;                 // this run (and every later one of the thread) is past the frame
+      const bool live = k_lo + r0 <= A_last;
+      if (!FUSE && !live) break;                     // this run (and every later one of the thread) is past the frame
+      int mb = 0;                                    // FUSE: tile sample index of this thread's first pair
+      if constexpr (FUSE) mb = fz.LB + 8 * (grp * RUN + e) + 2 * sub;
+      if (live) {
       const float* wp = w_s + (r0 - JT + kFLB);      // symbols A0-JT .. A0+RUN-2
       const uint32_t* fp = f_s + (r0 - JT - 1 + kFLB);  // F[A0-JT ..]
       float w[JT + RUN - 1];   // sample b's window (and sample a's unless it sits one interval back)
@@ -521,7 +660,14 @@ cpm_modulate_f32s8_kernel(const __grid_constant__ ModParams<float> p) {
           const float2 g0 = box_muller16(wa, noise_lgt(wa), ncoef), g1 = box_muller16(wb, noise_lgt(wb), ncoef);
           c0f += g0.x; s0f += g0.y; c1f += g1.x; s1f += g1.y;
         }
-        if ((unsigned)(n0 + 8 * i) < (unsigned)Ti) o[4 * i] = make_float4(c0f, s0f, c1f, s1f);
+        if constexpr (FUSE) {
+          const bool in = (unsigned)(n0 + 8 * i) < (unsigned)Ti;
+          const int m = mb + 8 * i;
+          *reinterpret_cast<float4*>(tile + m + ((m >> 5) << 1)) =
+              in ? make_float4(c0f, s0f, c1f, s1f) : make_float4(0.f, 0.f, 0.f, 0.f);
+        } else {
+          if ((unsigned)(n0 + 8 * i) < (unsigned)Ti) o[4 * i] = make_float4(c0f, s0f, c1f, s1f);
+        }
       }
       if (NOISE && m_min == 0u) {  // some radius uniform of this run needs its tail refined: redo those pairs
 #pragma unroll 1
@@ -529,10 +675,41 @@ cpm_modulate_f32s8_kernel(const __grid_constant__ ModParams<float> p) {
           ctr.x = c0 + 4u * (uint32_t)(i >> 1);
           const u32x4 rr = philox4x32_10_rk(ctr, p.rk);
           const uint32_t wa = (i & 1) ? rr.z : rr.x, wb = (i & 1) ? rr.w : rr.y;
-          if (((wa & 0xFFFFu) == 0u || (wb & 0xFFFFu) == 0u) && (unsigned)(n0 + 8 * i) < (unsigned)Ti)
-            o[4 * i] = mod_f32s8_slow_pair<JT>(p, (sha ? wp - 1 : wp) + i, wp + i, (sha ? fp - 1 : fp)[i], fp[i], qa0, qb0, ctr,
-                                               i & 1, ncoef);
+          if (((wa & 0xFFFFu) == 0u || (wb & 0xFFFFu) == 0u) && (unsigned)(n0 + 8 * i) < (unsigned)Ti) {
+            const float4 v4 = mod_f32s8_slow_pair<JT>(p, (sha ? wp - 1 : wp) + i, wp + i, (sha ? fp - 1 : fp)[i], fp[i], qa0,
+                                                      qb0, ctr, i & 1, ncoef);
+            if constexpr (FUSE) {
+              const int m = mb + 8 * i;
+              *reinterpret_cast<float4*>(tile + m + ((m >> 5) << 1)) = v4;
+            } else {
+              o[4 * i] = v4;
+            }
+          }
         }
+      }
+      } else if constexpr (FUSE) {  // run past the end of the frame: its samples are zeros for the bank
+#pragma unroll
+        for (int i = 0; i < RUN; ++i) {
+          const int m = mb + 8 * i;
+          *reinterpret_cast<float4*>(tile + m + ((m >> 5) << 1)) = make_float4(0.f, 0.f, 0.f, 0.f);
+        }
+      }
+      if constexpr (FUSE) {
+        __syncthreads();  // the chunk's 4096 samples (and the carried look-back) are in the tile
+        const int q = tid - kFzThreads;
+        const bool carry_lane = q >= 0 && 2 * q < fz.LB;
+        float4 keep = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (carry_lane) keep = *reinterpret_cast<const float4*>(tile + fz_pos(8 * kFzChunk + 2 * q));
+        if constexpr (KSPLIT) {
+          if (tid < kFzThreads)
+            fz_bank_phase<0>(fz, tile, tid, (k_lo + cs) - fz.CB, fz.z + frame * fz.ld_z * kFzNF);
+          else
+            fz_bank_phase<1>(fz, tile, q, (k_lo + cs) - fz.CB, fz.z + frame * fz.ld_z * kFzNF);
+        } else {
+          if (tid < kFzThreads) fz_bank_phase2(fz, tile, tid, (k_lo + cs) - fz.CB, fz.z + frame * fz.ld_z * kFzNF);
+        }
+        __syncthreads();  // bank reads done: the front of the tile may take the next chunk's look-back
+        if (carry_lane) *reinterpret_cast<float4*>(tile + fz_pos(2 * q)) = keep;
       }
     }
   }
@@ -648,11 +825,10 @@ phase_modulate_kernel(const double* __restrict__ ph, int64_t n, double sensitivi
 }
 
 template <typename T>
-static int launch_modulate(const int8_t* d_syms, int64_t B, int64_t S, const double* mod_index, int n_h,
+static int fill_mod_params(ModParams<T>& p, const int8_t* d_syms, int64_t B, int64_t S, const double* mod_index, int n_h,
                            const double* pulse, int K, int sps, double initial_phase, double derotate,
                            void* d_out, int64_t ld_out, const float* d_sigma, const int32_t* d_point,
-                           uint64_t seed, uint64_t first_frame, cudaStream_t stream) {
-  ModParams<T> p;
+                           uint64_t seed, uint64_t first_frame) {
   memset(&p, 0, sizeof(p));
   p.syms = d_syms; p.out = d_out; p.sigma = d_sigma; p.point = d_point;
   p.B = B; p.S = S; p.Tn = (S + 1) * sps; p.ld_out = ld_out;
@@ -680,6 +856,18 @@ static int launch_modulate(const int8_t* d_syms, int64_t B, int64_t S, const dou
   double ph0 = (initial_phase + derotate) / two_pi;
   p.phase0_turns = (T)(ph0 - floor(ph0 + 0.5));
   p.inv_sps = (T)(1.0 / (double)sps);
+  return WF_OK;
+}
+
+template <typename T>
+static int launch_modulate(const int8_t* d_syms, int64_t B, int64_t S, const double* mod_index, int n_h,
+                           const double* pulse, int K, int sps, double initial_phase, double derotate,
+                           void* d_out, int64_t ld_out, const float* d_sigma, const int32_t* d_point,
+                           uint64_t seed, uint64_t first_frame, cudaStream_t stream) {
+  ModParams<T> p;
+  int rcp = fill_mod_params<T>(p, d_syms, B, S, mod_index, n_h, pulse, K, sps, initial_phase, derotate, d_out, ld_out,
+                               d_sigma, d_point, seed, first_frame);
+  if (rcp) return rcp;
   const bool noise = d_sigma != nullptr;
   const dim3 grid((unsigned)B), block(kModThreads);
   const bool fast8 = (sps == 8) && (p.off % 2 == 0);
@@ -694,8 +882,8 @@ static int launch_modulate(const int8_t* d_syms, int64_t B, int64_t S, const dou
     const ModParams<float>& pf = reinterpret_cast<const ModParams<float>&>(p);  // T == float on this branch
 #define WF_MODF_LAUNCH(JT_, RUN_, MINB_, ODD_)                                                                   \
   do {                                                                                                          \
-    if (noise) cpm_modulate_f32s8_kernel<JT_, true, RUN_, MINB_, ODD_><<<grid, block, kFSmemBytes, stream>>>(pf);  \
-    else cpm_modulate_f32s8_kernel<JT_, false, RUN_, MINB_, ODD_><<<grid, block, kFSmemBytes, stream>>>(pf);       \
+    if (noise) cpm_modulate_f32s8_kernel<JT_, true, RUN_, MINB_, ODD_><<<grid, block, kFSmemBytes, stream>>>(pf, FuseNone{0});  \
+    else cpm_modulate_f32s8_kernel<JT_, false, RUN_, MINB_, ODD_><<<grid, block, kFSmemBytes, stream>>>(pf, FuseNone{0});       \
   } while (0)
     // RUN = 8 intervals per thread at 4 resident blocks/SM (64 registers) measured fastest on B200
     // among RUN in {4, 8, 16} x blocks/SM in {3, 4, 5} (profiles/r1f_kbench_mod_variants.log)
@@ -718,9 +906,103 @@ static int launch_modulate(const int8_t* d_syms, int64_t B, int64_t S, const dou
   return WF_OK;
 }
 
+// Geometry of the fused kernel for a bank described the way wf_mf_bank takes it.  Returns false when
+// the shape is not the one the fused kernel is built for (callers then run the two-kernel path).
+static bool fuse_geometry(int K, int sps, int n_filt, int n_taps, int center, int64_t first_instant, int64_t S,
+                          int64_t n_calls, int& CB, int& LB) {
+  if (sps != 8 || n_filt != kFzNF || n_taps != kFzNT || K < 2) return false;
+  const int off = (K - 1) / 2, J = (K - 1 + sps - 1) / sps;
+  if (J != 8 || (off % 8) != 0) return false;            // JT = 8 instance; off % 8 == 0 keeps every lane's e at 0
+  if (first_instant < 0 || first_instant >= 4096 || center < 0 || center >= kFzNT) return false;
+  if (S < 1 || (S + 1) * 8 >= 0x7FFFF000LL || n_calls < 0 || n_calls >= 0x7FFFF000LL) return false;
+  const int x = (int)first_instant + center + off - 7;    // window of call c ends at sample 8 c + x + 7 - off
+  CB = x > 0 ? (x + 7) / 8 : 0;
+  LB = kFzNT - 1 + 8 * CB - off - (int)first_instant - center;
+  if (LB < 0 || LB > kFzLBMax || (LB & 1)) return false;
+  const int64_t A_last = ((S + 1) * 8 - 1 + off) >> 3;
+  const int64_t n_chunks = A_last / kFzChunk + 1;
+  return n_calls <= n_chunks * kFzChunk - CB;
+}
+
+static int launch_modulate_bank(const int8_t* d_syms, int64_t B, int64_t S, const double* mod_index, int n_h,
+                                const double* pulse, int K, int sps, double initial_phase, double derotate,
+                                const float* d_sigma, const int32_t* d_point, uint64_t seed, uint64_t first_frame,
+                                const double* taps_re, int n_filt, int n_taps, int center, int64_t first_instant,
+                                int64_t n_calls, void* d_z, int64_t ld_z, cudaStream_t stream) {
+  int CB = 0, LB = 0;
+  if (!fuse_geometry(K, sps, n_filt, n_taps, center, first_instant, S, n_calls, CB, LB)) {
+    return fail(WF_ERR_UNSUPPORTED, "wf_cpm_modulate_bank: shape not covered by the fused kernel (see wf_cpm_modulate_bank_supported)");
+  }
+  ModParams<float> p;
+  int rc = fill_mod_params<float>(p, d_syms, B, S, mod_index, n_h, pulse, K, sps, initial_phase, derotate, nullptr,
+                                  (S + 1) * sps, d_sigma, d_point, seed, first_frame);
+  if (rc) return rc;
+  FuseParams fz;
+  memset(&fz, 0, sizeof(fz));
+  fz.z = reinterpret_cast<float2*>(d_z); fz.ld_z = ld_z; fz.n_calls = (int)n_calls; fz.CB = CB; fz.LB = LB;
+  fz.n_sm = sm_count();
+  {
+    const char* ev = getenv("WF_FUSE_STAGGER");
+    fz.stagger = ev ? atoi(ev) : 2500;
+    if (fz.stagger < 0 || fz.stagger > 1000000) fz.stagger = 2500;
+  }
+  for (int i = 0; i < kFzNF * kFzNT; ++i) fz.tap2[2 * i] = fz.tap2[2 * i + 1] = (float)taps_re[i];
+  const dim3 grid((unsigned)B), block(kModThreads);
+  // Scan segment length / resident blocks per SM of the fused instance.  Short segments keep the scan arrays small
+  // (8 B per symbol interval), which is what lets 4 blocks of (scan arrays + 36 KB sample tile) share an SM.
+  static int variant = -1;
+  if (variant < 0) {
+    const char* ev = getenv("WF_FUSE_VARIANT");
+    variant = ev ? atoi(ev) : 3;
+    if (variant < 1 || variant > 3) variant = 3;
+  }
+#define WF_FZ_LAUNCH(NOISE_, MINB_, FSEG_, KS_)                                                                 \
+  do {                                                                                                      \
+    auto kfn = cpm_modulate_f32s8_kernel<8, NOISE_, 8, MINB_, false, true, FSEG_, KS_>;                     \
+    cudaError_t e = cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)fz_smem_bytes(FSEG_)); \
+    if (e != cudaSuccess) return cuda_fail(e, "cudaFuncSetAttribute(cpm_modulate_f32s8_kernel fused)");    \
+    kfn<<<grid, block, fz_smem_bytes(FSEG_), stream>>>(p, fz);                                             \
+  } while (0)
+  if (!d_sigma) WF_FZ_LAUNCH(false, 4, 2048, true);
+  else if (variant == 1) WF_FZ_LAUNCH(true, 4, 2048, false);
+  else if (variant == 2) WF_FZ_LAUNCH(true, 4, 1024, true);
+  else WF_FZ_LAUNCH(true, 4, 2048, true);
+#undef WF_FZ_LAUNCH
+  WF_LAUNCH_CHECK("cpm_modulate_f32s8_kernel (fused bank)");
+  return WF_OK;
+}
+
 }  // namespace wf
 
 extern "C" {
+
+int wf_cpm_modulate_bank_supported(int K, int sps, int n_filt, int n_taps, int center, int64_t first_instant, int64_t S,
+                                   int64_t n_calls) {
+  int CB, LB;
+  return wf::fuse_geometry(K, sps, n_filt, n_taps, center, first_instant, S, n_calls, CB, LB) ? 1 : 0;
+}
+
+int wf_cpm_modulate_bank(const int8_t* d_syms, int64_t B, int64_t S, const double* mod_index, int n_h,
+                         const double* pulse, int K, int sps, double initial_phase, double derotate,
+                         const float* d_sigma, const int32_t* d_point, uint64_t seed, uint64_t first_frame,
+                         const double* taps_re, int n_filt, int n_taps, int center, int64_t first_instant,
+                         int64_t n_calls, void* d_z, int64_t ld_z, void* stream) {
+  using namespace wf;
+  WF_REQUIRE(B >= 0 && S >= 0 && n_calls >= 0, "negative shape");
+  WF_REQUIRE(K >= 1 && pulse, "empty pulse filter");
+  WF_REQUIRE(n_h >= 1 && n_h <= kMaxH && mod_index, "n_h=%d outside 1..%d", n_h, kMaxH);
+  WF_REQUIRE(taps_re && n_filt >= 1 && n_taps >= 1, "bad filter bank shape");
+  WF_REQUIRE(ld_z >= n_calls, "ld_z smaller than n_calls");
+  WF_REQUIRE(B <= 0x7FFFFFFF, "batch too large for one launch");
+  int rc;
+  if ((rc = require_device())) return rc;
+  if (B == 0 || n_calls == 0) return WF_OK;
+  WF_REQUIRE(d_syms && d_z, "NULL device pointer");
+  WF_REQUIRE((reinterpret_cast<uintptr_t>(d_z) & 15) == 0, "d_z must be 16-byte aligned");
+  return launch_modulate_bank(d_syms, B, S, mod_index, n_h, pulse, K, sps, initial_phase, derotate, d_sigma, d_point, seed,
+                              first_frame, taps_re, n_filt, n_taps, center, first_instant, n_calls, d_z, ld_z,
+                              as_stream(stream));
+}
 
 int wf_cpm_modulate(const int8_t* d_syms, int64_t B, int64_t S, const double* mod_index, int n_h,
                     const double* pulse, int K, int sps, double initial_phase, double derotate,

@@ -99,9 +99,18 @@ class LinkSimulator:
                          and not bool(cfg.extra.get("combine_in_bank", False)))
         if self.raw_bank:
             self._n_out = 2
+        # Fused modulate -> AWGN -> PAM bank (wf_cpm_modulate_bank): the noisy baseband never reaches HBM and
+        # the rx buffer is not allocated.  Same z, bit for bit, as the two-kernel path; opt-in with
+        # extra["fused"] = True, taken when the library covers the shape (SOQPSK-TG at sps 8 today).
+        self.fused = bool(cfg.extra.get("fused", False)) and self.raw_bank and cfg.dtype == torch.complex64 and bool(
+            _ffi.lib().wf_cpm_modulate_bank_supported(int(self.pulse.size), cfg.sps, int(self._taps.shape[0]),
+                                                      int(self._taps.shape[1]), (int(self._taps.shape[1]) - 1) // 2,
+                                                      int(self.first_instant), int(self.n_sym), int(self.n_calls)))
+        self.stage_names = (("prbs_encode", "modulate_awgn_bank", "viterbi_bert") if self.fused
+                            else ("prbs_encode", "modulate_awgn", "mf_bank", "viterbi_bert"))
         self.max_batch = 0
         self._alloc(int(max_batch))
-        self.launches = 0  # kernels launched so far (4 per run_batch)
+        self.launches = 0  # kernels launched so far (len(stage_names) per run_batch)
 
     def _init_generic(self, h, bps) -> None:
         """PCM/FM and multi-h: generic pulse-truncated trellis detector (no reference detector exists)."""
@@ -122,6 +131,8 @@ class LinkSimulator:
         self._tap_im = _dev.host_f64(self._taps.imag.ravel())
         self._comb_re = self._comb_im = None
         self._n_out = self._taps.shape[0]
+        self.fused = False
+        self.stage_names = ("prbs_encode", "modulate_awgn", "mf_bank", "viterbi_bert")
         self.max_batch = 0
         self._alloc(int(self._max_batch_arg))
         self.launches = 0
@@ -135,11 +146,11 @@ class LinkSimulator:
         self.ld_z = (self.n_calls + 3) & ~3 if self.soqpsk else self.n_calls
         self.packed = torch.zeros((max_batch, self.ld_words), dtype=torch.int32, device=dev)
         self.syms = torch.empty((max_batch, self.n_sym), dtype=torch.int8, device=dev)
-        self.rx = torch.empty((max_batch, self.ld_rx), dtype=cfg.dtype, device=dev)
+        self.rx = None if self.fused else torch.empty((max_batch, self.ld_rx), dtype=cfg.dtype, device=dev)
         self.z = torch.empty((max_batch, self.ld_z, self._n_out), dtype=cfg.dtype, device=dev)
 
     def workspace_bytes(self) -> int:
-        return sum(t.numel() * t.element_size() for t in (self.packed, self.syms, self.rx, self.z))
+        return sum(t.numel() * t.element_size() for t in (self.packed, self.syms, self.rx, self.z) if t is not None)
 
     # ------------------------------------------------------------------ one batch
     def run_batch(self, first_frame: int, sigma: torch.Tensor, point: torch.Tensor | None, counters: torch.Tensor,
@@ -147,7 +158,7 @@ class LinkSimulator:
         """Frames first_frame .. first_frame+B-1 (B = len(sigma) <= max_batch) through the whole
         chain; adds (bit errors, symbol errors, compared) to counters[point[b]].  Everything is
         enqueued on the current stream; nothing is synchronised.  ``events`` (optional list)
-        receives five CUDA events recorded on that stream around the four kernels."""
+        receives len(stage_names) + 1 CUDA events recorded on that stream around the kernels."""
         cfg, lib, dev = self.cfg, _ffi.lib(), self.device
         B = sigma.shape[0]
         if B > self.max_batch:
@@ -169,6 +180,21 @@ class LinkSimulator:
                                           cfg.n_bits, self.encoder, None, None, _dev.ptr(self.packed), self.ld_words,
                                           _dev.ptr(self.syms), st))
             mark()
+            if self.fused:
+                _ffi.check(lib.wf_cpm_modulate_bank(_dev.ptr(self.syms), B, self.n_sym, _dev.f64_ptr(self.h), self.h.size,
+                                                    _dev.f64_ptr(self.pulse), self.pulse.size, cfg.sps, math.pi / 4,
+                                                    -math.pi / 4, _dev.ptr(sigma), _dev.ptr(point), seed, int(first_frame),
+                                                    _dev.f64_ptr(self._tap_re), self._taps.shape[0], self._taps.shape[1],
+                                                    (self._taps.shape[1] - 1) // 2, self.first_instant, self.n_calls,
+                                                    _dev.ptr(self.z), self.ld_z, st))
+                mark()
+                _ffi.check(lib.wf_viterbi_soqpsk_combined(_dev.ptr(self.z), dt, B, self.n_calls, self.ld_z, 2,
+                                                          _dev.f64_ptr(self._comb_re), _dev.f64_ptr(self._comb_im),
+                                                          int(cfg.differential), _dev.ptr(self.packed), self.ld_words,
+                                                          self.n_sym, _dev.ptr(point), _dev.ptr(counters), st))
+                mark()
+                self.launches += 3
+                return
             _ffi.check(lib.wf_cpm_modulate(_dev.ptr(self.syms), B, self.n_sym, _dev.f64_ptr(self.h), self.h.size,
                                            _dev.f64_ptr(self.pulse), self.pulse.size, cfg.sps, math.pi / 4, -math.pi / 4,
                                            dt, _dev.ptr(self.rx), self.ld_rx, _dev.ptr(sigma), _dev.ptr(point), seed,
