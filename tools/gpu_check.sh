@@ -17,6 +17,8 @@ timeout 600 python bench.py --frames 4096 --steps 3 --warmup 3 --no-cpu-baseline
 echo "bench_small exit $?"; tail -c 600 $OUT/bench_small.json
 timeout 900 python bench.py --steps 10 --warmup 3 > $OUT/bench.json 2> $OUT/bench.err
 echo "bench exit $?"; cat $OUT/bench.json
+timeout 900 python bench.py --fused --steps 10 --warmup 3 --no-cpu-baseline > $OUT/bench_fused.json 2> $OUT/bench_fused.err
+echo "bench fused exit $?"; cat $OUT/bench_fused.json
 timeout 900 python bench.py --impl reference --steps 2 --warmup 1 > $OUT/bench_reference.json 2> $OUT/bench_reference.err
 echo "bench ref exit $?"
 
@@ -34,4 +36,13 @@ ls -la $OUT
 for wf in pcmfm multih soqpsk-tg; do
   timeout 300 python tools/kbench.py --frames 65536 --reps 3 --waveform $wf >> $OUT/kbench_waveforms.log 2>&1
 done
+timeout 300 python tools/kbench.py --frames 65536 --reps 3 --fused >> $OUT/kbench_waveforms.log 2>&1
 cat $OUT/kbench_waveforms.log
+# launch list of the fused link (only after the identical command exited 0 without ncu)
+FCMD="python bench.py --fused --frames ${NCU_FRAMES:-32768} --steps 2 --warmup 3 --no-cpu-baseline"
+$FCMD > $OUT/ncu_plain_fused.log 2>&1 &&
+ncu --metrics gpu__time_duration.sum --clock-control none -c 200 --csv --log-file $OUT/launches_fused.csv $FCMD > $OUT/ncu_launches_fused.log 2>&1
+echo "ncu fused launches exit $?"
+$FCMD > $OUT/ncu_plain_fused2.log 2>&1 &&
+timeout 600 ncu --set full --clock-control none --import-source on -k regex:cpm_modulate -s 3 -c 1 -o $OUT/prof_fused $FCMD > $OUT/ncu_full_fused.log 2>&1
+echo "ncu fused full exit $?"

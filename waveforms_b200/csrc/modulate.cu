@@ -14,7 +14,6 @@
 #include "common.cuh"
 #include <math.h>
 #include <string.h>
-#include <stdlib.h>
 #include <type_traits>
 
 #ifndef WF_MOD_FFMA2
@@ -281,14 +280,14 @@ constexpr int kFzThreads = 128;                   // threads that run the bank p
 constexpr int kFzChunk = kFzR * kFzThreads;       // calls per chunk == intervals per chunk
 constexpr int kFzLBMax = 96;                      // look-back samples kept from the previous chunk
 constexpr int kFzSlots = 4464;                    // pos(8 * kFzChunk + kFzLBMax) rounded up
-constexpr size_t fz_smem_bytes(int fseg) { return (size_t)(kFLB + fseg + 8) * 8 + (size_t)kFzSlots * 8; }
+constexpr int kFzSeg = 2048;                      // scan segment of the fused instance (symbol intervals)
+constexpr size_t kFzSmemBytes = (size_t)(kFLB + kFzSeg + 8) * 8 + (size_t)kFzSlots * 8;
 __host__ __device__ constexpr int fz_pos(int m) { return m + 2 * (m >> 5); }
 
 struct FuseParams {
   float2* z;            // [B][ld_z][2] raw outputs of the two real-tap filters
   int64_t ld_z;
   int n_calls, CB, LB;
-  int n_sm, stagger;    // first-wave blocks of residency slot k = (blockIdx / n_sm) & 3 start k * stagger cycles late
   alignas(16) float tap2[2 * kFzNF * kFzNT];  // (t, t) pairs, filter-major: 64-bit uniform operands of the packed FFMA2
 };
 struct FuseNone { int unused; };
@@ -337,47 +336,6 @@ static __device__ __forceinline__ void fz_bank_phase2(const FuseParams& fz, cons
   }
 }
 
-// R = 4 consecutive calls of thread t, filter F, from the tile; per (call, filter) the same FFMA2 sequence as
-// mf_bank_f32_kernel<8, 2, 73, false, 4> (oldest sample first), so the sums are bit-identical.  Warps 0-3 run
-// F = 0 and warps 4-7 F = 1 over the same 512 calls: all eight warps of the block share the bank phase.
-template <int F>
-static __device__ __forceinline__ void fz_bank_phase(const FuseParams& fz, const float2* tile, int t, int cbase, float2* zrow) {
-  const int c0 = cbase + kFzR * t;
-  if (c0 + kFzR - 1 < 0 || c0 >= fz.n_calls) return;
-  constexpr int NV = (kFzR - 1) * 8 + kFzNT;
-  const float2* tap2 = reinterpret_cast<const float2*>(fz.tap2) + F * kFzNT;
-  float2 y[kFzR];
-#pragma unroll
-  for (int e = 0; e < kFzR; ++e) y[e] = make_float2(0.f, 0.f);
-  const float2* seg = tile + t * (kFzR * 8 + 2);
-#pragma unroll
-  for (int v = 0; v < NV; v += 2) {
-    float4 xx;
-    if (v + 1 < NV) {
-      xx = *reinterpret_cast<const float4*>(seg + fz_pos(v));
-    } else {
-      const float2 x1 = seg[fz_pos(v)];
-      xx = make_float4(x1.x, x1.y, 0.f, 0.f);
-    }
-#pragma unroll
-    for (int s = 0; s < 2; ++s) {
-      if (v + s < NV) {
-        const float2 x = s ? make_float2(xx.z, xx.w) : make_float2(xx.x, xx.y);
-#pragma unroll
-        for (int e = 0; e < kFzR; ++e) {
-          const int u = v + s - e * 8;
-          if (u >= 0 && u < kFzNT) y[e] = ffma2(x, tap2[kFzNT - 1 - u], y[e]);
-        }
-      }
-    }
-  }
-#pragma unroll
-  for (int e = 0; e < kFzR; ++e) {
-    const int c = c0 + e;
-    if ((unsigned)c < (unsigned)fz.n_calls) zrow[2 * (int64_t)c + F] = y[e];
-  }
-}
-
 // Rare path (p = 2^-15 per pair): one pair again, this time with the tail refinement of the
 // radius uniform.  Kept out of line so the unrolled main loop stays branch free.
 // Sample a: window wa (symbols A-JT .. A-1 of ITS interval), fa = F[A - JT], Q index qa0 + 8 j;
@@ -406,7 +364,7 @@ static __device__ __noinline__ float4 mod_f32s8_slow_pair(const ModParams<float>
 // even for ODD a, so a thread's pair is a = 8 A + 2 sub - 1, 8 A + 2 sub; for sub = 0 the first of
 // the two is the LAST sample (rho = 7) of interval A - 1: one symbol further back in the window and
 // in F.  The pair then runs on two scalar FFMA chains instead of one packed FFMA2 chain.
-template <int JT, bool NOISE, int RUN, int MINB, bool ODD, bool FUSE = false, int FSEG = kFSeg, bool KSPLIT = true>
+template <int JT, bool NOISE, int RUN, int MINB, bool ODD, bool FUSE = false, int FSEG = kFSeg>
 __global__ void __launch_bounds__(kModThreads, MINB)
 cpm_modulate_f32s8_kernel(const __grid_constant__ ModParams<float> p,
                           const __grid_constant__ typename std::conditional<FUSE, FuseParams, FuseNone>::type fz) {
@@ -429,16 +387,6 @@ cpm_modulate_f32s8_kernel(const __grid_constant__ ModParams<float> p,
   float2* tile = reinterpret_cast<float2*>(smem_raw + kFSmemBytes);  // FUSE only
   if constexpr (FUSE) {  // samples before the frame are zero; published by the scan's barriers
     if (tid < kFzLBMax / 2 + 8) *reinterpret_cast<float4*>(tile + fz_pos(2 * tid)) = make_float4(0.f, 0.f, 0.f, 0.f);
-#ifndef WF_HOSTEMU
-    // Blocks that start together on an SM would run their produce (XU-bound) and bank (FMA-bound) phases in
-    // lockstep, all in the same phase at the same time.  The first wave is therefore started a fraction of a chunk
-    // period apart per residency slot; later blocks inherit the offset (each starts when its predecessor ends).
-    if (fz.stagger > 0 && blockIdx.x < 4u * (unsigned)fz.n_sm) {
-      const long long wait = (long long)((blockIdx.x / (unsigned)fz.n_sm) & 3u) * fz.stagger;
-      const long long t0 = clock64();
-      while (clock64() - t0 < wait) {}
-    }
-#endif
   }
   const int off = p.off;
   const int S = (int)p.S, Ti = (int)p.Tn;
@@ -700,14 +648,7 @@ cpm_modulate_f32s8_kernel(const __grid_constant__ ModParams<float> p,
         const bool carry_lane = q >= 0 && 2 * q < fz.LB;
         float4 keep = make_float4(0.f, 0.f, 0.f, 0.f);
         if (carry_lane) keep = *reinterpret_cast<const float4*>(tile + fz_pos(8 * kFzChunk + 2 * q));
-        if constexpr (KSPLIT) {
-          if (tid < kFzThreads)
-            fz_bank_phase<0>(fz, tile, tid, (k_lo + cs) - fz.CB, fz.z + frame * fz.ld_z * kFzNF);
-          else
-            fz_bank_phase<1>(fz, tile, q, (k_lo + cs) - fz.CB, fz.z + frame * fz.ld_z * kFzNF);
-        } else {
-          if (tid < kFzThreads) fz_bank_phase2(fz, tile, tid, (k_lo + cs) - fz.CB, fz.z + frame * fz.ld_z * kFzNF);
-        }
+        if (tid < kFzThreads) fz_bank_phase2(fz, tile, tid, (k_lo + cs) - fz.CB, fz.z + frame * fz.ld_z * kFzNF);
         __syncthreads();  // bank reads done: the front of the tile may take the next chunk's look-back
         if (carry_lane) *reinterpret_cast<float4*>(tile + fz_pos(2 * q)) = keep;
       }
@@ -940,33 +881,22 @@ static int launch_modulate_bank(const int8_t* d_syms, int64_t B, int64_t S, cons
   FuseParams fz;
   memset(&fz, 0, sizeof(fz));
   fz.z = reinterpret_cast<float2*>(d_z); fz.ld_z = ld_z; fz.n_calls = (int)n_calls; fz.CB = CB; fz.LB = LB;
-  fz.n_sm = sm_count();
-  {
-    const char* ev = getenv("WF_FUSE_STAGGER");
-    fz.stagger = ev ? atoi(ev) : 2500;
-    if (fz.stagger < 0 || fz.stagger > 1000000) fz.stagger = 2500;
-  }
   for (int i = 0; i < kFzNF * kFzNT; ++i) fz.tap2[2 * i] = fz.tap2[2 * i + 1] = (float)taps_re[i];
   const dim3 grid((unsigned)B), block(kModThreads);
-  // Scan segment length / resident blocks per SM of the fused instance.  Short segments keep the scan arrays small
-  // (8 B per symbol interval), which is what lets 4 blocks of (scan arrays + 36 KB sample tile) share an SM.
-  static int variant = -1;
-  if (variant < 0) {
-    const char* ev = getenv("WF_FUSE_VARIANT");
-    variant = ev ? atoi(ev) : 3;
-    if (variant < 1 || variant > 3) variant = 3;
-  }
-#define WF_FZ_LAUNCH(NOISE_, MINB_, FSEG_, KS_)                                                                 \
+  // 2048-interval scan segments keep the scan arrays at 16.6 KB (8 B per symbol interval): with the 35.7 KB sample
+  // tile that is 52 KB per block, four blocks per SM at 64 registers -- the occupancy the produce phase wants.
+  // Measured alternatives (profiles/r1p_fused_variants.log): 5120-interval segments at 2 blocks/SM 8.81 ms, 1024 at 3
+  // 8.36, 1024 at 4 8.28, this one 8.11 ms per 65536 frames; the bank phase split by filter over all eight warps
+  // 8.34; eight modulator warps + four dedicated bank warps on two tiles (named barriers, 2 blocks/SM) 8.36.
+#define WF_FZ_LAUNCH(NOISE_)                                                                                \
   do {                                                                                                      \
-    auto kfn = cpm_modulate_f32s8_kernel<8, NOISE_, 8, MINB_, false, true, FSEG_, KS_>;                     \
-    cudaError_t e = cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)fz_smem_bytes(FSEG_)); \
+    auto kfn = cpm_modulate_f32s8_kernel<8, NOISE_, 8, 4, false, true, kFzSeg>;                             \
+    cudaError_t e = cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kFzSmemBytes); \
     if (e != cudaSuccess) return cuda_fail(e, "cudaFuncSetAttribute(cpm_modulate_f32s8_kernel fused)");    \
-    kfn<<<grid, block, fz_smem_bytes(FSEG_), stream>>>(p, fz);                                             \
+    kfn<<<grid, block, kFzSmemBytes, stream>>>(p, fz);                                                     \
   } while (0)
-  if (!d_sigma) WF_FZ_LAUNCH(false, 4, 2048, true);
-  else if (variant == 1) WF_FZ_LAUNCH(true, 4, 2048, false);
-  else if (variant == 2) WF_FZ_LAUNCH(true, 4, 1024, true);
-  else WF_FZ_LAUNCH(true, 4, 2048, true);
+  if (d_sigma) WF_FZ_LAUNCH(true);
+  else WF_FZ_LAUNCH(false);
 #undef WF_FZ_LAUNCH
   WF_LAUNCH_CHECK("cpm_modulate_f32s8_kernel (fused bank)");
   return WF_OK;
