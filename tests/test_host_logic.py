@@ -133,6 +133,30 @@ def test_bank_tables_and_instants():
         assert calls == inst.size and (calls == 0 or first == inst[0]), (n, sps, off, length)
 
 
+def test_fused_modulate_bank_shape_query():
+    """wf_cpm_modulate_bank_supported is pure host arithmetic: the SOQPSK-TG / PAM shape at sps 8 is covered for
+    every frame length, anything else is refused (the caller then runs wf_cpm_modulate + wf_mf_bank); the compute
+    entry point itself fails loudly without a GPU."""
+    lib = _ffi.lib()
+    K = freq_pulse_soqpsk_tg(8).size
+    for S in (1, 95, 511, 512, 4096, 5119, 5120, 7000, 100000):
+        first, calls = mfbank.symbol_instants((S + 1) * 8, 8, 0, 2)
+        assert lib.wf_cpm_modulate_bank_supported(K, 8, 2, 73, 36, first, S, calls) == 1, S
+    first, calls = mfbank.symbol_instants(4097 * 8, 8, 0, 2)
+    assert lib.wf_cpm_modulate_bank_supported(K, 8, 2, 73, 36, first, 4096, 4600) == 1      # last call the chunks cover
+    assert lib.wf_cpm_modulate_bank_supported(K, 8, 2, 73, 36, first, 4096, 4601) == 0      # one call too many
+    assert lib.wf_cpm_modulate_bank_supported(K, 10, 2, 91, 45, first, 4096, calls) == 0     # sps 10
+    assert lib.wf_cpm_modulate_bank_supported(K, 8, 3, 9, 4, first, 4096, calls) == 0        # PT bank
+    assert lib.wf_cpm_modulate_bank_supported(K, 8, 2, 73, 36, 5, 4096, calls) == 0          # odd tile origin
+    assert lib.wf_cpm_modulate_bank_supported(freq_pulse_pcmfm(8).size, 8, 2, 73, 36, first, 4096, calls) == 0
+    assert lib.wf_cpm_modulate_bank_supported(freq_pulse_soqpsk_b(8).size, 8, 2, 73, 36, first, 4096, calls) == 0
+    if not torch.cuda.is_available():
+        h, g, t = _ffi.dbl_array([0.25]), _ffi.dbl_array(freq_pulse_soqpsk_tg(8)), _ffi.dbl_array(np.zeros(146))
+        rc = lib.wf_cpm_modulate_bank(ctypes.c_void_p(16), 1, 16, h, 1, g, K, 8, 0.0, 0.0, None, None, 0, 0, t, 2, 73, 36, 0,
+                                      15, ctypes.c_void_p(16), 16, None)
+        assert rc == -2  # WF_ERR_DEVICE
+
+
 # ---- sweep arithmetic ---------------------------------------------------------------------
 def test_shard_range_partitions():
     for n in (0, 1, 7, 8, 65536, 1000003):
