@@ -1,14 +1,20 @@
 #!/usr/bin/env python
 """bench.py -- Viterbi-decoded SOQPSK-TG bits/s of the link-simulation hot path.
 
-    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference]
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference] [--unfused]
     python -m torch.distributed.run --nnodes=1 --nproc-per-node N ... bench.py --gpus N ...
+    python bench.py --sweep 1024,4096,...,1048576 [--sweep-out profiles/r2_sweep_n1.json]   (BASELINE configs[4])
 
 One step = one pass of the whole chain (PRBS+precode -> CPM modulate + AWGN -> PAM
 matched-filter bank -> Viterbi + error count) over one batch of synthetic frames per GPU
 (BASELINE.json configs[4], largest single-GPU batch: 65536 frames x 4096 PN15 bits,
 sps 8, Eb/N0 6 dB).  Weak scaling: every rank runs its own batch of distinct frames;
 the only cross-GPU traffic is the final counter all-reduce.  Rank 0 prints ONE JSON line.
+
+--sweep runs BASELINE configs[4] as written: a FIXED TOTAL of B frames, B in
+{2^10 .. 2^20}, split over the N ranks (strong scaling), each point timed (a) device-resident and
+(b) through LinkSimulator.sweep() with host inputs / outputs and the NCCL counter all-reduce inside
+the timed region, so that the launch-latency floor of small batches is visible, not hidden.
 """
 from __future__ import annotations
 
@@ -31,11 +37,12 @@ METRIC = "viterbi_decoded_bits_per_s_soqpsk_tg"
 # bank's two raw filter outputs between bank and detector (16 B per call), so the
 # bank moves 64 + 16 and the detector 16 + 1/8 bytes per bit (SURVEY's reference-shaped [calls, 3]
 # array would be 64 + 24 and 24 + 1/8).
-# The fused modulate+AWGN+bank kernel (wf_cpm_modulate_bank, the default link) reads 1 B and writes the
-# 16 B of raw bank outputs per bit: the 64 B/bit baseband stays in shared memory.
+# The fused modulate+AWGN+bank kernel (wf_cpm_modulate_bank, chosen with --fused / --unfused, see DEFAULT_FUSED)
+# reads 1 B and writes the 16 B of raw bank outputs per bit: the 64 B/bit baseband stays in shared memory.
 ALGO_BYTES_PER_BIT = {"prbs_encode": 1.125, "modulate_awgn": 65.0, "mf_bank": 80.0, "viterbi_bert": 16.125,
                       "modulate_awgn_bank": 17.0}
 # what ncu shows each stage is limited by (profiles/*_ncu_full_summary.csv)
+DEFAULT_FUSED = False
 BOUND = {"prbs_encode": "alu pipe (integer LFSR / precoder work, ~1 B/bit of HBM)",
          "modulate_awgn": "xu pipe + issue (12 MUFU per sample pair: sin/cos of the signal, Box-Muller); HBM write 62 %",
          "mf_bank": "hbm",
@@ -139,6 +146,90 @@ def cpu_reference_line(args, as_main):
             "e2e": {"value": value, "unit": "bits/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
 
 
+def sweep_mode(args, sim_factory, dev, rank, world, local_rank, barrier, emit):
+    """BASELINE configs[4]: fixed TOTAL frame counts split over the ranks (strong scaling)."""
+    import torch
+    import torch.distributed as dist
+
+    from waveforms_b200.linksim import shard_range
+    from waveforms_b200.noise import sigma_from_ebn0_db
+
+    totals = [int(x) for x in args.sweep.split(",")]
+    rows = []
+    sigma_v = float(sigma_from_ebn0_db(EBN0_DB, SPS))
+    sim = None
+    for total in totals:
+        lo, hi = shard_range(total, rank, world)
+        n_loc = hi - lo
+        mb = max(1, min(n_loc, FRAMES_PER_GPU))
+        if sim is None or sim.max_batch != mb:
+            sim = None
+            torch.cuda.empty_cache()
+            sim = sim_factory(mb)
+        sigma = torch.full((mb,), sigma_v, dtype=torch.float32, device=dev)
+        point = torch.zeros((mb,), dtype=torch.int32, device=dev)
+        counters = torch.zeros((1, 3), dtype=torch.int64, device=dev)
+
+        def one_pass(base):
+            for f0 in range(0, n_loc, mb):
+                b = min(mb, n_loc - f0)
+                sim.run_batch(base + lo + f0, sigma[:b], point[:b], counters)
+
+        reps = max(3, min(200, int(3e5 // max(total, 1))))
+        for w in range(3):
+            one_pass(w * total)
+        barrier()
+        t0, t1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        t0.record(torch.cuda.current_stream(dev))
+        for r in range(reps):
+            one_pass((3 + r) * total)
+        t1.record(torch.cuda.current_stream(dev))
+        barrier()
+        t = torch.tensor([t0.elapsed_time(t1) / reps], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        dev_ms = float(t.item())
+        # end to end: host Eb/N0 in, host counters out, counter all-reduce inside
+        for w in range(2):
+            sim.sweep([EBN0_DB], total, first_frame=w * total)
+        barrier()
+        w0 = time.perf_counter()
+        for r in range(reps):
+            sim.sweep([EBN0_DB], total, first_frame=(2 + r) * total)
+        torch.cuda.synchronize(dev)
+        te = torch.tensor([(time.perf_counter() - w0) / reps], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(te, op=dist.ReduceOp.MAX)
+        e2e_ms = float(te.item()) * 1e3
+        rows.append({"total_frames": total, "n_gpus": world, "frames_per_gpu": n_loc if world == 1 else [total // world, -(-total // world)],
+                     "reps": reps, "device_ms": dev_ms, "device_bits_per_s": total * N_BITS / (dev_ms * 1e-3),
+                     "e2e_ms": e2e_ms, "e2e_bits_per_s": total * N_BITS / (e2e_ms * 1e-3),
+                     "launches_per_pass": len(sim.stage_names) * -(-max(n_loc, 1) // mb)})
+    if rank == 0:
+        out = {"metric": METRIC, "unit": "bits/s", "n_gpus": world, "scaling": "strong", "link": "fused" if sim.fused else "four kernels",
+               "config": {"workload": f"BASELINE configs[4] throughput sweep: total frames x {N_BITS} PN15 bits, sps {SPS}, "
+                                      f"Eb/N0 {EBN0_DB} dB, {DETECTOR} bank; total frames split over {world} GPU(s)"},
+               "points": rows}
+        if args.sweep_cpu and world == 1:
+            from oracle import cpu_bench
+            cores = os.cpu_count() or 1
+            cpu = []
+            for total in totals:
+                if total <= args.sweep_cpu:
+                    r = cpu_bench.run(total, n_bits=N_BITS, sps=SPS, ebn0_db=EBN0_DB, detector=DETECTOR, cores=cores)
+                    cpu.append({"total_frames": total, "seconds": r["seconds"], "bits_per_s": r["bits_per_s"], "measured": True})
+                elif cpu:
+                    cpu.append({"total_frames": total, "seconds": total * N_BITS / cpu[-1]["bits_per_s"],
+                                "bits_per_s": cpu[-1]["bits_per_s"], "measured": False})
+            out["cpu_port"] = {"cores": cores, "kind": "port", "points": cpu,
+                               "note": "oracle port on all host cores; points beyond --sweep-cpu frames are the last measured rate extrapolated"}
+        if args.sweep_out:
+            os.makedirs(os.path.dirname(os.path.abspath(args.sweep_out)), exist_ok=True)
+            with open(args.sweep_out, "w") as f:
+                json.dump(out, f, indent=1)
+        emit(out)
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -147,8 +238,13 @@ def main():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--frames", type=int, default=FRAMES_PER_GPU, help="frames per GPU per step")
     ap.add_argument("--no-cpu-baseline", action="store_true")
-    ap.add_argument("--fused", action="store_true", help="fused modulate+AWGN+bank kernel (baseband stays in shared memory) instead of the four-kernel link")
+    ap.add_argument("--fused", action="store_true", help="fused modulate+AWGN+bank kernel (baseband stays in shared memory)")
+    ap.add_argument("--unfused", action="store_true", help="four-kernel link (baseband through HBM)")
+    ap.add_argument("--sweep", default=None, help="comma-separated TOTAL frame counts: BASELINE configs[4], strong scaling")
+    ap.add_argument("--sweep-out", default=None, help="also write the sweep result to this JSON file")
+    ap.add_argument("--sweep-cpu", type=int, default=0, help="time the CPU port for totals up to this many frames (N=1 only)")
     args = ap.parse_args()
+    fused = (DEFAULT_FUSED or args.fused) and not args.unfused
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     # stdout carries exactly ONE JSON line: anything a library writes to fd 1 on the way
@@ -167,7 +263,7 @@ def main():
 
     # the CPU baseline forks worker processes: take it BEFORE this process owns a CUDA context
     cpu_line = None
-    if world == 1 and rank == 0 and not args.no_cpu_baseline:
+    if world == 1 and rank == 0 and not args.no_cpu_baseline and not args.sweep:
         cpu_line = cpu_reference_line(args, as_main=False)
 
     import torch
@@ -188,9 +284,19 @@ def main():
             dist.barrier(device_ids=[local_rank])
         torch.cuda.synchronize(dev)
 
+    def sim_factory(max_batch):
+        return LinkSimulator(LinkConfig(n_bits=N_BITS, sps=SPS, detector=DETECTOR, extra={"fused": fused}),
+                             device=dev, max_batch=max_batch)
+
+    if args.sweep:
+        sweep_mode(args, sim_factory, dev, rank, world, local_rank, barrier, emit)
+        if world > 1:
+            dist.barrier(device_ids=[local_rank])
+            dist.destroy_process_group()
+        return
+
     B, K, W = args.frames, args.steps, max(args.warmup, 3)
-    sim = LinkSimulator(LinkConfig(n_bits=N_BITS, sps=SPS, detector=DETECTOR, extra={"fused": args.fused}),
-                        device=dev, max_batch=B)
+    sim = sim_factory(B)
     KERNELS = list(sim.stage_names)
     NK = len(KERNELS)
     sigma = torch.full((B,), float(sigma_from_ebn0_db(EBN0_DB, SPS)), dtype=torch.float32, device=dev)
@@ -198,22 +304,20 @@ def main():
     counters = torch.zeros((1, 3), dtype=torch.int64, device=dev)
     frame_of = lambda step: (step * world + rank) * B  # noqa: E731  distinct frames per rank and step
 
-    # ---------------- device-resident loop: `value` ------------------------------------
+    # ---------------- device-resident loop: `value` (no events inside the timed region) ----------
     for s in range(W):
         sim.run_batch(frame_of(s), sigma, point, counters)
     barrier()
     sampler = ClockSampler(local_rank) if rank == 0 else None
     launches0 = sim.launches
-    events = []
     t0, t1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     counters.zero_()
     barrier()
     t0.record(torch.cuda.current_stream(dev))
     for s in range(K):
-        sim.run_batch(frame_of(W + s), sigma, point, counters, events=events)
+        sim.run_batch(frame_of(W + s), sigma, point, counters)
     t1.record(torch.cuda.current_stream(dev))
     barrier()
-    clocks = sampler.stop() if sampler else None
     elapsed_ms = t0.elapsed_time(t1)
     launches = sim.launches - launches0
     t = torch.tensor([elapsed_ms], dtype=torch.float64, device=dev)
@@ -222,6 +326,15 @@ def main():
         dist.all_reduce(counters, op=dist.ReduceOp.SUM)  # the path's one collective
     elapsed_ms = float(t.item())
     bit_err, _, compared = counters[0].tolist()
+
+    # ---------------- per-kernel pass: the same K steps again with CUDA events between the launches
+    # (same stream, clocks still sampled) -- kept OUT of the region `value` is timed over
+    events = []
+    scratch = torch.zeros_like(counters)
+    for s in range(K):
+        sim.run_batch(frame_of(W + s), sigma, point, scratch, events=events)
+    barrier()
+    clocks = sampler.stop() if sampler else None
     per_kernel_ms = [statistics.fmean(events[(NK + 1) * s + k].elapsed_time(events[(NK + 1) * s + k + 1]) for s in range(K))
                      for k in range(NK)]
 
@@ -247,7 +360,9 @@ def main():
         name = KERNELS[dom]
         algo_bytes = ALGO_BYTES_PER_BIT[name] * B * N_BITS
         achieved = algo_bytes / (per_kernel_ms[dom] * 1e-3) / 1e9
-        # measured DRAM bytes per launch (ncu --set full, tools/ncu_summary.py), scaled to this batch
+        # measured DRAM bytes per launch: NOT measured by this run (ncu cannot run inside the timed bench);
+        # taken from profiles/traffic.json = one `ncu --set full` launch per stage kernel captured on the same
+        # tree by tools/ncu_summary.py at `frames` frames, scaled linearly to this batch (traffic_source says so)
         tpath = os.path.join(ROOT, "profiles", "traffic.json")
         tj_all = {}
         if os.path.exists(tpath):
@@ -258,6 +373,13 @@ def main():
             tj = tj_all.get(stage)
             return tj["dram_bytes_per_launch"] * (B / tj["frames"]) if tj and tj.get("frames") else None
 
+        def traffic_src(stage):
+            tj = tj_all.get(stage)
+            if not (tj and tj.get("frames")):
+                return None
+            return (f"profiles/traffic.json: ncu --set full, one launch at {tj['frames']} frames "
+                    f"({tj.get('source', 'source?')}), scaled x{B / tj['frames']:g} to this batch")
+
         traffic = traffic_of(name)
         line = {
             "metric": METRIC, "value": value, "unit": "bits/s", "n_gpus": world, "steps": K, "warmup": W,
@@ -267,7 +389,8 @@ def main():
             "e2e": {"value": bits_per_step * K / e2e_s, "unit": "bits/s", "h2d_bytes_per_step": B * 8,
                     "d2h_bytes_per_step": int(host_counts.nbytes)},
             "roofline": {"bound": "hbm", "kernel": name, "achieved": achieved, "peak": peak, "unit": "GB/s",
-                         "frac": achieved / peak, "traffic": traffic, "peak_source": peak_src,
+                         "frac": achieved / peak, "traffic": traffic, "traffic_source": traffic_src(name),
+                         "peak_source": peak_src,
                          "algorithmic_bytes_per_bit": ALGO_BYTES_PER_BIT[name], "binding_resource": BOUND[name]},
             "link": "fused (prbs | modulate+awgn+bank | viterbi+bert)" if sim.fused else "four kernels",
             "kernels": {KERNELS[k]: {"ms": per_kernel_ms[k],
@@ -276,6 +399,7 @@ def main():
                                      "algorithmic_bytes": ALGO_BYTES_PER_BIT[KERNELS[k]] * B * N_BITS,
                                      "traffic": traffic_of(KERNELS[k]), "bound": BOUND[KERNELS[k]],
                                      "share": per_kernel_ms[k] / sum(per_kernel_ms)} for k in range(NK)},
+            "per_kernel_timing": "separate pass of the same K steps with CUDA events between launches (not inside the region `value` is timed over)",
             "clocks": clocks,
             "ber": {"ebn0_db": EBN0_DB, "bit_errors": bit_err, "compared": compared,
                     "ber": bit_err / compared if compared else None},

@@ -23,7 +23,7 @@
 extern "C" {
 #endif
 
-#define WF_ABI_VERSION 1
+#define WF_ABI_VERSION 2
 
 #if defined(__GNUC__)
 #define WF_API __attribute__((visibility("default")))
@@ -108,14 +108,17 @@ WF_API int wf_trellis_encode(const uint8_t* d_bits_in, int64_t B, int64_t N,
  * phase[n] = 2pi/sps * cumsum(convolve(upsampled, pulse, "same"))[n] + initial_phase;
  * the output is exp(j(phase + derotate)) (derotate = -pi/4 reproduces
  * examples/soqpsk_detection.py:85; 0 = plain cpm_modulate).
- * When d_sigma != NULL complex AWGN is added in the same pass (see wf_awgn_add). */
+ * When d_sigma != NULL complex AWGN is added in the same pass (see wf_awgn_add).
+ * d_frame_ids uint64[B] (may be NULL): the GLOBAL frame id of every row, which keys its noise
+ * stream; NULL means row b is frame first_frame + b.  With it one launch can carry frames of
+ * several Eb/N0 points (LinkSimulator.run packs a whole small sweep into one batch). */
 WF_API int wf_cpm_modulate(const int8_t* d_syms, int64_t B, int64_t S,
                     const double* mod_index, int n_h,
                     const double* pulse, int K, int sps,
                     double initial_phase, double derotate,
                     int dtype, void* d_out, int64_t ld_out,
                     const float* d_sigma, const int32_t* d_point,
-                    uint64_t seed, uint64_t first_frame, void* stream);
+                    uint64_t seed, uint64_t first_frame, const uint64_t* d_frame_ids, void* stream);
 
 /* Fused cpm_modulate -> + AWGN -> decimated real-tap bank (examples/soqpsk_detection.py:78-90 followed by
  * the PAM bank of :158-173) in ONE kernel: the noisy baseband stays in shared memory, only the bank's
@@ -131,7 +134,7 @@ WF_API int wf_cpm_modulate_bank(const int8_t* d_syms, int64_t B, int64_t S,
                     const double* pulse, int K, int sps,
                     double initial_phase, double derotate,
                     const float* d_sigma, const int32_t* d_point,
-                    uint64_t seed, uint64_t first_frame,
+                    uint64_t seed, uint64_t first_frame, const uint64_t* d_frame_ids,
                     const double* taps_re, int n_filt, int n_taps, int center,
                     int64_t first_instant, int64_t n_calls,
                     void* d_z, int64_t ld_z, void* stream);
@@ -147,17 +150,26 @@ WF_API int wf_phase_modulate(const double* d_phase, int64_t n, double sensitivit
                              void* stream);
 
 /* generate_complex_awgn(sigma, size) added in place: d_sig[b][n] += sigma[b] *
- * (N(0,1) + j N(0,1)).  Philox4x32-10, key = seed, counter = (n/2, global frame
- * first_frame+b, point d_point[b] (0 if NULL), 0): two complex samples per
- * counter, so results do not depend on batching or sharding.
- * d_sigma float[B] (sigma per real component, as in noise.py). */
+ * (N(0,1) + j N(0,1)), sigma per real component as in noise.py.  The noise of a sample depends
+ * only on (seed, point, global frame, sample index) -- never on batching or sharding:
+ *   Philox4x32-10, key = (seed lo, seed hi), counter = (call, frame lo, frame hi ^ (call hi << 16), point).
+ *   One call yields FOUR 32-bit words = FOUR complex samples.  Sample pair q (samples 2q, 2q+1) uses
+ *   call(q) = 4 (q >> 3) + (q & 3) and its words (x, y) when (q & 4) == 0, else (z, w): pairs q and
+ *   q ^ 4 (the same offset inside two neighbouring sps-8 symbol intervals) share a call.
+ *   Word w -> one complex sample: radius uniform u = ((w & 0xFFFF) + 0.5) 2^-16 (when the 16-bit field
+ *   is 0, u = (t + 0.5) 2^-48 with t the matching word of the call whose counter has bit 31 of
+ *   `point` set), angle = ((w >> 16) + 0.5) 2 pi 2^-16 - pi,
+ *   sample = sigma sqrt(-2 ln u) (cos angle + j sin angle).
+ * Global frame of row b: d_frame_ids[b] when given, else first_frame + b.
+ * d_sigma float[B]; d_point int32[B] (0 if NULL). */
 WF_API int wf_awgn_add(void* d_sig, int dtype, int64_t B, int64_t T, int64_t ld,
                 const float* d_sigma, const int32_t* d_point,
-                uint64_t seed, uint64_t first_frame, void* stream);
+                uint64_t seed, uint64_t first_frame, const uint64_t* d_frame_ids, void* stream);
 
 /* raw N(0,1) pairs, for statistical tests: d_out float2[B][T] */
 WF_API int wf_awgn_fill(float* d_out, int64_t B, int64_t T, const float* d_sigma,
-                 const int32_t* d_point, uint64_t seed, uint64_t first_frame, void* stream);
+                 const int32_t* d_point, uint64_t seed, uint64_t first_frame, const uint64_t* d_frame_ids,
+                 void* stream);
 
 /* ---- A8/A9  decimated matched-filter bank:
  *      examples/soqpsk_detection.py:134-173 (np.convolve(rx, taps, "same") then
@@ -224,7 +236,9 @@ WF_API int wf_bert(const uint8_t* d_dec_bits, const int8_t* d_dec_syms, int64_t 
  * h = h_num[k % n_h] / p.  State count 2p * M^(Lp-1) <= 256; register-exchange survivors of
  * `depth` symbols (0 -> min(32, 64 / log2 M)).  Outputs: d_dec_syms int8[B][n_steps] (alphabet values,
  * may be NULL) and, when d_tx_syms int8[B][S] is given, counters[point][3] += (bit errors,
- * symbol errors, compared symbols) over symbols [skip_head, min(S, n_steps) - skip_tail). */
+ * symbol errors, compared BITS = log2(M) per compared symbol) over symbols
+ * [skip_head, min(S, n_steps) - skip_tail): column 0 / column 2 is a bit-error ratio for every
+ * waveform, exactly as in wf_viterbi_soqpsk. */
 WF_API int wf_viterbi_cpm(const void* d_z, int dtype, int64_t B, int64_t n_steps, int64_t ld_z,
                           int M, int Lp, int p, const int32_t* h_num, int n_h, int depth,
                           int8_t* d_dec_syms, const int8_t* d_tx_syms, int64_t S,

@@ -76,10 +76,16 @@ class CpmTrellis:
             z[i] = tpl @ seg
         return z
 
-    def detect(self, z, depth=None):
+    def detect(self, z, depth=None, return_margin=False):
         """Register-exchange Viterbi, maximising sum Re{e^{-j pi v/p} z}.  z complex[n_steps, n_h*n_filt].
         Returns symbol INDICES (0..M-1) uint8[n_steps]; decision delay = depth-1 steps, the tail is
-        flushed from the best final state.  All states start equal (unknown start)."""
+        flushed from the best final state.  All states start equal (unknown start).
+
+        ``return_margin``: also return float64[n_steps, 2] = per step (smallest gap between the best and
+        the runner-up candidate over all states and between the two largest new path metrics, largest
+        |candidate|).  The decision for symbol k leaves the survivor memory at step k + depth - 1, so a
+        float32 detector may differ at k only if some step in [k, k + depth) has a margin at float32
+        resolution."""
         M, Lp, p2 = self.M, self.Lp, 2 * self.p
         bits = max(1, (M - 1).bit_length())
         D = depth or min(32, 64 // bits)
@@ -89,6 +95,7 @@ class CpmTrellis:
         hist = np.zeros(NS, dtype=np.uint64)
         rot = np.exp(-1j * np.pi * np.arange(p2) / self.p)
         out = np.zeros(n_steps, dtype=np.uint8)
+        marg = np.zeros((n_steps, 2))
         mask = np.uint64((1 << 64) - 1) if D * bits >= 64 else np.uint64((1 << (D * bits)) - 1)
         sp = np.arange(NS)
         vnew, hnew = sp // NH, sp % NH          # next state = (v', [a_0 .. a_{Lp-2}])
@@ -97,8 +104,10 @@ class CpmTrellis:
             K_leave = self.h_num[(i - Lp + 1) % self.n_h]
             zi = z[i, par * self.n_filt:(par + 1) * self.n_filt]
             best = np.full(NS, -np.inf)
+            second = np.full(NS, -np.inf)
             arg = np.zeros(NS, dtype=np.int64)
             argx = np.zeros(NS, dtype=np.int64)
+            amax = 0.0
             for x in range(M):                   # x = index of the symbol leaving the window
                 vpred = (vnew - K_leave * self.alphabet[x]) % p2
                 if Lp == 1:
@@ -108,16 +117,23 @@ class CpmTrellis:
                     f = hnew * M + x
                 cand = pm[pred] + np.real(rot[vpred] * zi[f])
                 take = cand > best               # strict: the lowest x wins ties
+                second = np.where(take, best, np.maximum(second, cand))
+                amax = max(amax, float(np.max(np.abs(cand))))
                 best = np.where(take, cand, best)
                 arg = np.where(take, pred, arg)
                 argx = np.where(take, x, argx)
             newest = argx if Lp == 1 else hnew // (NH // M)   # symbol index of step i
             hist = ((hist[arg] << np.uint64(bits)) | newest.astype(np.uint64)) & mask
             pm = best - best.max()
+            if return_margin:
+                top = np.sort(best)
+                marg[i] = (min(float(np.min(best - second)), float(top[-1] - top[-2])), amax)
             if i >= D - 1:
                 s = int(np.argmax(pm))
                 out[i - D + 1] = int((hist[s] >> np.uint64((D - 1) * bits)) & np.uint64((1 << bits) - 1))
         s = int(np.argmax(pm))
         for d in range(min(D - 1, n_steps)):
             out[n_steps - 1 - d] = int((hist[s] >> np.uint64(d * bits)) & np.uint64((1 << bits) - 1))
+        if return_margin:
+            return out, marg
         return out

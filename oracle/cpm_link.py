@@ -451,12 +451,18 @@ def detect_soqpsk(z_calls, length=2, diff=True):
     return bits, syms
 
 
-def detect_soqpsk_fast(z_calls, diff=True):
+def detect_soqpsk_fast(z_calls, diff=True, return_margin=False):
     """length=2 detector in the compact form of SURVEY Appendix A, vectorised
     over a leading batch axis: z_calls complex [..., calls, 3].  Identical
     float64 operation order per frame (Mn = M - min; stage A with previous
     increments; stage B with current; first-min ties) so decisions are
-    bit-identical to ``detect_soqpsk`` -- asserted in tests."""
+    bit-identical to ``detect_soqpsk`` -- asserted in tests.
+
+    ``return_margin``: also return, per call, the smallest float64 decision margin (the
+    |difference| of the two candidates of each of the 8 compare-selects and the gap argmin
+    separates) and the largest |candidate| -- the quantities oracle/make_golden.py:acs_margin
+    freezes from the reference object (G5/G7/G11 ``*_margin`` / ``*_scale``).  A float32 detector
+    may differ from this one only on calls whose margin/scale is at float32 resolution."""
     z = np.asarray(z_calls)
     batch = z.shape[:-2]
     n = z.shape[-2]
@@ -473,6 +479,8 @@ def detect_soqpsk_fast(z_calls, diff=True):
     bits = np.zeros(batch + (n,), dtype=np.uint8)
     syms = np.zeros(batch + (n,), dtype=np.int8)
     rot = np.array(_STATE_ROT)
+    margin = np.zeros(batch + (n,))
+    scale = np.zeros(batch + (n,))
     for c in range(n):
         col = cols[c % 2]
         bcur = np.stack(
@@ -489,6 +497,10 @@ def detect_soqpsk_fast(z_calls, diff=True):
             m1 = Mn[..., s1] + bprev[..., b1]
             m2 = Mn[..., s2] + bprev[..., b2]
             second = m2 < m1
+            if return_margin:
+                d, a = np.abs(m1 - m2), np.maximum(np.abs(m1), np.abs(m2))
+                margin[..., c] = d if st == 0 else np.minimum(margin[..., c], d)
+                scale[..., c] = a if st == 0 else np.maximum(scale[..., c], a)
             M0[..., st] = np.where(second, m2, m1)
             p0[..., st] = np.where(second, s2, s1)
             bitA[..., st] = np.where(second, i2, i1)
@@ -500,13 +512,21 @@ def detect_soqpsk_fast(z_calls, diff=True):
             m1 = M0[..., s1] + bcur[..., b1]
             m2 = M0[..., s2] + bcur[..., b2]
             second = m2 < m1
+            if return_margin:
+                margin[..., c] = np.minimum(margin[..., c], np.abs(m1 - m2))
+                scale[..., c] = np.maximum(scale[..., c], np.maximum(np.abs(m1), np.abs(m2)))
             M1[..., st] = np.where(second, m2, m1)
             p1[..., st] = np.where(second, s2, s1)
         s1st = np.argmin(M1, axis=-1)
         s0 = np.take_along_axis(p1, s1st[..., None], axis=-1)
         bits[..., c] = np.take_along_axis(bitA, s0, axis=-1)[..., 0]
         syms[..., c] = np.take_along_axis(symA, s0, axis=-1)[..., 0]
+        if return_margin:
+            fin = np.sort(M1, axis=-1)
+            margin[..., c] = np.minimum(margin[..., c], fin[..., 1] - fin[..., 0])
         M, bprev = M0, bcur
+    if return_margin:
+        return bits, syms, margin, scale
     return bits, syms
 
 
@@ -544,12 +564,13 @@ def soqpsk_link_frame(bits, pulse, sps, sigma, rng=None, noise=None, detector="P
     mf = pt_bank(rx, pulse, mod_index, sps) if detector == "PT" else pam_bank(rx, pulse, mod_index, sps)
     inst = symbol_instants(rx.size, sps, timing_offset, length)
     z = mf[:, inst].T
+    margin = scale = None
     if fast and length == 2:
-        db, ds = detect_soqpsk_fast(z, diff)
+        db, ds, margin, scale = detect_soqpsk_fast(z, diff, return_margin=True)
     else:
         db, ds = detect_soqpsk(z, length, diff)
     be, se, n = count_errors(db, ds, bits, syms, length)
     if return_all:
         return dict(bits=bits, symbols=syms, signal=s, rx=rx, z=z, dec_bits=db,
-                    dec_syms=ds, bit_errors=be, sym_errors=se, compared=n)
+                    dec_syms=ds, bit_errors=be, sym_errors=se, compared=n, margin=margin, scale=scale)
     return be, se, n

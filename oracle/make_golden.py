@@ -63,18 +63,44 @@ def banks(rx, pulse, h, sps):
     return pt, pam, rho
 
 
+def acs_margin(det, carried, i):
+    """Float64 decision margins of the detector call that just ran (call counter was ``i``,
+    ``carried`` = metrics[:, 0] before the call), recomputed from the reference object's own
+    state arrays (algorithm.py:65-90): for every stage j and end state the |difference| of the
+    competing candidate metrics, and the gap between the two smallest final metrics that
+    np.argmin separates (:92).  Returns (smallest margin of the call, largest |candidate|): a
+    float32 detector may legitimately differ from the float64 one only where the first is within
+    rounding of zero relative to the second."""
+    n = det.length
+    prev = carried - carried.min()
+    small, scale = np.inf, 0.0
+    for j in range(n):
+        branches = det.fsm.trellis.branches[(i + j - 1) % det.fsm.columns]
+        for st in range(det.fsm.states):
+            c = [prev[b.start] + det.bi_history[k, j] for k, b in enumerate(branches) if b.end == st]
+            scale = max(scale, max(abs(x) for x in c))
+            c.sort()
+            if len(c) > 1:
+                small = min(small, c[1] - c[0])
+        prev = det.metrics[:, j]
+    fin = np.sort(det.metrics[:, -1])
+    return min(small, fin[1] - fin[0]), scale
+
+
 def drive(mf, n_samples, sps, timing_offset, length=2, diff=True):
     """soqpsk_detection.py:177-198."""
     det = SOQPSKTrellisDetector(length=length, differantial_encoding=diff)
-    ob, osy, inst = [], [], []
+    ob, osy, inst, marg = [], [], [], []
     for n in range(n_samples - det.length * sps):
         if (n + timing_offset) % sps:
             continue
+        carried, i = det.metrics[:, 0].copy(), det.i
         rb, rs = det.iteration(mf[:, n])
         ob.append(rb[0])
         osy.append(rs[0])
         inst.append(n)
-    return np.array(ob), np.array(osy), np.array(inst)
+        marg.append(acs_margin(det, carried, i))
+    return np.array(ob), np.array(osy), np.array(inst), np.array(marg)
 
 
 def tally(ob, osy, bits, symbols, length=2):
@@ -98,11 +124,13 @@ def replay_frame(bits, pulse, sps, sigma, rng, offsets, h=0.25, diff=True, lengt
     rx = sig + noise
     pt, pam, rho = banks(rx, pulse, h, sps)
     out = dict(symbols=symbols, tx=tx, noise=noise, rho0=rho[0], rho1=rho[1])
-    for name, mf in (("PT", pt), ("PAM", pam)):
-        ob, osy, inst = drive(mf, rx.size, sps, offsets[name], length, diff)
+    for name, off in offsets.items():  # "PT", "PAM", or e.g. "PT@-1" for a second timing offset on the same bank
+        mf = pt if name.startswith("PT") else pam
+        ob, osy, inst, marg = drive(mf, rx.size, sps, off, length, diff)
         be, se, n = tally(ob, osy, bits, symbols, length)
         out[name] = dict(z=mf[:, inst].T.copy(), dec_bits=ob.astype(np.uint8),
-                         dec_syms=osy.astype(np.int8), bit_errors=be, sym_errors=se, compared=n)
+                         dec_syms=osy.astype(np.int8), bit_errors=be, sym_errors=se, compared=n,
+                         margin=marg[:, 0].copy(), scale=marg[:, 1].copy())
     return out
 
 
@@ -189,6 +217,18 @@ def main():
     g4["bits"] = b1k
     sv("g4_modulated.npz", **g4)
 
+    # G4b: the configs[1] / configs[2] modulators at the BASELINE frame size (N = 4096 bits, sps 8:
+    # T = 32776 / 16392 samples; TG at this size is G5's tx)
+    b4k = bit_array[:4096]
+    g4b = {"bits": b4k}
+    for lab, (sy, h, g) in {
+        "pcmfm": (TrellisEncoder(tm.SimpleTrellis2)(b4k), PCMFM_NUMER / PCMFM_DENOM, freq_pulse_pcmfm(8, 4)),
+        "multih": (TrellisEncoder(tm.SimpleTrellis4)(b4k), MULTIH_IRIG_NUMER / MULTIH_IRIG_DENOM, freq_pulse_multih_irig(8)),
+    }.items():
+        _t, s = cpm_modulate(symbols=sy, mod_index=h, pulse_filter=g, sps=8)
+        g4b[f"{lab}_8"] = s
+    sv("g4b_modulated_n4096.npz", **g4b)
+
     # G5-G8: BASELINE config 1 (first 4096 PN15 bits, sps 8, TG, 6 dB, PCG64(1))
     sps = 8
     sigma = float(np.sqrt(sps / (2 * 10 ** 0.6)))
@@ -214,8 +254,32 @@ def main():
                 g7[f"{k}_bits_{tag}"] = rr[k]["dec_bits"]
                 g7[f"{k}_syms_{tag}"] = rr[k]["dec_syms"]
                 g7[f"{k}_counts_{tag}"] = np.array([rr[k]["bit_errors"], rr[k]["sym_errors"], rr[k]["compared"]])
+                g7[f"{k}_margin_{tag}"] = rr[k]["margin"]
+                g7[f"{k}_scale_{tag}"] = rr[k]["scale"]
     g7["bits"] = b512
     sv("g7_variants.npz", **g7)
+
+    # G11: SOQPSK-A and -B end to end (soqpsk/pulse_filters.py:53-74; 65 / 129-tap pulses, rho pulses
+    # 73+65 / 137+129 taps): 1024-bit frame, sps 8, 6 dB, PCG64(11), both banks at timing offset 0
+    # (probed: the noiseless replay decodes without error for offsets -2..0 on both)
+    g11 = {}
+    b1024 = bit_array[2000:3024]
+    for lab, f in (("a", freq_pulse_soqpsk_a), ("b", freq_pulse_soqpsk_b)):
+        rng = np.random.Generator(np.random.PCG64(seed=11))
+        rr = replay_frame(b1024, f(8), 8, float(np.sqrt(8 / (2 * 10 ** 0.6))), rng, {"PT": 0, "PAM": 0})
+        g11[f"noise_{lab}"] = rr["noise"]
+        g11[f"symbols_{lab}"] = rr["symbols"]
+        for k in ("PT", "PAM"):
+            g11[f"{lab}_{k}_z"] = rr[k]["z"]
+            g11[f"{lab}_{k}_bits"] = rr[k]["dec_bits"]
+            g11[f"{lab}_{k}_syms"] = rr[k]["dec_syms"]
+            g11[f"{lab}_{k}_counts"] = np.array([rr[k]["bit_errors"], rr[k]["sym_errors"], rr[k]["compared"]])
+            g11[f"{lab}_{k}_margin"] = rr[k]["margin"]
+            g11[f"{lab}_{k}_scale"] = rr[k]["scale"]
+        print("soqpsk-" + lab, {k: tuple(g11[f"{lab}_{k}_counts"]) for k in ("PT", "PAM")})
+    g11["bits"] = b1024
+    g11["sigma"] = float(np.sqrt(8 / (2 * 10 ** 0.6)))
+    sv("g11_soqpsk_ab.npz", **g11)
 
     if not a.skip_example:
         # G8: the example exactly as shipped: sps 10, sigma sqrt(2)/2, MIL then TG

@@ -12,11 +12,14 @@ import torch.multiprocessing as mp
 from waveforms_b200 import linksim
 
 
-def _fake_run(self, ebn0_db, n_frames, first_frame=0):
-    """Counters that depend on every (point, frame) pair individually, like the real chain."""
+def _fake_run(self, ebn0_db, n_frames, first_frame=0, active=None):
+    """Counters that depend on every (point, frame) pair individually, like the real chain
+    (same signature as LinkSimulator.run)."""
     eb = np.atleast_1d(np.asarray(ebn0_db, dtype=np.float64))
     out = np.zeros((eb.size, 3), dtype=np.int64)
     for p in range(eb.size):
+        if active is not None and not active[p]:
+            continue
         f = np.arange(first_frame, first_frame + n_frames, dtype=np.int64)
         out[p, 0] = int(np.sum((f * 2654435761 + p * 40503) % 97))
         out[p, 1] = int(np.sum((f * 40503 + p) % 89))
@@ -135,3 +138,28 @@ def test_waterfall_two_ranks_equals_one_rank():
         p.join(timeout=60)
         assert p.exitcode == 0
     assert np.array_equal(res[0], want) and np.array_equal(res[1], want)
+
+
+# ---------------------------------------------------------------- work list of LinkSimulator.run
+def test_run_work_list_covers_every_point_frame_pair_once():
+    """run() cuts the point-major (point, frame) list into batches that ignore point boundaries:
+    every pair appears exactly once, in order, for any batch size; inactive points get no rows."""
+    pts = np.array([0, 2, 3])  # point 1 inactive
+    n_frames, first = 37, 1000
+    total = pts.size * n_frames
+    for max_batch in (1, 5, 37, 40, 64, 500):
+        seen = []
+        for w0 in range(0, total, max_batch):
+            pw, fw = linksim.work_slice(pts, n_frames, first, w0, min(max_batch, total - w0))
+            seen += list(zip(pw.tolist(), fw.tolist()))
+        assert seen == [(p, first + f) for p in pts for f in range(n_frames)], max_batch
+
+
+def test_run_bit_offsets_are_exact_for_far_frames():
+    sim = object.__new__(linksim.LinkSimulator)
+    sim.cfg = linksim.LinkConfig(n_bits=4096)
+    for degree in (15, 23, 33):
+        sim.period = (1 << degree) - 1
+        frames = np.array([0, 1, 7, 123456789, 2 ** 40 + 3], dtype=np.int64)
+        want = [(int(f) * 4096) % sim.period for f in frames]
+        assert sim._bit_offsets(frames).tolist() == want, degree

@@ -36,9 +36,33 @@ def cu(a, dtype=None):
     return t.to(DEV)
 
 
+REL_TIE = 1e-5  # a float32 decision may differ from the float64 one only where margin < 1e-5
+
+
+def assert_fp32_flips_are_near_ties(dec32, dec64, margin, scale, window=1, what=""):
+    """SURVEY 8(c) acceptance for the float32 path: every decision that differs from the float64
+    detector's must sit on a step whose float64 decision margin (frozen from the reference object by
+    oracle/make_golden.py:acs_margin, or computed by the oracle the same way) is below REL_TIE x the
+    largest candidate metric of that step -- i.e. a genuine near-tie, not an ordering bug.  ``window``:
+    steps [k, k + window) can influence decision k (1 for the SOQPSK detector, the survivor memory for the
+    block-traceback CPM detectors).  Prints the relative-margin histogram."""
+    dec32, dec64 = np.asarray(dec32), np.asarray(dec64)
+    rel = np.asarray(margin, dtype=np.float64) / np.maximum(np.asarray(scale, dtype=np.float64), 1.0)
+    hist = np.histogram(np.log10(np.maximum(rel, 1e-12)), bins=[-12, -7, -6, -5, -4, -3, -2, -1, 1])[0]
+    flips = np.flatnonzero(dec32 != dec64)
+    print(f"{what}: {flips.size} float32 flips of {dec64.size}; relative margin histogram "
+          f"(<1e-7, 1e-7..1e-6, ..1e-5, ..1e-4, ..1e-3, ..1e-2, ..1e-1, >=1e-1) = {hist.tolist()}")
+    for k in flips:
+        m = float(rel[k:k + window].min())
+        assert m < REL_TIE, f"{what}: decision {k} differs but the smallest float64 margin in reach is {m:.3e}"
+    # and near-ties are rare enough that the check has teeth
+    assert np.count_nonzero(rel < REL_TIE) <= max(4, dec64.size // 200), (what, hist.tolist())
+    return flips.size
+
+
 def test_library_is_native_and_loaded():
     lib = _ffi.lib()
-    assert lib.wf_abi_version() == 1
+    assert lib.wf_abi_version() == _ffi.ABI_VERSION
     assert lib.wf_device_check() == 0, lib.wf_last_error_string()
     with open("/proc/self/maps") as f:
         assert "libwfb200.so" in f.read()
@@ -166,6 +190,23 @@ def test_modulators_vs_reference(lab, sps):
     assert np.max(np.abs(s64.cpu().numpy() - ref)) < 1e-10
     if lab == "tg" and sps == 8:
         np.testing.assert_allclose(t.cpu().numpy(), g["time_tg_8"], rtol=0, atol=0)
+
+
+@pytest.mark.parametrize("lab", ["pcmfm", "multih"])
+def test_modulators_vs_reference_at_baseline_size(lab):
+    """BASELINE configs[1] / configs[2] modulators at N = 4096 bits (G4b, produced by the reference):
+    1e-5 for the float32 throughput kernels (PCM/FM takes the ODD fast path), 1e-10 for float64."""
+    g = golden("g4b_modulated_n4096.npz")
+    tre, h, pf = _MOD[lab]
+    sy = cu(o.fsm_encode(o.TRELLISES[tre], g["bits"]))
+    ref = g[f"{lab}_8"]
+    _, s = wmod.cpm_modulate(sy, h, pf(8), 8)
+    assert s.shape == ref.shape and np.max(np.abs(s.cpu().numpy() - ref)) < 1e-5
+    _, s64 = wmod.cpm_modulate(sy, h, pf(8), 8, dtype=torch.complex128)
+    assert np.max(np.abs(s64.cpu().numpy() - ref)) < 1e-10
+    # the same frame inside a batch (other rows = shifted copies) is unchanged
+    syb = torch.stack([sy, torch.roll(sy, 5), torch.roll(sy, 11)])
+    assert torch.equal(wmod.modulate_frames(syb, h, pf(8), 8)[0], s)
 
 
 def test_modulator_long_frames_batch():
@@ -333,11 +374,14 @@ def test_detector_bit_exact_on_reference_noise(det):
     want = [int(g[f"{det}_bit_errors"]), int(g[f"{det}_sym_errors"]), int(g[f"{det}_compared"])]
     assert counters[0].tolist() == want
     assert bert.count_errors(db, tx_bits, 2, dec_symbols=ds, ref_symbols=tx_syms) == tuple(want)
-    # float32 throughput path, same input: decisions may differ only where the float64 ACS
-    # margin is below float32 resolution; on this frame there is no such place
+    # float32 throughput path, same input: decisions may differ only where the reference's own float64
+    # ACS margin (G5 *_margin / *_scale) is at float32 resolution
     z32 = bank(cu(rx, torch.complex64)[None], pulse, 0.25, 8)
-    db32, _ = SOQPSKTrellisDetector().detect(z32)
-    assert int((db32[0].cpu().numpy() != g[f"{det}_dec_bits"]).sum()) <= 1
+    db32, ds32 = SOQPSKTrellisDetector().detect(z32)
+    assert_fp32_flips_are_near_ties(db32[0].cpu().numpy(), g[f"{det}_dec_bits"], g[f"{det}_margin"], g[f"{det}_scale"],
+                                    what=f"config-1 {det} bits")
+    assert_fp32_flips_are_near_ties(ds32[0].cpu().numpy(), g[f"{det}_dec_syms"], g[f"{det}_margin"], g[f"{det}_scale"],
+                                    what=f"config-1 {det} symbols")
 
 
 @pytest.mark.parametrize("diff", [True, False])
@@ -354,6 +398,53 @@ def test_detector_variants(diff, length):
         db, ds = SOQPSKTrellisDetector(length, differantial_encoding=diff).detect(z)
         assert np.array_equal(db[0].cpu().numpy(), g[f"{det}_bits_{tag}"])
         assert np.array_equal(ds[0].cpu().numpy(), g[f"{det}_syms_{tag}"])
+        z32 = bank(cu(r["rx"], torch.complex64)[None], pulse, 0.25, 8, length=length)
+        db32, _ = SOQPSKTrellisDetector(length, differantial_encoding=diff).detect(z32)
+        assert_fp32_flips_are_near_ties(db32[0].cpu().numpy(), g[f"{det}_bits_{tag}"], g[f"{det}_margin_{tag}"],
+                                        g[f"{det}_scale_{tag}"], what=f"G7 {det} {tag}")
+
+
+@pytest.mark.parametrize("lab", ["a", "b"])
+def test_soqpsk_a_b_end_to_end_on_reference_noise(lab):
+    """SOQPSK-A / -B (soqpsk/pulse_filters.py:53-74; B has a 129-tap pulse and 137/129-tap rho
+    pulses) through modulator -> bank -> detector -> count, fed the REFERENCE's own noise (G11): float64
+    instantiation identical on every decision and count, float32 flips only at near-ties."""
+    g = golden("g11_soqpsk_ab.npz")
+    pf = {"a": freq_pulse_soqpsk_a, "b": freq_pulse_soqpsk_b}[lab]
+    pulse = pf(8)
+    syms = TrellisEncoder(tm.SOQPSKTrellis4x2DiffEncoded)(cu(g["bits"]))
+    assert np.array_equal(syms.cpu().numpy(), g[f"symbols_{lab}"])
+    _, s = wmod.cpm_modulate(syms, 0.25, pulse, 8, dtype=torch.complex128)
+    rx = (s * np.exp(-1j * np.pi / 4) + cu(g[f"noise_{lab}"]))[None]
+    pk = cu(np.packbits(g["bits"], bitorder="little").view(np.uint32).view(np.int32))[None]
+    for det, bank in (("PT", mfbank.pt_bank), ("PAM", mfbank.pam_bank)):
+        z = bank(rx, pulse, 0.25, 8)
+        assert np.max(np.abs(z[0].cpu().numpy() - g[f"{lab}_{det}_z"])) < 1e-9
+        counters = torch.zeros((1, 3), dtype=torch.int64, device=DEV)
+        db, ds = SOQPSKTrellisDetector().detect(z, tx_packed=pk, tx_symbols=syms[None], counters=counters)
+        assert np.array_equal(db[0].cpu().numpy(), g[f"{lab}_{det}_bits"])
+        assert np.array_equal(ds[0].cpu().numpy(), g[f"{lab}_{det}_syms"])
+        assert counters[0].tolist() == list(g[f"{lab}_{det}_counts"]), (lab, det)
+        # float32 chain (float32 modulator included: the throughput path end to end)
+        _, s32 = wmod.cpm_modulate(syms, 0.25, pulse, 8)
+        rx32 = (s32 * complex(np.exp(-1j * np.pi / 4)) + cu(g[f"noise_{lab}"], torch.complex64))[None].contiguous()
+        db32, _ = SOQPSKTrellisDetector().detect(bank(rx32, pulse, 0.25, 8))
+        assert_fp32_flips_are_near_ties(db32[0].cpu().numpy(), g[f"{lab}_{det}_bits"], g[f"{lab}_{det}_margin"],
+                                        g[f"{lab}_{det}_scale"], what=f"SOQPSK-{lab.upper()} {det}")
+
+
+@pytest.mark.parametrize("lab", ["a", "b"])
+def test_soqpsk_a_b_link_simulator_noiseless_and_monotone(lab):
+    """LinkSimulator on SOQPSK-A / -B at the BASELINE frame size: noiseless frames decode without error
+    (the reference replay does, offsets -2..0), BER falls with Eb/N0."""
+    for det in ("PAM", "PT"):
+        sim = LinkSimulator(LinkConfig(waveform=f"soqpsk-{lab}", detector=det), device=DEV, max_batch=256)
+        counters = torch.zeros((1, 3), dtype=torch.int64, device=DEV)
+        sim.run_batch(3, torch.zeros(256, dtype=torch.float32, device=DEV), None, counters)
+        assert counters[0].tolist()[::2] == [0, 256 * 4093], (lab, det)
+        got = sim.run([2.0, 6.0, 10.0], 128)
+        ber = got[:, 0] / got[:, 2]
+        assert ber[0] > ber[1] > ber[2] > 0 and ber[2] < 3e-3, (lab, det, ber)
 
 
 def test_detector_streaming_and_odd_windows():
@@ -461,7 +552,7 @@ def test_fused_link_covers_soqpsk_tg_and_other_shapes_fall_back_to_four_kernels(
             assert np.array_equal(sim.run(e, 4), ref.run(e, 4)), kw
         else:
             assert len(sim.stage_names) == 4, kw
-    rc = _ffi.lib().wf_cpm_modulate_bank(None, 1, 16, None, 1, None, 9, 8, 0.0, 0.0, None, None, 0, 0, None, 2, 73, 36, 0,
+    rc = _ffi.lib().wf_cpm_modulate_bank(None, 1, 16, None, 1, None, 9, 8, 0.0, 0.0, None, None, 0, 0, None, None, 2, 73, 36, 0,
                                          15, None, 16, None)
     assert rc < 0  # bad arguments are refused, not run
 
@@ -482,7 +573,23 @@ def test_link_matches_oracle_chain_with_philox_noise():
                                             detector="PAM"))
     got = counters[0].tolist()
     assert got[2] == tot[2]
-    assert abs(got[0] - tot[0]) <= 2  # float32 front end vs float64 oracle (run_batch counts bit errors only)
+    # decision level: the same frames stage by stage through the float32 API (same kernels as run_batch),
+    # every flip against the float64 oracle gated on the oracle's ACS margin; the fused counters must then
+    # equal the errors of exactly these decisions
+    from waveforms_b200.glfsr import PNSequence as _PN
+    bits = _PN(15).frames(40, 8, 1024)
+    syms = TrellisEncoder(tm.SOQPSKTrellis4x2DiffEncoded)(bits)
+    rx = wmod.modulate_frames(syms, [0.25], freq_pulse_soqpsk_tg(8), 8, derotate=-np.pi / 4, sigma=sg, seed=cfg.seed,
+                              first_frame=40).contiguous()
+    db, _ = SOQPSKTrellisDetector().detect(mfbank.pam_bank(rx, freq_pulse_soqpsk_tg(8), 0.25, 8))
+    db = db.cpu().numpy()
+    errs = 0
+    for b in range(8):
+        r = o.soqpsk_link_frame(o.pn_frame_bits(15, 40 + b, 1024), o.pulse_soqpsk_tg(8), 8, sigma,
+                                noise=noise[b].astype(np.complex128), detector="PAM", return_all=True)
+        assert_fp32_flips_are_near_ties(db[b], r["dec_bits"], r["margin"], r["scale"], what=f"Philox frame {40 + b}")
+        errs += int(np.count_nonzero(db[b, 2:2 + 1021] != r["bits"][:1021]))
+    assert got[0] == errs
 
 
 def test_link_batching_independence_and_e2e_host_call():

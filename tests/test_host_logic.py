@@ -31,7 +31,7 @@ def test_library_exports_every_declared_symbol():
     for name in sorted(declared):
         assert hasattr(lib, name), f"{name} declared in wfb200.h but not exported"
     assert declared == set(_ffi.PROTOTYPES), declared ^ set(_ffi.PROTOTYPES)
-    assert _ffi.lib().wf_abi_version() == 1
+    assert _ffi.lib().wf_abi_version() == _ffi.ABI_VERSION
 
 
 @pytest.mark.skipif(torch.cuda.is_available(), reason="checks the no-GPU failure mode")
@@ -48,7 +48,7 @@ def test_no_cpu_fallback():
     h = (ctypes.c_double * 1)(0.5)
     out = np.zeros(40, np.complex64)
     rc = lib.wf_cpm_modulate(syms.ctypes.data, 1, 4, h, 1, pulse, 3, 8, 0.0, 0.0, 0, out.ctypes.data, 40, None, None, 0,
-                             0, None)
+                             0, None, None)
     assert rc == -2 and not out.any()
 
 
@@ -152,7 +152,7 @@ def test_fused_modulate_bank_shape_query():
     assert lib.wf_cpm_modulate_bank_supported(freq_pulse_soqpsk_b(8).size, 8, 2, 73, 36, first, 4096, calls) == 0
     if not torch.cuda.is_available():
         h, g, t = _ffi.dbl_array([0.25]), _ffi.dbl_array(freq_pulse_soqpsk_tg(8)), _ffi.dbl_array(np.zeros(146))
-        rc = lib.wf_cpm_modulate_bank(ctypes.c_void_p(16), 1, 16, h, 1, g, K, 8, 0.0, 0.0, None, None, 0, 0, t, 2, 73, 36, 0,
+        rc = lib.wf_cpm_modulate_bank(ctypes.c_void_p(16), 1, 16, h, 1, g, K, 8, 0.0, 0.0, None, None, 0, 0, None, t, 2, 73, 36, 0,
                                       15, ctypes.c_void_p(16), 16, None)
         assert rc == -2  # WF_ERR_DEVICE
 

@@ -205,3 +205,47 @@ def test_example_replay(pn15_stream):
             assert np.array_equal(np.packbits(r["dec_bits"]), g[f"{lab}_{det}_bits"])
     assert list(g["TG_PT_counts"])[::2] == [14, 32765] and list(g["TG_PAM_counts"])[::2] == [11, 32765]
     assert list(g["MIL_PT_counts"])[::2] == [61, 32765] and list(g["MIL_PAM_counts"])[::2] == [0, 32765]
+
+
+# ---- G4b: configs[1] / configs[2] modulators at the BASELINE frame size (N = 4096)
+@pytest.mark.parametrize("lab", ["pcmfm", "multih"])
+def test_modulators_baseline_size(lab):
+    g = golden("g4b_modulated_n4096.npz")
+    tre, h, pf = _MOD[lab]
+    sy = o.fsm_encode(o.TRELLISES[tre], g["bits"])
+    ref = g[f"{lab}_8"]
+    assert ref.shape == ((sy.size + 1) * 8,) and sy.size == (4096 if lab == "pcmfm" else 2048)
+    assert np.max(np.abs(o.cpm_modulate(sy, h, pf(8), 8)[1] - ref)) < 1e-12
+    assert np.max(np.abs(o.cpm_modulate_closed_form(sy, h, pf(8), 8) - ref)) < 1e-10
+
+
+# ---- G5/G7/G11 margins: the oracle's float64 ACS margins are the ones frozen from the reference object
+def test_margins_equal_the_reference_objects():
+    g = golden("g5_config1.npz")
+    for det in ("PT", "PAM"):
+        b, s, m, sc = o.detect_soqpsk_fast(g[f"{det}_z"], True, return_margin=True)
+        assert np.array_equal(b, g[f"{det}_dec_bits"])
+        assert np.array_equal(m, g[f"{det}_margin"]) and np.array_equal(sc, g[f"{det}_scale"])
+        assert m[0] == 0.0 and np.count_nonzero(m[1:] == 0.0) == 0  # call 0 starts from all-equal metrics
+    g7 = golden("g7_variants.npz")
+    for diff in (True, False):
+        tag = f"d{int(diff)}_l2"
+        r = o.soqpsk_link_frame(g7["bits"], o.pulse_soqpsk_tg(8), 8, 1.0, noise=g7[f"noise_{tag}"], detector="PAM",
+                                diff=diff, return_all=True)
+        np.testing.assert_allclose(r["margin"], g7[f"PAM_margin_{tag}"], rtol=0, atol=1e-9)
+
+
+# ---- G11: SOQPSK-A / -B end to end on the reference's noise (soqpsk/pulse_filters.py:53-74)
+@pytest.mark.parametrize("lab", ["a", "b"])
+def test_soqpsk_a_b_chain(lab):
+    g = golden("g11_soqpsk_ab.npz")
+    pulse = {"a": o.pulse_soqpsk_a, "b": o.pulse_soqpsk_b}[lab](8)
+    for det in ("PT", "PAM"):
+        r = o.soqpsk_link_frame(g["bits"], pulse, 8, float(g["sigma"]), noise=g[f"noise_{lab}"], detector=det,
+                                return_all=True)
+        assert np.array_equal(r["symbols"], g[f"symbols_{lab}"])
+        assert np.max(np.abs(r["z"] - g[f"{lab}_{det}_z"])) < 1e-10
+        assert np.array_equal(r["dec_bits"], g[f"{lab}_{det}_bits"])
+        assert np.array_equal(r["dec_syms"], g[f"{lab}_{det}_syms"])
+        assert [r["bit_errors"], r["sym_errors"], r["compared"]] == list(g[f"{lab}_{det}_counts"])
+        np.testing.assert_allclose(r["margin"], g[f"{lab}_{det}_margin"], rtol=0, atol=1e-9)

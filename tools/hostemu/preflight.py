@@ -126,7 +126,7 @@ def modulate(syms, h, pulse, sps, dtype, derot=0.0, sigma=None, seed=0, first=0)
     hv, hp = darr(h)
     pv, pp = darr(pulse)
     ok(L.wf_cpm_modulate(ptr(syms), B, S, hp, hv.size, pp, pv.size, sps, np.pi / 4, derot, dtype, ptr(out), ld,
-                         ptr(sigma), None, seed, first, None))
+                         ptr(sigma), None, seed, first, None, None))
     return out[:, :T]
 
 
@@ -166,7 +166,7 @@ def t_modedge():
             got = modulate(sy, h, pulse, 8, 0)
             sg = np.full(B, 0.8, np.float32)
             buf = np.ascontiguousarray(got.copy())
-            ok(L.wf_awgn_add(ptr(buf), 0, B, got.shape[1], got.shape[1], ptr(sg), None, 5, 9, None))
+            ok(L.wf_awgn_add(ptr(buf), 0, B, got.shape[1], got.shape[1], ptr(sg), None, 5, 9, None, None))
             fused = modulate(sy, h, pulse, 8, 0, sigma=sg, seed=5, first=9)
             for b in range(B):
                 ref = o.cpm_modulate_closed_form(sy[b], h if len(h) > 1 else h[0], pulse, 8)
@@ -302,14 +302,14 @@ def t_noise():
     B, T = 4, 20000
     out = np.zeros((B, T, 2), np.float32)
     sig = np.array([1.0, 2.0, 0.5, 1.0], np.float32)
-    ok(L.wf_awgn_fill(ptr(out), B, T, ptr(sig), None, 1234, 0, None))
+    ok(L.wf_awgn_fill(ptr(out), B, T, ptr(sig), None, 1234, 0, None, None))
     for b in range(B):
         x = out[b].ravel() / sig[b]
         print(f"  noise frame {b}: mean {x.mean():+.4f} var {x.var():.4f} kurt {np.mean(x**4):.3f}")
         assert abs(x.mean()) < 0.03 and abs(x.var() - 1) < 0.03 and abs(np.mean(x ** 4) - 3) < 0.15
     # sharding independence: frames 2..3 generated alone with first_frame=2
     out2 = np.zeros((2, T, 2), np.float32)
-    ok(L.wf_awgn_fill(ptr(out2), 2, T, ptr(sig[2:].copy()), None, 1234, 2, None))
+    ok(L.wf_awgn_fill(ptr(out2), 2, T, ptr(sig[2:].copy()), None, 1234, 2, None, None))
     assert np.array_equal(out2, out[2:])
     # fused modulate+noise == modulate then add
     sy = o.fsm_encode(o.TRELLISES["SOQPSKTrellis4x2DiffEncoded"], G("g4_modulated.npz")["bits"])[None]
@@ -317,7 +317,7 @@ def t_noise():
     T1 = s1.shape[1]
     sg = np.array([0.7], np.float32)
     buf = np.ascontiguousarray(s1.copy())
-    ok(L.wf_awgn_add(ptr(buf), 0, 1, T1, T1, ptr(sg), None, 99, 5, None))
+    ok(L.wf_awgn_add(ptr(buf), 0, 1, T1, T1, ptr(sg), None, 99, 5, None, None))
     s2 = modulate(sy, [0.25], o.pulse_soqpsk_tg(8), 8, 0, derot=-np.pi / 4, sigma=sg, seed=99, first=5)
     assert np.max(np.abs(buf - s2)) < 1e-6, np.max(np.abs(buf - s2))
     # same identity on every fused kernel shape: the sps-8 fast path with aligned (TG, off 32) and
@@ -338,7 +338,7 @@ def t_noise():
         clean = modulate(sy, h, pulse, sps, dtype)
         Tn = clean.shape[1]
         buf = np.ascontiguousarray(clean.copy())
-        ok(L.wf_awgn_add(ptr(buf), dtype, B, Tn, Tn, ptr(sg), None, 77, 3, None))
+        ok(L.wf_awgn_add(ptr(buf), dtype, B, Tn, Tn, ptr(sg), None, 77, 3, None, None))
         fused = modulate(sy, h, pulse, sps, dtype, sigma=sg, seed=77, first=3)
         err = np.max(np.abs(buf - fused))
         nz = (buf - clean) / sg[:, None]

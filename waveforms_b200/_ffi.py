@@ -11,6 +11,7 @@ import ctypes as C
 import os
 import threading
 
+ABI_VERSION = 2  # WF_ABI_VERSION of include/wfb200.h
 WF_F32, WF_F64 = 0, 1
 ENC_SOQPSK_DIFF, ENC_SOQPSK, ENC_BINARY, ENC_QUATERNARY, ENC_SOQPSK_TERNARY = range(5)
 
@@ -27,14 +28,14 @@ PROTOTYPES = {
     "wf_bits_encode": (_i32, [_vp, _i64, _i64, _i32, _vp, _vp, _i64, _vp, _vp]),
     "wf_trellis_encode": (_i32, [_vp, _i64, _i64, _vp, _vp, _i32, _i32, _i32, _vp, _vp, _vp]),
     "wf_cpm_modulate": (_i32, [_vp, _i64, _i64, _vp, _i32, _vp, _i32, _i32, _dbl, _dbl, _i32, _vp, _i64,
-                               _vp, _vp, _u64, _u64, _vp]),
+                               _vp, _vp, _u64, _u64, _vp, _vp]),
     "wf_cpm_modulate_bank_supported": (_i32, [_i32, _i32, _i32, _i32, _i32, _i64, _i64, _i64]),
-    "wf_cpm_modulate_bank": (_i32, [_vp, _i64, _i64, _vp, _i32, _vp, _i32, _i32, _dbl, _dbl, _vp, _vp, _u64, _u64,
+    "wf_cpm_modulate_bank": (_i32, [_vp, _i64, _i64, _vp, _i32, _vp, _i32, _i32, _dbl, _dbl, _vp, _vp, _u64, _u64, _vp,
                                     _vp, _i32, _i32, _i32, _i64, _i64, _vp, _i64, _vp]),
     "wf_frequency_modulate": (_i32, [_vp, _i64, _i64, _i64, _i32, _dbl, _i32, _vp, _i64, _vp]),
     "wf_phase_modulate": (_i32, [_vp, _i64, _dbl, _i32, _vp, _vp]),
-    "wf_awgn_add": (_i32, [_vp, _i32, _i64, _i64, _i64, _vp, _vp, _u64, _u64, _vp]),
-    "wf_awgn_fill": (_i32, [_vp, _i64, _i64, _vp, _vp, _u64, _u64, _vp]),
+    "wf_awgn_add": (_i32, [_vp, _i32, _i64, _i64, _i64, _vp, _vp, _u64, _u64, _vp, _vp]),
+    "wf_awgn_fill": (_i32, [_vp, _i64, _i64, _vp, _vp, _u64, _u64, _vp, _vp]),
     "wf_mf_bank": (_i32, [_vp, _i32, _i64, _i64, _i64, _vp, _vp, _i32, _i32, _i32, _vp, _vp, _i32, _i32, _i64, _i64,
                           _vp, _i64, _vp]),
     "wf_viterbi_soqpsk": (_i32, [_vp, _i32, _i64, _i64, _i64, _i32, _i32, _vp, _vp, _vp, _i64, _vp, _i64, _vp, _vp, _vp,
@@ -75,7 +76,7 @@ def lib() -> C.CDLL:
 
                     _build.build()
                 _lib = bind(C.CDLL(path))
-                if _lib.wf_abi_version() != 1:
+                if _lib.wf_abi_version() != ABI_VERSION:
                     raise RuntimeError("libwfb200 ABI version mismatch")
     return _lib
 

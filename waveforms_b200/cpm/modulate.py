@@ -49,9 +49,10 @@ def frequency_modulate(freq_pulses: torch.Tensor, sps: int, initial_phase: float
 def modulate_frames(symbols: torch.Tensor, mod_index, pulse_filter, sps: int = 8, *, dtype=torch.complex64,
                     initial_phase: float = INITIAL_PHASE, derotate: float = 0.0, sigma: torch.Tensor | None = None,
                     point: torch.Tensor | None = None, seed: int = 0, first_frame: int = 0,
-                    out: torch.Tensor | None = None) -> torch.Tensor:
+                    out: torch.Tensor | None = None, frame_ids: torch.Tensor | None = None) -> torch.Tensor:
     """Batched core: int8[B, S] -> complex[B, T], T = (S+1)*sps, optionally with AWGN of
-    per-frame ``sigma`` (float32[B]) fused in.  ``out`` may be a preallocated [B, ld>=T] buffer."""
+    per-frame ``sigma`` (float32[B]) fused in.  ``out`` may be a preallocated [B, ld>=T] buffer;
+    ``frame_ids`` (int64[B], optional) keys every row's noise stream by its own global frame id."""
     symbols = _dev.require_cuda(symbols, "symbols", torch.int8)
     B, S = symbols.shape
     T = (S + 1) * sps
@@ -67,11 +68,13 @@ def modulate_frames(symbols: torch.Tensor, mod_index, pulse_filter, sps: int = 8
         sigma = _dev.require_cuda(sigma, "sigma", torch.float32)
     if point is not None:
         point = _dev.require_cuda(point, "point", torch.int32)
+    if frame_ids is not None:
+        frame_ids = _dev.require_cuda(frame_ids, "frame_ids", torch.int64)
     with torch.cuda.device(symbols.device):
         _ffi.check(_ffi.lib().wf_cpm_modulate(_dev.ptr(symbols), B, S, _dev.f64_ptr(h), h.size, _dev.f64_ptr(g), g.size,
                                               int(sps), float(initial_phase), float(derotate), _dev.COMPLEX[dtype],
                                               _dev.ptr(out), ld, _dev.ptr(sigma), _dev.ptr(point),
-                                              int(seed) & (2**64 - 1), int(first_frame),
+                                              int(seed) & (2**64 - 1), int(first_frame), _dev.ptr(frame_ids),
                                               _dev.stream_ptr(symbols.device)))
     return out[:, :T]
 

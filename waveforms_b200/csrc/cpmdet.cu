@@ -81,7 +81,7 @@ viterbi_cpm_kernel(const __grid_constant__ CpmParams p) {
       const unsigned t = (unsigned)(((int)tx[idx] + (M - 1)) >> 1);
       sym_err += (t != v) ? 1u : 0u;
       bit_err += __popc((t ^ v) & sym_mask);
-      ++compared;
+      compared += (unsigned)bits;  // column 2 counts compared BITS for every waveform
     }
   };
 
@@ -339,7 +339,7 @@ viterbi_cpm_lanev_kernel(const __grid_constant__ CpmParams p, const __grid_const
         const unsigned t = (unsigned)(((int)tx[k] + (M - 1)) >> 1);
         sym_err += (t != dec_reg) ? 1u : 0u;
         bit_err += __popc((t ^ dec_reg) & (unsigned)(M - 1));
-        ++compared;
+        compared += BITS;  // column 2 counts compared BITS for every waveform
       }
     }
   };

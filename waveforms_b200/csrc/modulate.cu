@@ -57,6 +57,7 @@ struct ModParams {
   void* out;
   const float* sigma;
   const int32_t* point;
+  const uint64_t* frame_ids;  // global frame id per row (NULL: first_frame + row)
   int64_t B, S, Tn, ld_out;
   uint64_t seed, first_frame;
   int n_h, K, sps, off, J;
@@ -111,7 +112,7 @@ cpm_modulate_kernel(const __grid_constant__ ModParams<T> p) {
   if (NOISE) {
     ncoef = noise_coef(p.sigma[frame]);
     pt = p.point ? (uint32_t)p.point[frame] : 0u;
-    gframe = p.first_frame + (uint64_t)frame;
+    gframe = p.frame_ids ? p.frame_ids[frame] : p.first_frame + (uint64_t)frame;
   }
 
   // hoisted Q coefficients (fast path): rho of this thread's even sample is fixed
@@ -417,7 +418,7 @@ cpm_modulate_f32s8_kernel(const __grid_constant__ ModParams<float> p,
   ctr.x = 0; ctr.y = 0; ctr.z = 0; ctr.w = 0;
   if (NOISE) {
     ncoef = noise_coef(p.sigma[frame]);
-    const uint64_t gframe = p.first_frame + (uint64_t)frame;
+    const uint64_t gframe = p.frame_ids ? p.frame_ids[frame] : p.first_frame + (uint64_t)frame;
     ctr.y = (uint32_t)gframe; ctr.z = (uint32_t)(gframe >> 32);
     ctr.w = p.point ? (uint32_t)p.point[frame] : 0u;
   }
@@ -663,7 +664,7 @@ cpm_modulate_f32s8_kernel(const __grid_constant__ ModParams<float> p,
 template <typename T, bool ADD>
 __global__ void __launch_bounds__(256)
 awgn_kernel(T* __restrict__ sig, int64_t B, int64_t Tn, int64_t ld, const float* __restrict__ sigma,
-            const int32_t* __restrict__ point, uint64_t seed, uint64_t first_frame) {
+            const int32_t* __restrict__ point, uint64_t seed, uint64_t first_frame, const uint64_t* __restrict__ frame_ids) {
   const int64_t pairs_per_frame = (Tn + 1) >> 1;
   const int64_t calls_per_frame = ((pairs_per_frame + 7) >> 3) << 2;
   const int64_t total = B * calls_per_frame;
@@ -674,7 +675,7 @@ awgn_kernel(T* __restrict__ sig, int64_t B, int64_t Tn, int64_t ld, const float*
     const int64_t call = i - b * calls_per_frame;
     const NoiseCoef nc = noise_coef(sigma ? sigma[b] : 1.0f);
     const uint32_t pt = point ? (uint32_t)point[b] : 0u;
-    const u32x4 ctr = noise_counter((uint64_t)call, first_frame + (uint64_t)b, pt);
+    const u32x4 ctr = noise_counter((uint64_t)call, frame_ids ? frame_ids[b] : first_frame + (uint64_t)b, pt);
     const u32x4 r = philox4x32_10(ctr, k0, k1);
 #pragma unroll
     for (int half = 0; half < 2; ++half) {
@@ -769,9 +770,9 @@ template <typename T>
 static int fill_mod_params(ModParams<T>& p, const int8_t* d_syms, int64_t B, int64_t S, const double* mod_index, int n_h,
                            const double* pulse, int K, int sps, double initial_phase, double derotate,
                            void* d_out, int64_t ld_out, const float* d_sigma, const int32_t* d_point,
-                           uint64_t seed, uint64_t first_frame) {
+                           uint64_t seed, uint64_t first_frame, const uint64_t* d_frame_ids) {
   memset(&p, 0, sizeof(p));
-  p.syms = d_syms; p.out = d_out; p.sigma = d_sigma; p.point = d_point;
+  p.syms = d_syms; p.out = d_out; p.sigma = d_sigma; p.point = d_point; p.frame_ids = d_frame_ids;
   p.B = B; p.S = S; p.Tn = (S + 1) * sps; p.ld_out = ld_out;
   p.seed = seed; p.first_frame = first_frame; p.rk = philox_round_keys(seed);
   p.n_h = n_h; p.K = K; p.sps = sps; p.off = (K - 1) / 2;
@@ -804,10 +805,10 @@ template <typename T>
 static int launch_modulate(const int8_t* d_syms, int64_t B, int64_t S, const double* mod_index, int n_h,
                            const double* pulse, int K, int sps, double initial_phase, double derotate,
                            void* d_out, int64_t ld_out, const float* d_sigma, const int32_t* d_point,
-                           uint64_t seed, uint64_t first_frame, cudaStream_t stream) {
+                           uint64_t seed, uint64_t first_frame, const uint64_t* d_frame_ids, cudaStream_t stream) {
   ModParams<T> p;
   int rcp = fill_mod_params<T>(p, d_syms, B, S, mod_index, n_h, pulse, K, sps, initial_phase, derotate, d_out, ld_out,
-                               d_sigma, d_point, seed, first_frame);
+                               d_sigma, d_point, seed, first_frame, d_frame_ids);
   if (rcp) return rcp;
   const bool noise = d_sigma != nullptr;
   const dim3 grid((unsigned)B), block(kModThreads);
@@ -868,6 +869,7 @@ static bool fuse_geometry(int K, int sps, int n_filt, int n_taps, int center, in
 static int launch_modulate_bank(const int8_t* d_syms, int64_t B, int64_t S, const double* mod_index, int n_h,
                                 const double* pulse, int K, int sps, double initial_phase, double derotate,
                                 const float* d_sigma, const int32_t* d_point, uint64_t seed, uint64_t first_frame,
+                                const uint64_t* d_frame_ids,
                                 const double* taps_re, int n_filt, int n_taps, int center, int64_t first_instant,
                                 int64_t n_calls, void* d_z, int64_t ld_z, cudaStream_t stream) {
   int CB = 0, LB = 0;
@@ -876,7 +878,7 @@ static int launch_modulate_bank(const int8_t* d_syms, int64_t B, int64_t S, cons
   }
   ModParams<float> p;
   int rc = fill_mod_params<float>(p, d_syms, B, S, mod_index, n_h, pulse, K, sps, initial_phase, derotate, nullptr,
-                                  (S + 1) * sps, d_sigma, d_point, seed, first_frame);
+                                  (S + 1) * sps, d_sigma, d_point, seed, first_frame, d_frame_ids);
   if (rc) return rc;
   FuseParams fz;
   memset(&fz, 0, sizeof(fz));
@@ -915,6 +917,7 @@ int wf_cpm_modulate_bank_supported(int K, int sps, int n_filt, int n_taps, int c
 int wf_cpm_modulate_bank(const int8_t* d_syms, int64_t B, int64_t S, const double* mod_index, int n_h,
                          const double* pulse, int K, int sps, double initial_phase, double derotate,
                          const float* d_sigma, const int32_t* d_point, uint64_t seed, uint64_t first_frame,
+                         const uint64_t* d_frame_ids,
                          const double* taps_re, int n_filt, int n_taps, int center, int64_t first_instant,
                          int64_t n_calls, void* d_z, int64_t ld_z, void* stream) {
   using namespace wf;
@@ -930,14 +933,14 @@ int wf_cpm_modulate_bank(const int8_t* d_syms, int64_t B, int64_t S, const doubl
   WF_REQUIRE(d_syms && d_z, "NULL device pointer");
   WF_REQUIRE((reinterpret_cast<uintptr_t>(d_z) & 15) == 0, "d_z must be 16-byte aligned");
   return launch_modulate_bank(d_syms, B, S, mod_index, n_h, pulse, K, sps, initial_phase, derotate, d_sigma, d_point, seed,
-                              first_frame, taps_re, n_filt, n_taps, center, first_instant, n_calls, d_z, ld_z,
+                              first_frame, d_frame_ids, taps_re, n_filt, n_taps, center, first_instant, n_calls, d_z, ld_z,
                               as_stream(stream));
 }
 
 int wf_cpm_modulate(const int8_t* d_syms, int64_t B, int64_t S, const double* mod_index, int n_h,
                     const double* pulse, int K, int sps, double initial_phase, double derotate,
                     int dtype, void* d_out, int64_t ld_out, const float* d_sigma, const int32_t* d_point,
-                    uint64_t seed, uint64_t first_frame, void* stream) {
+                    uint64_t seed, uint64_t first_frame, const uint64_t* d_frame_ids, void* stream) {
   using namespace wf;
   WF_REQUIRE(B >= 0 && S >= 0, "negative batch or symbol count");
   WF_REQUIRE(sps >= 1 && sps <= 64, "sps=%d outside 1..64", sps);
@@ -954,13 +957,14 @@ int wf_cpm_modulate(const int8_t* d_syms, int64_t B, int64_t S, const double* mo
   WF_REQUIRE(d_out, "d_out is NULL");
   if (dtype == WF_F32)
     return launch_modulate<float>(d_syms, B, S, mod_index, n_h, pulse, K, sps, initial_phase, derotate, d_out, ld_out,
-                                  d_sigma, d_point, seed, first_frame, as_stream(stream));
+                                  d_sigma, d_point, seed, first_frame, d_frame_ids, as_stream(stream));
   return launch_modulate<double>(d_syms, B, S, mod_index, n_h, pulse, K, sps, initial_phase, derotate, d_out, ld_out,
-                                 d_sigma, d_point, seed, first_frame, as_stream(stream));
+                                 d_sigma, d_point, seed, first_frame, d_frame_ids, as_stream(stream));
 }
 
 static int awgn_common(void* d_sig, int dtype, int64_t B, int64_t T, int64_t ld, const float* d_sigma,
-                       const int32_t* d_point, uint64_t seed, uint64_t first_frame, void* stream, bool add) {
+                       const int32_t* d_point, uint64_t seed, uint64_t first_frame, const uint64_t* d_frame_ids, void* stream,
+                       bool add) {
   using namespace wf;
   WF_REQUIRE(B >= 0 && T >= 0 && ld >= T, "bad AWGN shape");
   WF_REQUIRE(dtype == WF_F32 || dtype == WF_F64, "dtype must be WF_F32 or WF_F64");
@@ -974,25 +978,25 @@ static int awgn_common(void* d_sig, int dtype, int64_t B, int64_t T, int64_t ld,
   if (blocks > cap) blocks = cap;
   cudaStream_t st = as_stream(stream);
   if (dtype == WF_F32) {
-    if (add) awgn_kernel<float, true><<<(unsigned)blocks, 256, 0, st>>>((float*)d_sig, B, T, ld, d_sigma, d_point, seed, first_frame);
-    else awgn_kernel<float, false><<<(unsigned)blocks, 256, 0, st>>>((float*)d_sig, B, T, ld, d_sigma, d_point, seed, first_frame);
+    if (add) awgn_kernel<float, true><<<(unsigned)blocks, 256, 0, st>>>((float*)d_sig, B, T, ld, d_sigma, d_point, seed, first_frame, d_frame_ids);
+    else awgn_kernel<float, false><<<(unsigned)blocks, 256, 0, st>>>((float*)d_sig, B, T, ld, d_sigma, d_point, seed, first_frame, d_frame_ids);
   } else {
-    if (add) awgn_kernel<double, true><<<(unsigned)blocks, 256, 0, st>>>((double*)d_sig, B, T, ld, d_sigma, d_point, seed, first_frame);
-    else awgn_kernel<double, false><<<(unsigned)blocks, 256, 0, st>>>((double*)d_sig, B, T, ld, d_sigma, d_point, seed, first_frame);
+    if (add) awgn_kernel<double, true><<<(unsigned)blocks, 256, 0, st>>>((double*)d_sig, B, T, ld, d_sigma, d_point, seed, first_frame, d_frame_ids);
+    else awgn_kernel<double, false><<<(unsigned)blocks, 256, 0, st>>>((double*)d_sig, B, T, ld, d_sigma, d_point, seed, first_frame, d_frame_ids);
   }
   WF_LAUNCH_CHECK("awgn_kernel");
   return WF_OK;
 }
 
 int wf_awgn_add(void* d_sig, int dtype, int64_t B, int64_t T, int64_t ld, const float* d_sigma,
-                const int32_t* d_point, uint64_t seed, uint64_t first_frame, void* stream) {
+                const int32_t* d_point, uint64_t seed, uint64_t first_frame, const uint64_t* d_frame_ids, void* stream) {
   WF_REQUIRE(d_sigma, "d_sigma is NULL");
-  return awgn_common(d_sig, dtype, B, T, ld, d_sigma, d_point, seed, first_frame, stream, true);
+  return awgn_common(d_sig, dtype, B, T, ld, d_sigma, d_point, seed, first_frame, d_frame_ids, stream, true);
 }
 
 int wf_awgn_fill(float* d_out, int64_t B, int64_t T, const float* d_sigma, const int32_t* d_point,
-                 uint64_t seed, uint64_t first_frame, void* stream) {
-  return awgn_common(d_out, WF_F32, B, T, T, d_sigma, d_point, seed, first_frame, stream, false);
+                 uint64_t seed, uint64_t first_frame, const uint64_t* d_frame_ids, void* stream) {
+  return awgn_common(d_out, WF_F32, B, T, T, d_sigma, d_point, seed, first_frame, d_frame_ids, stream, false);
 }
 
 int wf_frequency_modulate(const double* d_freq, int64_t B, int64_t T, int64_t ld_in, int sps, double initial_phase,

@@ -125,7 +125,7 @@ class LinkSimulator:
                                       memory=int(cfg.extra.get("memory", 2)), depth=int(cfg.extra.get("depth", 0)))
         self.skip = int(cfg.extra.get("skip", 4))
         self.first_instant, self.n_calls = self.det.first_instant, self.n_sym
-        self.n_compared = max(0, self.n_sym - 2 * self.skip)
+        self.n_compared = max(0, self.n_sym - 2 * self.skip) * bps  # compared BITS per frame, as for SOQPSK
         self._taps = self.det.taps
         self._tap_re = _dev.host_f64(self._taps.real.ravel())
         self._tap_im = _dev.host_f64(self._taps.imag.ravel())
@@ -154,11 +154,15 @@ class LinkSimulator:
 
     # ------------------------------------------------------------------ one batch
     def run_batch(self, first_frame: int, sigma: torch.Tensor, point: torch.Tensor | None, counters: torch.Tensor,
-                  events: list | None = None) -> None:
+                  events: list | None = None, frame_ids: torch.Tensor | None = None,
+                  bit_offsets: torch.Tensor | None = None) -> None:
         """Frames first_frame .. first_frame+B-1 (B = len(sigma) <= max_batch) through the whole
-        chain; adds (bit errors, symbol errors, compared) to counters[point[b]].  Everything is
+        chain; adds (bit errors, symbol errors, compared bits) to counters[point[b]].  Everything is
         enqueued on the current stream; nothing is synchronised.  ``events`` (optional list)
-        receives len(stage_names) + 1 CUDA events recorded on that stream around the kernels."""
+        receives len(stage_names) + 1 CUDA events recorded on that stream around the kernels.
+        ``frame_ids`` / ``bit_offsets`` (int64[B] device tensors, both or neither): row b is global
+        frame frame_ids[b], whose PN bits start bit_offsets[b] = frame_ids[b] * n_bits (mod period)
+        into the stream -- how ``run`` packs frames of several Eb/N0 points into one launch."""
         cfg, lib, dev = self.cfg, _ffi.lib(), self.device
         B = sigma.shape[0]
         if B > self.max_batch:
@@ -167,6 +171,9 @@ class LinkSimulator:
         dt = _dev.COMPLEX[cfg.dtype]
         seed = cfg.seed & (2**64 - 1)
         raw = self.soqpsk and self.raw_bank
+        if (frame_ids is None) != (bit_offsets is None):
+            raise ValueError("frame_ids and bit_offsets go together")
+        fid, boff = _dev.ptr(frame_ids), _dev.ptr(bit_offsets)
 
         def mark():
             if events is not None:
@@ -176,7 +183,7 @@ class LinkSimulator:
 
         with torch.cuda.device(dev):
             mark()
-            _ffi.check(lib.wf_prbs_encode(self.mask, cfg.pn_degree, self.period, self.period, None, int(first_frame), B,
+            _ffi.check(lib.wf_prbs_encode(self.mask, cfg.pn_degree, self.period, self.period, boff, int(first_frame), B,
                                           cfg.n_bits, self.encoder, None, None, _dev.ptr(self.packed), self.ld_words,
                                           _dev.ptr(self.syms), st))
             mark()
@@ -184,7 +191,7 @@ class LinkSimulator:
                 _ffi.check(lib.wf_cpm_modulate_bank(_dev.ptr(self.syms), B, self.n_sym, _dev.f64_ptr(self.h), self.h.size,
                                                     _dev.f64_ptr(self.pulse), self.pulse.size, cfg.sps, math.pi / 4,
                                                     -math.pi / 4, _dev.ptr(sigma), _dev.ptr(point), seed, int(first_frame),
-                                                    _dev.f64_ptr(self._tap_re), self._taps.shape[0], self._taps.shape[1],
+                                                    fid, _dev.f64_ptr(self._tap_re), self._taps.shape[0], self._taps.shape[1],
                                                     (self._taps.shape[1] - 1) // 2, self.first_instant, self.n_calls,
                                                     _dev.ptr(self.z), self.ld_z, st))
                 mark()
@@ -198,7 +205,7 @@ class LinkSimulator:
             _ffi.check(lib.wf_cpm_modulate(_dev.ptr(self.syms), B, self.n_sym, _dev.f64_ptr(self.h), self.h.size,
                                            _dev.f64_ptr(self.pulse), self.pulse.size, cfg.sps, math.pi / 4, -math.pi / 4,
                                            dt, _dev.ptr(self.rx), self.ld_rx, _dev.ptr(sigma), _dev.ptr(point), seed,
-                                           int(first_frame), st))
+                                           int(first_frame), fid, st))
             mark()
             _ffi.check(lib.wf_mf_bank(_dev.ptr(self.rx), dt, B, self.n_samples, self.ld_rx, _dev.f64_ptr(self._tap_re),
                                       None if self._tap_im is None else _dev.f64_ptr(self._tap_im),
@@ -231,25 +238,69 @@ class LinkSimulator:
         self.launches += 4
 
     # ------------------------------------------------------------------ host-facing calls
+    def _staging(self, slot: int):
+        """Pinned host tables + their device twins for one batch, allocated once (two slots: the
+        host fills slot k+1 while the copy of slot k may still be in flight; an event per slot
+        says when its pinned memory may be overwritten)."""
+        if not hasattr(self, "_stage"):
+            self._stage = []
+            for _ in range(2):
+                h = {"sigma": torch.empty(self.max_batch, dtype=torch.float32).pin_memory(),
+                     "point": torch.empty(self.max_batch, dtype=torch.int32).pin_memory(),
+                     "frame": torch.empty(self.max_batch, dtype=torch.int64).pin_memory(),
+                     "off": torch.empty(self.max_batch, dtype=torch.int64).pin_memory()}
+                d = {k: torch.empty_like(v, device=self.device) for k, v in h.items()}
+                self._stage.append((h, d, torch.cuda.Event()))
+            self._stage_used = [False, False]
+        return self._stage[slot]
+
+    def _bit_offsets(self, frames: np.ndarray) -> np.ndarray:
+        """(frame * n_bits) mod PN period, exact for any frame id."""
+        n = self.cfg.n_bits
+        if self.period < (1 << 31):
+            return ((frames % self.period) * (n % self.period)) % self.period
+        return np.array([(int(f) * n) % self.period for f in frames], dtype=np.int64)
+
     def run(self, ebn0_db, n_frames: int, first_frame: int = 0, active=None) -> np.ndarray:
         """End-to-end call with HOST inputs and outputs: ``ebn0_db`` is a host sequence of P
         Eb/N0 points; every point is simulated on frames first_frame .. first_frame+n_frames-1.
-        Per-frame sigma / point tables are staged through pinned memory; returns int64[P, 3] =
-        (bit errors, symbol errors, compared bits) as a numpy array."""
+        The (point, frame) work list is cut into batches of ``max_batch`` rows REGARDLESS of point
+        boundaries -- per-row sigma / point / frame-id / PN-offset tables go through preallocated
+        pinned memory -- so a 13-point sweep of 96 frames is one launch of the chain, not 13.
+        Returns int64[P, 3] = (bit errors, symbol errors, compared bits) as a numpy array.
+        ``active`` (bool[P], optional): points that get no frames keep their row and noise stream id."""
         eb = np.atleast_1d(np.asarray(ebn0_db, dtype=np.float64))
         P = eb.size
         sig = sigma_from_ebn0_db(eb, self.cfg.sps, self.bits_per_symbol).astype(np.float32)
         counters = torch.zeros((P, 3), dtype=torch.int64, device=self.device)
-        for p in range(P):
-            if active is not None and not active[p]:
-                continue  # the point keeps its row and its noise stream id, it just gets no frames
-            for f0 in range(0, n_frames, self.max_batch):
-                B = min(self.max_batch, n_frames - f0)
-                h_sigma = torch.full((B,), float(sig[p]), dtype=torch.float32).pin_memory()
-                h_point = torch.full((B,), p, dtype=torch.int32).pin_memory()
-                d_sigma = h_sigma.to(self.device, non_blocking=True)
-                d_point = h_point.to(self.device, non_blocking=True)
-                self.run_batch(first_frame + f0, d_sigma, d_point, counters)
+        pts = np.arange(P) if active is None else np.flatnonzero(np.asarray(active, dtype=bool))
+        total = pts.size * int(n_frames)
+        stream = torch.cuda.current_stream(self.device)
+        k = 0
+        for w0 in range(0, total, self.max_batch):
+            B = min(self.max_batch, total - w0)
+            h, d, ev = self._staging(k & 1)
+            if self._stage_used[k & 1]:
+                ev.synchronize()  # the previous copy out of this pinned slot has completed
+            pw, fw = work_slice(pts, int(n_frames), int(first_frame), w0, B)
+            one_run = pw[0] == pw[-1]  # one point, consecutive frames: no per-row frame tables needed
+            h["sigma"][:B] = torch.from_numpy(sig[pw])
+            h["point"][:B] = torch.from_numpy(pw.astype(np.int32))
+            names = ("sigma", "point")
+            if not one_run:
+                h["frame"][:B] = torch.from_numpy(fw)
+                h["off"][:B] = torch.from_numpy(self._bit_offsets(fw).astype(np.int64))
+                names += ("frame", "off")
+            for nm in names:
+                d[nm][:B].copy_(h[nm][:B], non_blocking=True)
+            ev.record(stream)
+            self._stage_used[k & 1] = True
+            if one_run:
+                self.run_batch(int(fw[0]), d["sigma"][:B], d["point"][:B], counters)
+            else:
+                self.run_batch(0, d["sigma"][:B], d["point"][:B], counters, frame_ids=d["frame"][:B],
+                               bit_offsets=d["off"][:B])
+            k += 1
         return counters.cpu().numpy()
 
     def sweep(self, ebn0_db, n_frames: int, first_frame: int = 0, group=None, active=None) -> np.ndarray:
@@ -260,11 +311,11 @@ class LinkSimulator:
 
         eb = np.atleast_1d(np.asarray(ebn0_db, dtype=np.float64))
         if not (dist.is_available() and dist.is_initialized()):
-            return self.run(eb, n_frames, first_frame, active) if active is not None else self.run(eb, n_frames, first_frame)
+            return self.run(eb, n_frames, first_frame, active)
         rank, world = dist.get_rank(group), dist.get_world_size(group)
         lo, hi = shard_range(n_frames, rank, world)
         if hi > lo:
-            local = self.run(eb, hi - lo, first_frame + lo, active) if active is not None else self.run(eb, hi - lo, first_frame + lo)
+            local = self.run(eb, hi - lo, first_frame + lo, active)
         else:
             local = np.zeros((eb.size, 3), dtype=np.int64)
         return allreduce_counters(local, self.device, group)
@@ -293,6 +344,14 @@ class LinkSimulator:
             frame += chunk
             active = (total[:, 0] < min_errors) & (total[:, 2] < max_bits)
         return total
+
+
+def work_slice(points: np.ndarray, n_frames: int, first_frame: int, w0: int, count: int):
+    """Rows w0 .. w0+count-1 of the (point, frame) work list of ``LinkSimulator.run``: point-major,
+    frames first_frame .. first_frame+n_frames-1 inside each point.  Returns (point index per row,
+    global frame id per row) as int64 arrays."""
+    w = np.arange(w0, w0 + count, dtype=np.int64)
+    return np.asarray(points, dtype=np.int64)[w // n_frames], first_frame + (w % n_frames)
 
 
 def allreduce_counters(local: np.ndarray, device, group=None) -> np.ndarray:

@@ -48,26 +48,31 @@ def generate_complex_awgn(sigma, size: int, rng: PhiloxRNG | None = None, *, bat
     out = torch.empty((B, int(size), 2), dtype=torch.float32, device=dev)
     with torch.cuda.device(dev):
         _ffi.check(_ffi.lib().wf_awgn_fill(_dev.ptr(out), B, int(size), _dev.ptr(sig), None,
-                                           rng.seed & (2**64 - 1), rng.take(B), _dev.stream_ptr(dev)))
+                                           rng.seed & (2**64 - 1), rng.take(B), None, _dev.stream_ptr(dev)))
     z = torch.view_as_complex(out)
     return z[0] if batch is None else z
 
 
 def add_awgn(signal: torch.Tensor, sigma: torch.Tensor, rng: PhiloxRNG | None = None, *, point=None,
-             first_frame: int | None = None) -> torch.Tensor:
-    """In-place ``signal[b] += sigma[b] * (N(0,1) + j N(0,1))`` on complex[B, T] (wf_awgn_add)."""
+             first_frame: int | None = None, frame_ids: torch.Tensor | None = None) -> torch.Tensor:
+    """In-place ``signal[b] += sigma[b] * (N(0,1) + j N(0,1))`` on complex[B, T] (wf_awgn_add).
+    ``frame_ids`` (int64 CUDA tensor [B], optional) gives every row its own global frame id."""
     rng = rng or DEFAULT_RNG
-    signal = _dev.require_cuda(signal, "signal")
-    if signal.dim() != 2 or not signal.is_contiguous():
+    # contiguity is checked on the caller's tensor: a strided view would otherwise be copied and the
+    # "in-place" add would land in the copy
+    if isinstance(signal, torch.Tensor) and (signal.dim() != 2 or not signal.is_contiguous()):
         raise ValueError("signal must be a contiguous [B, T] complex tensor")
+    signal = _dev.require_cuda(signal, "signal")
     B, T = signal.shape
     sig = _dev.require_cuda(sigma, "sigma", torch.float32)
     if point is not None:
         point = _dev.require_cuda(point, "point", torch.int32)
     first = rng.take(B) if first_frame is None else int(first_frame)
+    if frame_ids is not None:
+        frame_ids = _dev.require_cuda(frame_ids, "frame_ids", torch.int64)
     with torch.cuda.device(signal.device):
         _ffi.check(_ffi.lib().wf_awgn_add(_dev.ptr(signal), _dev.COMPLEX[signal.dtype], B, T, T, _dev.ptr(sig),
-                                          _dev.ptr(point), rng.seed & (2**64 - 1), first,
+                                          _dev.ptr(point), rng.seed & (2**64 - 1), first, _dev.ptr(frame_ids),
                                           _dev.stream_ptr(signal.device)))
     return signal
 

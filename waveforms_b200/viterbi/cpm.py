@@ -66,7 +66,8 @@ class CPMTrellisDetector:
                point: torch.Tensor | None = None, counters: torch.Tensor | None = None, return_decisions: bool = True):
         """z complex[B, n_steps, n_h * M^Lp] -> detected symbols int8[B, n_steps] (alphabet values).
         With ``counters`` int64[P, 3] and ``tx_symbols`` int8[B, S]: (bit errors, symbol errors, compared
-        symbols) over symbols [skip_head, min(S, n_steps) - skip_tail) are added at row point[b]."""
+        BITS = log2(M) per symbol) over symbols [skip_head, min(S, n_steps) - skip_tail) are added at row
+        point[b], so counters[:, 0] / counters[:, 2] is a BER for every alphabet."""
         z = _dev.require_cuda(z, "z")
         if z.dtype not in _dev.COMPLEX or z.dim() != 3 or z.shape[2] != self.n_h * self.n_filt:
             raise TypeError(f"z must be complex[B, steps, {self.n_h * self.n_filt}]")
