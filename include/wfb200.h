@@ -126,7 +126,10 @@ WF_API int wf_cpm_modulate(const int8_t* d_syms, int64_t B, int64_t S,
  * wf_cpm_modulate(.., WF_F32, ..) followed by wf_mf_bank(.., combine = NULL, ..) on the same arguments).
  * Built for the SOQPSK-TG shape only: sps 8, pulse with ceil((K-1)/8) == 8 and ((K-1)/2) % 8 == 0,
  * n_filt == 2 real filters of n_taps == 73; wf_cpm_modulate_bank_supported() says whether a shape is
- * covered (1) or not (0); uncovered shapes return WF_ERR_UNSUPPORTED and the caller runs the two calls. */
+ * covered (1) or not (0); uncovered shapes return WF_ERR_UNSUPPORTED and the caller runs the two calls.
+ * tune selects the kernel (same results, bit for bit): 0 = one BLOCK per frame (512-interval chunks, bank
+ * phase on four of eight warps, two block barriers per chunk); 1 / 2 = one WARP per frame, no block barrier
+ * (64- / 128-interval chunks, every lane does both phases, 2 / 4 bank calls per lane). */
 WF_API int wf_cpm_modulate_bank_supported(int K, int sps, int n_filt, int n_taps, int center,
                                           int64_t first_instant, int64_t S, int64_t n_calls);
 WF_API int wf_cpm_modulate_bank(const int8_t* d_syms, int64_t B, int64_t S,
@@ -137,7 +140,7 @@ WF_API int wf_cpm_modulate_bank(const int8_t* d_syms, int64_t B, int64_t S,
                     uint64_t seed, uint64_t first_frame, const uint64_t* d_frame_ids,
                     const double* taps_re, int n_filt, int n_taps, int center,
                     int64_t first_instant, int64_t n_calls,
-                    void* d_z, int64_t ld_z, void* stream);
+                    void* d_z, int64_t ld_z, int tune, void* stream);
 
 /* frequency_modulate(freq_pulses, sps, initial_phase) (cpm/modulate.py:28-54) for B rows
  * of arbitrary per-sample frequency pulses d_freq double[B][ld_in]:
@@ -233,8 +236,11 @@ WF_API int wf_bert(const uint8_t* d_dec_bits, const int8_t* d_dec_syms, int64_t 
  *      float64 statement in oracle/cpm_generic.py.  Parity unpinned. ---------------------- */
 /* d_z complex[B][ld_z][n_h * M^Lp]: per detection step the bank outputs for every symbol
  * hypothesis (newest symbol most significant), one block of M^Lp per step parity i % n_h.
- * h = h_num[k % n_h] / p.  State count 2p * M^(Lp-1) <= 256; register-exchange survivors of
- * `depth` symbols (0 -> min(32, 64 / log2 M)).  Outputs: d_dec_syms int8[B][n_steps] (alphabet values,
+ * h = h_num[k % n_h] / p.  State count 2p * M^(Lp-1) <= 256.  Decision rule (oracle/cpm_generic.py):
+ * BLOCK RELEASE with survivor memory 2 D, D = `depth` (0 -> min(16, 32 / log2 M)): whenever t + 1 is a
+ * multiple of D and t + 1 >= 2 D the survivor of the best state at step t releases the symbols of
+ * steps [t - 2D + 1, t - D]; the best final survivor releases the rest.  This entry point keeps
+ * 2 D-symbol register-exchange words (2 D log2 M <= 64).  Outputs: d_dec_syms int8[B][n_steps] (alphabet values,
  * may be NULL) and, when d_tx_syms int8[B][S] is given, counters[point][3] += (bit errors,
  * symbol errors, compared BITS = log2(M) per compared symbol) over symbols
  * [skip_head, min(S, n_steps) - skip_tail): column 0 / column 2 is a bit-error ratio for every
@@ -244,6 +250,27 @@ WF_API int wf_viterbi_cpm(const void* d_z, int dtype, int64_t B, int64_t n_steps
                           int8_t* d_dec_syms, const int8_t* d_tx_syms, int64_t S,
                           int64_t skip_head, int64_t skip_tail,
                           const int32_t* d_point, int64_t* d_counters, void* stream);
+
+/* The same detector straight from the RECEIVED SAMPLES: the hypothesis bank of
+ * wf_mf_bank(.., center = sps - 1, ..) is computed inside the detector kernel, so neither the bank
+ * launch nor its output array exists (the detector reads 8 sps bytes of rx per step instead of
+ * 8 n_h M^Lp bytes of z), and the survivors are decision bits in shared memory traced back every D
+ * steps.  d_rx complex64[B][ld_rx]; taps_re / taps_im HOST double[n_h * M^Lp][sps] exactly as wf_mf_bank
+ * takes them.  Built for the two IRIG shapes (sps 8, Lp 2, first_instant -1, hypothesis M^Lp-1-f the
+ * complex conjugate of f): PCM/FM (M 2, h 7/10, depth <= 32) and ARTM CPM (M 4, h {4,5}/16, depth <= 32);
+ * wf_cpm_detect_supported() says whether a shape is covered (1) or not (0); uncovered shapes return
+ * WF_ERR_UNSUPPORTED and the caller runs wf_mf_bank + wf_viterbi_cpm.  Same decision rule and counters as
+ * wf_viterbi_cpm (float32 arithmetic: decisions may differ from the float64 statement at near-ties only).
+ * tune: path metrics are re-normalised every `tune` steps (0 / 1 = every step; 2, 4). */
+WF_API int wf_cpm_detect_supported(int dtype, int64_t T, int64_t ld_rx, const double* taps_re, const double* taps_im,
+                                   int sps, int64_t first_instant, int64_t n_steps,
+                                   int M, int Lp, int p, const int32_t* h_num, int n_h, int depth);
+WF_API int wf_cpm_detect(const void* d_rx, int dtype, int64_t B, int64_t T, int64_t ld_rx,
+                         const double* taps_re, const double* taps_im, int sps, int64_t first_instant, int64_t n_steps,
+                         int M, int Lp, int p, const int32_t* h_num, int n_h, int depth,
+                         int8_t* d_dec_syms, const int8_t* d_tx_syms, int64_t S,
+                         int64_t skip_head, int64_t skip_tail,
+                         const int32_t* d_point, int64_t* d_counters, int tune, void* stream);
 
 #ifdef __cplusplus
 }

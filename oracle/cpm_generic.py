@@ -76,29 +76,48 @@ class CpmTrellis:
             z[i] = tpl @ seg
         return z
 
+    def default_depth(self):
+        bits = max(1, (self.M - 1).bit_length())
+        return max(1, 32 // bits)
+
     def detect(self, z, depth=None, return_margin=False):
-        """Register-exchange Viterbi, maximising sum Re{e^{-j pi v/p} z}.  z complex[n_steps, n_h*n_filt].
-        Returns symbol INDICES (0..M-1) uint8[n_steps]; decision delay = depth-1 steps, the tail is
-        flushed from the best final state.  All states start equal (unknown start).
+        """Viterbi detection maximising sum Re{e^{-j pi v/p} z}.  z complex[n_steps, n_h*n_filt].
+        Returns symbol INDICES (0..M-1) uint8[n_steps].  All states start equal (unknown start).
+
+        Decision rule -- BLOCK RELEASE with survivor memory 2 D (D = ``depth``, default 32 / log2 M):
+        the add-compare-select of every step stores, per state, which predecessor won; whenever
+        (t + 1) is a multiple of D and t + 1 >= 2 D the survivor of the best state at step t (largest
+        metric, lowest index on ties) is traced back 2 D steps and the symbols of steps
+        [t - 2D + 1, t - D] are released -- every decision is taken with at least D steps of look-ahead;
+        after the last step the survivor of the best final state releases everything still held.
+        (A register-exchange detector with 2 D-symbol survivor words released D at a time is the same rule.)
 
         ``return_margin``: also return float64[n_steps, 2] = per step (smallest gap between the best and
         the runner-up candidate over all states and between the two largest new path metrics, largest
-        |candidate|).  The decision for symbol k leaves the survivor memory at step k + depth - 1, so a
-        float32 detector may differ at k only if some step in [k, k + depth) has a margin at float32
-        resolution."""
+        |candidate|).  The decision for symbol k is released at a step < k + 2 D, so a float32 detector may
+        differ at k only if some step in [k, k + 2 D) has a margin at float32 resolution."""
         M, Lp, p2 = self.M, self.Lp, 2 * self.p
-        bits = max(1, (M - 1).bit_length())
-        D = depth or min(32, 64 // bits)
+        D = int(depth or self.default_depth())
         n_steps = z.shape[0]
         NS, NH = self.n_states, self.n_hist
         pm = np.zeros(NS)
-        hist = np.zeros(NS, dtype=np.uint64)
         rot = np.exp(-1j * np.pi * np.arange(p2) / self.p)
         out = np.zeros(n_steps, dtype=np.uint8)
         marg = np.zeros((n_steps, 2))
-        mask = np.uint64((1 << 64) - 1) if D * bits >= 64 else np.uint64((1 << (D * bits)) - 1)
+        pred_of = np.zeros((n_steps, NS), dtype=np.int32)   # winning predecessor state per step and state
+        sym_of = np.zeros((n_steps, NS), dtype=np.uint8)    # symbol index of step i on that branch
         sp = np.arange(NS)
         vnew, hnew = sp // NH, sp % NH          # next state = (v', [a_0 .. a_{Lp-2}])
+        released = 0
+
+        def release(t, upto):
+            """trace the best state at step t back to step `released`; emit steps [released, upto)."""
+            s_ = int(np.argmax(pm))
+            for tau in range(t, released - 1, -1):
+                if tau < upto:
+                    out[tau] = sym_of[tau, s_]
+                s_ = int(pred_of[tau, s_])
+
         for i in range(n_steps):
             par = i % self.n_h
             K_leave = self.h_num[(i - Lp + 1) % self.n_h]
@@ -122,18 +141,17 @@ class CpmTrellis:
                 best = np.where(take, cand, best)
                 arg = np.where(take, pred, arg)
                 argx = np.where(take, x, argx)
-            newest = argx if Lp == 1 else hnew // (NH // M)   # symbol index of step i
-            hist = ((hist[arg] << np.uint64(bits)) | newest.astype(np.uint64)) & mask
+            pred_of[i] = arg
+            sym_of[i] = argx if Lp == 1 else hnew // (NH // M)   # symbol index of step i
             pm = best - best.max()
             if return_margin:
                 top = np.sort(best)
                 marg[i] = (min(float(np.min(best - second)), float(top[-1] - top[-2])), amax)
-            if i >= D - 1:
-                s = int(np.argmax(pm))
-                out[i - D + 1] = int((hist[s] >> np.uint64((D - 1) * bits)) & np.uint64((1 << bits) - 1))
-        s = int(np.argmax(pm))
-        for d in range(min(D - 1, n_steps)):
-            out[n_steps - 1 - d] = int((hist[s] >> np.uint64(d * bits)) & np.uint64((1 << bits) - 1))
+            if (i + 1) % D == 0 and i + 1 >= 2 * D:
+                release(i, i + 1 - D)
+                released = i + 1 - D
+        if n_steps:
+            release(n_steps - 1, n_steps)
         if return_margin:
             return out, marg
         return out

@@ -153,7 +153,7 @@ def test_fused_modulate_bank_shape_query():
     if not torch.cuda.is_available():
         h, g, t = _ffi.dbl_array([0.25]), _ffi.dbl_array(freq_pulse_soqpsk_tg(8)), _ffi.dbl_array(np.zeros(146))
         rc = lib.wf_cpm_modulate_bank(ctypes.c_void_p(16), 1, 16, h, 1, g, K, 8, 0.0, 0.0, None, None, 0, 0, None, t, 2, 73, 36, 0,
-                                      15, ctypes.c_void_p(16), 16, None)
+                                      15, ctypes.c_void_p(16), 16, 1, None)
         assert rc == -2  # WF_ERR_DEVICE
 
 

@@ -134,6 +134,7 @@ static inline unsigned __ballot_sync(unsigned, int pred) {
 static inline int __all_sync(unsigned mk, int pred) { return __ballot_sync(mk, pred) == 0xFFFFFFFFu; }
 static inline int __any_sync(unsigned mk, int pred) { return __ballot_sync(mk, pred) != 0u; }
 
+static inline float fmaxf_emu(float a, float b) { return a > b ? a : b; }
 static inline int __popc(unsigned v) { return __builtin_popcount(v); }
 static inline int __ffs(unsigned v) { return __builtin_ffs((int)v); }
 static inline uint32_t __umulhi(uint32_t a, uint32_t b) { return (uint32_t)(((uint64_t)a * b) >> 32); }

@@ -436,6 +436,43 @@ def t_rawbank():
         assert np.array_equal(ca, cb) and ca[:, 2].sum() == B * max(0, min(S, n_calls - 2))
 
 
+def t_modbank():
+    """wf_cpm_modulate_bank (block kernel and the two warp-autonomous kernels) == wf_cpm_modulate + wf_mf_bank, bit for bit"""
+    from waveforms_b200 import mfbank as _mf
+    rng = np.random.default_rng(4)
+    sps = 8
+    pulse = o.pulse_soqpsk_tg(sps)
+    taps, _comb = _mf.pam_taps(pulse, 0.25, sps)
+    taps = np.asarray(taps)
+    tr, trp = darr(taps.real.ravel())
+    hv, hp = darr([0.25])
+    pv, pp = darr(pulse)
+    c = (taps.shape[1] - 1) // 2
+    for B, S in ((3, 40), (5, 200), (2, 520), (3, 1031), (1, 2100)):
+        T = (S + 1) * sps
+        first, n_calls = _mf.symbol_instants(T, sps, 0, 2)
+        ld = (n_calls + 3) & ~3
+        syms = rng.choice(np.array([-2, 0, 2], np.int8), size=(B, S)).astype(np.int8)
+        sg = np.linspace(0.0, 1.5, B).astype(np.float32)
+        pts = (np.arange(B) % 2).astype(np.int32)
+        fid = (1000 + 7 * np.arange(B)).astype(np.uint64)
+        ldrx = T + (T & 1)
+        rx = np.zeros((B, ldrx), np.complex64)
+        ok(L.wf_cpm_modulate(ptr(syms), B, S, hp, 1, pp, pv.size, sps, np.pi / 4, -np.pi / 4, 0, ptr(rx), ldrx, ptr(sg), ptr(pts), 77, 0,
+                             ptr(fid), None))
+        y = np.full((B, ld, 2), np.nan, np.complex64)
+        ok(L.wf_mf_bank(ptr(rx), 0, B, T, ldrx, trp, None, 2, taps.shape[1], c, None, None, 2, sps, first, n_calls, ptr(y), ld, None))
+        assert L.wf_cpm_modulate_bank_supported(pv.size, sps, 2, taps.shape[1], c, first, S, n_calls) == 1
+        for tune in (0, 1, 2):
+            z = np.full((B, ld, 2), np.nan, np.complex64)
+            ok(L.wf_cpm_modulate_bank(ptr(syms), B, S, hp, 1, pp, pv.size, sps, np.pi / 4, -np.pi / 4, ptr(sg), ptr(pts), 77, 0, ptr(fid),
+                                      trp, 2, taps.shape[1], c, first, n_calls, ptr(z), ld, tune, None))
+            same = np.array_equal(z[:, :n_calls].view(np.uint32), y[:, :n_calls].view(np.uint32))
+            bad = int(np.sum(z[:, :n_calls].view(np.uint32) != y[:, :n_calls].view(np.uint32)))
+            print(f"  B={B} S={S} tune={tune}: fused bank outputs identical to the two-kernel path: {same} ({bad} words differ)")
+            assert same, (B, S, tune)
+
+
 def t_cpm():
     """generic CPM detector (PCM/FM, multi-h) vs oracle/cpm_generic.py, bank + trellis"""
     from oracle.cpm_generic import CpmTrellis
@@ -469,12 +506,63 @@ def t_cpm():
             se = int(np.sum(ref[:, 4:S - 4] != syms[:, 4:S - 4]))
             print(f"  {name} dtype={dtype}: bank err {err:.1e}, decisions differing from oracle {nd}, symbol errors {cnt[0,1]} (oracle {se})")
             if dtype == 1:
-                assert nd == 0 and cnt[0, 1] == se and cnt[0, 2] == B * (S - 8)
+                assert nd == 0 and cnt[0, 1] == se and cnt[0, 2] == B * (S - 8) * bps
             else:
                 assert nd <= 2
 
 
-TESTS = {"lfsr": t_lfsr, "prbs": t_prbs, "mod": t_mod, "modedge": t_modedge, "mf": t_mf, "vit": t_vit, "noise": t_noise, "stream": t_stream, "lean": t_lean, "rawbank": t_rawbank, "cpm": t_cpm}
+def t_cpmfused():
+    """wf_cpm_detect (bank fused into the detector, decision bits + block traceback) vs oracle/cpm_generic.py"""
+    from oracle.cpm_generic import CpmTrellis
+    rng = np.random.default_rng(12)
+    cases = (("pcmfm", o.pulse_pcmfm(8, 4), [7], 10, 2), ("multih", o.pulse_multih(8), [4, 5], 16, 4))
+    for name, pulse, hnum, p, M in cases:
+        tr = CpmTrellis(pulse, hnum, p, M, 8, 2)
+        bps = 1 if M == 2 else 2
+        taps = tr.bank_taps()
+        tre, tim = np.ascontiguousarray(taps.real.ravel()), np.ascontiguousarray(taps.imag.ravel())
+        hn = np.array(hnum, np.int32)
+        for S, depth, ebn0, tune in ((200, 0, 5.0, 0), (67, 5, 3.0, 0), (33, 16, 4.0, 2), (130, 32, 2.0, 4), (7, 0, 6.0, 0), (1, 0, 6.0, 0),
+                                     (96, 8, 1.0, 0)):
+            B = 3 if name == "multih" else 35   # PCM/FM: more than one warp, a ragged last warp
+            bits = rng.integers(0, 2, (B, S * bps)).astype(np.uint8)
+            syms = np.ascontiguousarray(np.stack([o.map_pcmfm(b) if M == 2 else o.map_multih(b) for b in bits]))
+            sg = o.sigma_from_ebn0_db(ebn0, 8, bps)
+            rx = np.stack([o.cpm_modulate_closed_form(sy, np.array(hnum) / p, pulse, 8) * np.exp(-1j * np.pi / 4) for sy in syms])
+            rx = (rx + sg * (rng.normal(size=rx.shape) + 1j * rng.normal(size=rx.shape))).astype(np.complex64)
+            T = rx.shape[1]
+            assert T == (S + 1) * 8
+            sup = L.wf_cpm_detect_supported(0, T, T, ptr(tre), ptr(tim), 8, tr.first_instant, S, M, 2, p, ptr(hn), len(hnum), depth)
+            assert sup == 1, (name, S, depth)
+            dec = np.full((B, S), 99, np.int8)
+            cnt = np.zeros((1, 3), np.int64)
+            skip = 4 if S > 8 else 0
+            ok(L.wf_cpm_detect(ptr(rx), 0, B, T, T, ptr(tre), ptr(tim), 8, tr.first_instant, S, M, 2, p, ptr(hn), len(hnum), depth,
+                               ptr(dec), ptr(syms), S, skip, skip, None, ptr(cnt), tune, None))
+            D = depth or 16
+            nd = 0
+            for b in range(B):
+                ref, mg = tr.detect(tr.bank(rx[b].astype(np.complex128), S), depth=D, return_margin=True)
+                ref = 2 * ref.astype(np.int64) - (M - 1)
+                rel = mg[:, 0] / np.maximum(mg[:, 1], 1.0)
+                for k in np.flatnonzero(dec[b] != ref):
+                    nd += 1
+                    m = rel[k:k + 2 * D].min()
+                    assert m < 1e-5, (name, S, depth, b, k, m)
+            se = int(np.sum(dec[:, skip:S - skip] != syms[:, skip:S - skip]))
+            be = int(sum(bin(int(x)).count("1") for x in (((dec[:, skip:S - skip].astype(int) + M - 1) >> 1) ^
+                                                         ((syms[:, skip:S - skip].astype(int) + M - 1) >> 1)).ravel()))
+            assert cnt[0].tolist() == [be, se, B * max(0, S - 2 * skip) * bps], (name, S, depth, cnt, be, se)
+            print(f"  {name} S={S} depth={depth} tune={tune}: {nd} decisions differ from the float64 oracle (all near-ties), "
+                  f"symbol errors {se}")
+        # unsupported shapes are refused, not run
+        assert L.wf_cpm_detect_supported(1, 808, 808, ptr(tre), ptr(tim), 8, tr.first_instant, 100, M, 2, p, ptr(hn), len(hnum), 0) == 0
+        assert L.wf_cpm_detect_supported(0, 808, 808, ptr(tre), ptr(tim), 8, 0, 100, M, 2, p, ptr(hn), len(hnum), 0) == 0
+        bad = tre.copy(); bad[3] += 0.25
+        assert L.wf_cpm_detect_supported(0, 808, 808, ptr(bad), ptr(tim), 8, tr.first_instant, 100, M, 2, p, ptr(hn), len(hnum), 0) == 0
+
+
+TESTS = {"lfsr": t_lfsr, "prbs": t_prbs, "mod": t_mod, "modedge": t_modedge, "mf": t_mf, "vit": t_vit, "noise": t_noise, "stream": t_stream, "lean": t_lean, "rawbank": t_rawbank, "cpm": t_cpm, "cpmfused": t_cpmfused, "modbank": t_modbank}
 
 if __name__ == "__main__":
     names = sys.argv[1:] or list(TESTS)

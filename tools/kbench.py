@@ -20,7 +20,7 @@ import torch  # noqa: E402
 from waveforms_b200.linksim import LinkConfig, LinkSimulator  # noqa: E402
 
 BYTES = {"prbs_encode": 1.125, "modulate_awgn": 65.0, "mf_bank": 80.0, "viterbi_bert": 16.125,  # PAM raw-bank link (bench.py)
-         "modulate_awgn_bank": 17.0}
+         "modulate_awgn_bank": 17.0, "detect_fused": 65.0}  # detect_fused: 64 B of rx + 1 B of transmitted symbol per symbol
 
 
 def measure(sim, B, reps, cfg):
@@ -44,6 +44,7 @@ def measure(sim, B, reps, cfg):
         ms /= reps
         out[name] = {"ms": round(ms, 4), "algo_gbs": round(BYTES[name] * bits / ms / 1e6, 1)}
     out["waveform"] = cfg.waveform
+    out["extra"] = {k: v for k, v in cfg.extra.items() if v}
     out["frames"] = B
     out["total_ms"] = round(sum(v["ms"] for v in out.values() if isinstance(v, dict)), 4)
     out["bits_per_s"] = round(bits / out["total_ms"] * 1e3, 1)
@@ -58,8 +59,12 @@ def main():
     ap.add_argument("--waveform", default="soqpsk-tg", help="LinkConfig.waveform (algo_gbs figures are SOQPSK/PAM bytes)")
     ap.add_argument("--env", default=None)
     ap.add_argument("--fused", action="store_true")
+    ap.add_argument("--extra", default=None, help="JSON dict merged into LinkConfig.extra (e.g. '{\"tune\": 4}')")
     a = ap.parse_args()
-    cfg = LinkConfig(n_bits=4096, detector=a.detector, waveform=a.waveform, extra={"fused": a.fused})
+    extra = {"fused": a.fused}
+    if a.extra:
+        extra.update(json.loads(a.extra))
+    cfg = LinkConfig(n_bits=4096, detector=a.detector, waveform=a.waveform, extra=extra)
     sim = LinkSimulator(cfg, device=torch.device("cuda", 0), max_batch=a.frames)
     if a.env:
         name, vals = a.env.split("=")

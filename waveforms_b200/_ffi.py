@@ -31,7 +31,7 @@ PROTOTYPES = {
                                _vp, _vp, _u64, _u64, _vp, _vp]),
     "wf_cpm_modulate_bank_supported": (_i32, [_i32, _i32, _i32, _i32, _i32, _i64, _i64, _i64]),
     "wf_cpm_modulate_bank": (_i32, [_vp, _i64, _i64, _vp, _i32, _vp, _i32, _i32, _dbl, _dbl, _vp, _vp, _u64, _u64, _vp,
-                                    _vp, _i32, _i32, _i32, _i64, _i64, _vp, _i64, _vp]),
+                                    _vp, _i32, _i32, _i32, _i64, _i64, _vp, _i64, _i32, _vp]),
     "wf_frequency_modulate": (_i32, [_vp, _i64, _i64, _i64, _i32, _dbl, _i32, _vp, _i64, _vp]),
     "wf_phase_modulate": (_i32, [_vp, _i64, _dbl, _i32, _vp, _vp]),
     "wf_awgn_add": (_i32, [_vp, _i32, _i64, _i64, _i64, _vp, _vp, _u64, _u64, _vp, _vp]),
@@ -44,6 +44,9 @@ PROTOTYPES = {
                                           _vp]),
     "wf_viterbi_cpm": (_i32, [_vp, _i32, _i64, _i64, _i64, _i32, _i32, _i32, _vp, _i32, _i32, _vp, _vp, _i64, _i64, _i64,
                               _vp, _vp, _vp]),
+    "wf_cpm_detect_supported": (_i32, [_i32, _i64, _i64, _vp, _vp, _i32, _i64, _i64, _i32, _i32, _i32, _vp, _i32, _i32]),
+    "wf_cpm_detect": (_i32, [_vp, _i32, _i64, _i64, _i64, _vp, _vp, _i32, _i64, _i64, _i32, _i32, _i32, _vp, _i32, _i32,
+                             _vp, _vp, _i64, _i64, _i64, _vp, _vp, _i32, _vp]),
     "wf_bert": (_i32, [_vp, _vp, _i64, _vp, _vp, _i64, _i64, _i64, _i64, _vp, _vp, _vp]),
 }
 

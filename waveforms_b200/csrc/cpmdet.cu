@@ -1,17 +1,28 @@
-// cpmdet.cu -- A11/A12: generic pulse-truncated coherent CPM trellis detector
+// cpmdet.cu -- A11/A12: pulse-truncated coherent CPM trellis detection
 // (PCM/FM, ARTM multi-h CPM, any M-ary single/multi-h CPM).  The reference has NO detector
 // for these waveforms (waveforms.viterbi exports only SOQPSKTrellisDetector); the design
 // generalises its pulse-truncation bank + Re{e^{-j theta} z} metric
 // (examples/soqpsk_detection.py:134-156, viterbi/algorithm.py:57-63) and is specified by the
 // float64 statement oracle/cpm_generic.py (parity unpinned).
 //
-// One WARP per frame, lane-per-state: state s = v * M^(Lp-1) + hist with v the phase state
-// (theta = pi v / p, v in Z_2p) and hist the Lp-1 newest symbols; lane l owns states l, l+32, ...
-// Path metrics and REGISTER-EXCHANGE survivor words (the last `depth` symbols of each survivor,
-// 64 bits) ping-pong in shared memory, so there is no traceback: each step emits the oldest symbol
-// of the best survivor.  Per step the warp stages the bank outputs of the step, every lane does M
-// add-compare-selects per owned state, then two warp reductions (max for normalisation, argmax for
-// the output) run on shuffles.
+// State s = v * M^(Lp-1) + hist with v the phase state (theta = pi v / p, v in Z_2p) and hist the
+// Lp-1 newest symbols.  Decision rule, all kernels (oracle/cpm_generic.py:detect): BLOCK RELEASE with
+// survivor memory 2 D -- whenever (t + 1) is a multiple of D and t + 1 >= 2 D the survivor of the best
+// state at step t (largest metric, lowest index on ties) releases the symbols of steps
+// [t - 2D + 1, t - D]; the best final survivor releases the rest.
+//
+// Three kernels:
+//   viterbi_cpm_kernel         any (M, Lp, h list, p), float / double, bank outputs z as input: one warp
+//                              per frame, lane-per-state, metrics and 2D-symbol REGISTER-EXCHANGE
+//                              survivor words in shared memory (the parity instantiation).
+//   cpm_detect_m2l2_kernel     binary, memory 2, single h (IRIG PCM/FM): one THREAD per frame, reads the
+//                              RECEIVED SAMPLES, computes the step's 4 correlations itself (the bank is
+//                              fused in), add-compare-select on registers, one decision BIT per state per
+//                              step packed into a 64-bit word in shared memory, traceback every D steps.
+//   cpm_detect_lanev_kernel    M = 4, memory 2, 32 phase states, two h (ARTM CPM): one WARP per frame, lane
+//                              = phase state, bank fused in (16 correlations spread over the lanes),
+//                              metrics exchanged by shuffles, 2 decision bits per state per step in shared
+//                              memory, warp-uniform traceback every D steps.
 #include "common.cuh"
 #include <math.h>
 #include <string.h>
@@ -25,12 +36,13 @@ constexpr int kCpmMaxCols = 128;  // n_h * M^Lp bank outputs per step
 constexpr int kCpmMaxH = 8;
 
 struct CpmParams {
-  const void* z;
+  const void* z;    // bank outputs (viterbi_cpm_kernel)
+  const void* rx;   // received samples complex64[B][ld_rx] (fused kernels)
   int8_t* dec_syms;
   const int8_t* tx_syms;
   const int32_t* point;
   unsigned long long* counters;
-  int64_t B, n_steps, ld_z, S, skip_head, skip_tail;
+  int64_t B, n_steps, ld_z, S, skip_head, skip_tail, Tn, ld_rx;
   int M, Lp, p, n_h, depth, bits, n_filt, n_hist, n_states, n_cols;
   int delta[kCpmMaxH][16];  // (K_h * alphabet[x]) mod 2p
 };
@@ -60,7 +72,8 @@ viterbi_cpm_kernel(const __grid_constant__ CpmParams p) {
 
   const int M = p.M, Lp = p.Lp, NS = p.n_states, NH = p.n_hist, bits = p.bits, D = p.depth;
   const int NHM = NH >= M ? NH / M : 1;
-  const unsigned long long hmask = (D * bits >= 64) ? ~0ull : ((1ull << (D * bits)) - 1ull);
+  // survivor words hold the newest 2 D symbols (2 D bits <= 64, checked by the launcher)
+  const unsigned long long hmask = (2 * D * bits >= 64) ? ~0ull : ((1ull << (2 * D * bits)) - 1ull);
   const unsigned sym_mask = (1u << bits) - 1u;
   const C* zrow = reinterpret_cast<const C*>(p.z) + frame * p.ld_z * p.n_cols;
   const int8_t* tx = p.tx_syms ? p.tx_syms + frame * p.S : nullptr;
@@ -86,6 +99,7 @@ viterbi_cpm_kernel(const __grid_constant__ CpmParams p) {
   };
 
   int cur = 0;
+  int64_t released = 0;
   for (int64_t i = 0; i < n_steps; ++i) {
     const int par = (int)(i % p.n_h);
     int lpar = (int)((i - Lp + 1) % p.n_h);
@@ -139,10 +153,17 @@ viterbi_cpm_kernel(const __grid_constant__ CpmParams p) {
     }
     __syncwarp();
     cur ^= 1;
-    if (lane == 0 && i >= D - 1) emit(i - D + 1, (unsigned)((hs[cur][best_s] >> ((D - 1) * bits)) & sym_mask));
-    if (i == n_steps - 1 && lane == 0) {  // flush the tail from the best final survivor
+    // block release: the oldest D symbols of the best survivor's 2 D-symbol word
+    if ((i + 1) % D == 0 && i + 1 >= 2 * D) {
+      if (lane == 0) {
+        const unsigned long long h = hs[cur][best_s];
+        for (int j = 0; j < D; ++j) emit(i - 2 * D + 1 + j, (unsigned)((h >> ((2 * D - 1 - j) * bits)) & sym_mask));
+      }
+      released = i + 1 - D;
+    }
+    if (i == n_steps - 1 && lane == 0) {  // the best final survivor releases what is still held (< 2 D symbols)
       const unsigned long long h = hs[cur][best_s];
-      for (int d = 0; d < D - 1 && d < n_steps; ++d) emit(n_steps - 1 - d, (unsigned)((h >> (d * bits)) & sym_mask));
+      for (int64_t idx = released; idx < n_steps; ++idx) emit(idx, (unsigned)((h >> ((n_steps - 1 - idx) * bits)) & sym_mask));
     }
   }
   if (lane == 0 && p.counters) {
@@ -153,99 +174,40 @@ viterbi_cpm_kernel(const __grid_constant__ CpmParams p) {
   }
 }
 
-// ---------------------------------------------------------------------------
-// Binary, memory-2, single-h shape (IRIG PCM/FM: M = 2, Lp = 2, h = K/p): the same recursion with
-// one THREAD per frame.  The 2 * P2 path metrics live in registers (old and new generation), every
-// predecessor index, filter index and rotation is a compile-time constant (rotations are
-// constant-bank operands), and only the 64-bit survivor words ping-pong through shared memory,
-// laid out [state][thread] so a warp's LDS.64 / STS.64 are conflict free.  Per frame-step this is
-// ~25 instructions instead of the ~400 of the lane-per-state kernel (which spends a whole warp, two
-// shuffle reductions and run-time index arithmetic on one frame).  Semantics are identical: strict
-// '>' keeps x = 0 on ties, the best state is the LOWEST index with the maximum metric, metrics
-// are normalised by the maximum, the oldest survivor symbol of the best state is emitted.
-// ---------------------------------------------------------------------------
-constexpr int kM2Threads = 64;
-
-// SV: survivor word, uint32_t when depth <= 32 (the default: half the shared memory -- 7 blocks per SM, so the
-// 1024 blocks of a 65 536-frame batch are ONE wave instead of 1.4 -- and half the select / shift work)
-template <int P2, int D0, int D1, typename SV>
-__global__ void __launch_bounds__(kM2Threads, sizeof(SV) == 4 ? 7 : 5)
-viterbi_cpm_m2l2_kernel(const __grid_constant__ CpmParams p, const __grid_constant__ CpmRot rot) {
-  constexpr int NS = 2 * P2;
-  __shared__ SV sv_s[2][NS][kM2Threads];
-  const int tid = threadIdx.x;
-  const int64_t frame = (int64_t)blockIdx.x * kM2Threads + tid;
-  if (frame >= p.B) return;  // no barriers in this kernel: every thread is autonomous
-
-  const int D = p.depth;
-  const SV hmask = (D >= (int)(8 * sizeof(SV))) ? (SV)~(SV)0 : (SV)(((SV)1 << D) - (SV)1);
-  const float4* zrow = reinterpret_cast<const float4*>(p.z) + frame * p.ld_z * 2;  // 4 complex64 = 2 float4 per step
-  const int8_t* tx = p.tx_syms ? p.tx_syms + frame * p.S : nullptr;
-  int8_t* out = p.dec_syms ? p.dec_syms + frame * p.n_steps : nullptr;
-  const int64_t n_steps = p.n_steps;
-  const int64_t cmp_lo = p.skip_head, cmp_hi = min(p.S, n_steps) - p.skip_tail;
-
-  float pm[NS], pn[NS];
-#pragma unroll
-  for (int s = 0; s < NS; ++s) { pm[s] = 0.f; sv_s[0][s][tid] = (SV)0; }
-
-  unsigned long long sym_err = 0, compared = 0;
-  auto emit = [&](int64_t idx, unsigned v) {
-    if (out) out[idx] = (int8_t)(2 * (int)v - 1);
-    if (tx && idx >= cmp_lo && idx < cmp_hi) {
-      const unsigned t = (unsigned)(((int)tx[idx] + 1) >> 1);
-      sym_err += (t != v) ? 1u : 0u;
-      ++compared;
-    }
-  };
-
-  int cur = 0;
-  float4 za = n_steps > 0 ? zrow[0] : make_float4(0.f, 0.f, 0.f, 0.f);
-  float4 zb = n_steps > 0 ? zrow[1] : make_float4(0.f, 0.f, 0.f, 0.f);
-  for (int64_t i = 0; i < n_steps; ++i) {
-    const float zx[4] = {za.x, za.z, zb.x, zb.z}, zy[4] = {za.y, za.w, zb.y, zb.w};
-    if (i + 1 < n_steps) { za = zrow[2 * (i + 1)]; zb = zrow[2 * (i + 1) + 1]; }  // next step's sector, a step ahead
-    const SV(*ho)[kM2Threads] = sv_s[cur];
-    SV(*hn)[kM2Threads] = sv_s[cur ^ 1];
-#pragma unroll
-    for (int s = 0; s < NS; ++s) {
-      constexpr int dummy = 0; (void)dummy;
-      const int vnew = s >> 1, hnew = s & 1;
-      const int vp0 = (vnew - D0 + 2 * P2) % P2, vp1 = (vnew - D1 + 2 * P2) % P2;
-      const int pred0 = vp0 * 2, pred1 = vp1 * 2 + 1;
-      const int f0 = hnew * 2, f1 = hnew * 2 + 1;
-      // pm + Re{e^{-j pi v/p} z} = pm + (cos * zr + sin * zi), evaluated in this order (as in the generic kernel)
-      const float c0 = pm[pred0] + (rot.c[vp0] * zx[f0] + rot.s[vp0] * zy[f0]);
-      const float c1 = pm[pred1] + (rot.c[vp1] * zx[f1] + rot.s[vp1] * zy[f1]);
-      const bool win1 = c1 > c0;
-      pn[s] = win1 ? c1 : c0;
-      const SV h = win1 ? ho[pred1][tid] : ho[pred0][tid];
-      hn[s][tid] = (SV)(((SV)(h << 1) | (SV)hnew) & hmask);
-    }
-    float wmax = pn[0];
-#pragma unroll
-    for (int s = 1; s < NS; ++s) wmax = pn[s] > wmax ? pn[s] : wmax;
-    int best_s = NS - 1;
-#pragma unroll
-    for (int s = NS - 2; s >= 0; --s) best_s = (pn[s] == wmax) ? s : best_s;  // lowest index wins
-    if (pn[NS - 1] != wmax && best_s == NS - 1) best_s = 0;                    // unreachable (wmax is one of them)
-#pragma unroll
-    for (int s = 0; s < NS; ++s) pm[s] = pn[s] - wmax;
-    cur ^= 1;
-    if (i >= D - 1) emit(i - D + 1, (unsigned)((sv_s[cur][best_s][tid] >> (D - 1)) & (SV)1));
-    if (i == n_steps - 1) {  // flush the tail from the best final survivor
-      const SV h = sv_s[cur][best_s][tid];
-      for (int d = 0; d < D - 1 && d < n_steps; ++d) emit(n_steps - 1 - d, (unsigned)((h >> d) & (SV)1));
-    }
-  }
-  if (p.counters) {
-    const int64_t pt = p.point ? p.point[frame] : 0;
-    atomicAdd(&p.counters[3 * pt + 0], sym_err);  // binary alphabet: bit errors = symbol errors
-    atomicAdd(&p.counters[3 * pt + 1], sym_err);
-    atomicAdd(&p.counters[3 * pt + 2], compared);
-  }
+// ---- small device helpers -------------------------------------------------------------------------
+__device__ __forceinline__ uint32_t funnel_l1(uint32_t hi, uint32_t lo) {  // (hi << 1) | (lo >> 31)
+#ifdef WF_HOSTEMU
+  return (hi << 1) | (lo >> 31);
+#else
+  return __funnelshift_l(lo, hi, 1);
+#endif
 }
-
+__device__ __forceinline__ float2 fadd2(float2 a, float2 b) {
+#ifdef WF_HOSTEMU
+  return make_float2(a.x + b.x, a.y + b.y);
+#else
+  unsigned long long ra, rb, rd;
+  asm("mov.b64 %0, {%1, %2};" : "=l"(ra) : "f"(a.x), "f"(a.y));
+  asm("mov.b64 %0, {%1, %2};" : "=l"(rb) : "f"(b.x), "f"(b.y));
+  asm("add.rn.f32x2 %0, %1, %2;" : "=l"(rd) : "l"(ra), "l"(rb));
+  float2 d;
+  asm("mov.b64 {%0, %1}, %2;" : "=f"(d.x), "=f"(d.y) : "l"(rd));
+  return d;
+#endif
+}
+__device__ __forceinline__ float2 fmul2(float2 a, float2 b) {
+#ifdef WF_HOSTEMU
+  return make_float2(a.x * b.x, a.y * b.y);
+#else
+  unsigned long long ra, rb, rd;
+  asm("mov.b64 %0, {%1, %2};" : "=l"(ra) : "f"(a.x), "f"(a.y));
+  asm("mov.b64 %0, {%1, %2};" : "=l"(rb) : "f"(b.x), "f"(b.y));
+  asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(rd) : "l"(ra), "l"(rb));
+  float2 d;
+  asm("mov.b64 {%0, %1}, %2;" : "=f"(d.x), "=f"(d.y) : "l"(rd));
+  return d;
+#endif
+}
 // warp-wide max / min in one instruction (CREDUX; sm_100a has the f32 form)
 __device__ __forceinline__ float warp_max_f32(float v) {
 #ifdef WF_HOSTEMU
@@ -273,148 +235,443 @@ __device__ __forceinline__ int warp_min_s32(int v) {
 }
 
 // ---------------------------------------------------------------------------
-// Memory-2 trellises with 2p = 32 phase states (ARTM multi-h: M = 4, h = {4, 5}/16 -> 128 states):
-// one WARP per frame, lane = phase state v, the M history states of a lane in REGISTERS.
-// For Lp = 2 the predecessor of (v, h_new) through oldest symbol x is (v - delta[x], x): the same
-// lane and register for every h_new, so a step needs only M metric shuffles and M survivor
-// shuffles (lane-varying source = v - delta[x]); rotations and source lanes are per-lane registers
-// for each modulation-index parity, the step's M^2 bank outputs come from a 4-deep cp.async ring
-// read by broadcast LDS.128.  No shared-memory metric/survivor ping-pong, no run-time index
-// arithmetic, transmitted symbols fetched 32 at a time.  Same semantics as viterbi_cpm_kernel.
+// Binary, memory-2, single-h shape (IRIG PCM/FM: M = 2, Lp = 2, h = K/p, first instant -1), straight from
+// the received samples.  One THREAD per frame.
+//  * Bank fused in: the step's window is the 8 samples rx[8i-1 .. 8i+6]; the four hypothesis filters are two
+//    complex-conjugate pairs (hypothesis (-a0,-a1) is the conjugate of (a0,a1)), so four real sums per pair,
+//    (A, C) += (x_re, x_im) (c_re, c_re) and (E, B) += (x_re, x_im) (c_im, c_im) -- two packed FFMA2 per
+//    sample and pair, taps as constant-bank operands -- give z = (A - B, E + C) and its partner (A + B, C - E).
+//  * The 2p = 20 rotations fold to 10 products per filter (e^{-j pi (v+10)/10} = -e^{-j pi v/10}); the 2 P2
+//    path metrics live in registers, predecessors / filters / rotations are compile-time indices.
+//  * Survivors: ONE decision bit per state per step (sign of c0 - c1, funnel-shifted into a word) -- 40 bits
+//    stored as one 64-bit word in a shared-memory ring of RING steps, laid out [step][thread] (conflict
+//    free); every D steps the thread traces its best state back 2 D steps and releases D symbols, which are
+//    compared with the transmitted symbols 4 at a time.
+//  * Samples reach the thread through a warp-private cp.async double buffer: CS steps (16 CS samples) of the
+//    warp's 32 rows per chunk, 16-byte units, rows an odd number of units apart (LDS.128 conflict free); the
+//    unit that straddles two steps is carried in registers.
+// Same decisions as oracle/cpm_generic.py up to float32 near-ties (tested with the float64 margins).
 // ---------------------------------------------------------------------------
-constexpr int kLvWarps = 4;
-constexpr int kLvRing = 4;
+constexpr int kBfThreads = 64;  // two autonomous warps
+constexpr int kBfCS = 2;        // steps per staged chunk: 4 CS units of 16 bytes per row
+constexpr int kBfPitch = 4 * kBfCS + 1;
 
-template <int M, int NHH>
-__global__ void __launch_bounds__(kLvWarps * 32)
-viterbi_cpm_lanev_kernel(const __grid_constant__ CpmParams p, const __grid_constant__ CpmRot rot) {
-  constexpr int NF = M * M;                 // bank outputs per step and parity
-  constexpr int BITS = M == 2 ? 1 : (M == 4 ? 2 : (M == 8 ? 3 : 4));
-  __align__(16) __shared__ float2 z_s[kLvWarps][kLvRing][NF];
+struct CpmPairTaps {  // [pair][sample u][0: (c_re, c_re), 1: (c_im, c_im)] of the conj(template) of filters 0 and 1
+  alignas(16) float t[2][8][2][2];
+};
+
+template <int P2, int D0, int D1, int RING, int NORM>
+__global__ void __launch_bounds__(kBfThreads)
+cpm_detect_m2l2_kernel(const __grid_constant__ CpmParams p, const __grid_constant__ CpmRot rot,
+                       const __grid_constant__ CpmPairTaps tp) {
+  constexpr int NS = 2 * P2, HP = P2 / 2;
+  static_assert(NS <= 64 && NS > 32 && (RING & (RING - 1)) == 0, "40-state layout: one 64-bit decision word per step");
+  __align__(16) __shared__ float4 tile[2][kBfThreads * kBfPitch];
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  unsigned long long* tb = reinterpret_cast<unsigned long long*>(smem_raw);  // [RING][kBfThreads]
+
+  const int tid = threadIdx.x, lane = tid & 31, wrow0 = tid & ~31;
+  const int64_t wframe0 = (int64_t)blockIdx.x * kBfThreads + wrow0;
+  if (wframe0 >= p.B) return;  // whole warp; only warp-level synchronisation below
+  const int64_t frame = wframe0 + lane;
+  const bool active = frame < p.B;
+  const int n_steps = (int)p.n_steps, S = (int)p.S, D = p.depth;
+  const int8_t* tx = (active && p.tx_syms) ? p.tx_syms + frame * p.S : nullptr;
+  int8_t* out = (active && p.dec_syms) ? p.dec_syms + frame * p.n_steps : nullptr;
+  const int cmp_lo = (int)p.skip_head, cmp_hi = min(S, n_steps) - (int)p.skip_tail;
+  const bool tx_vec = tx != nullptr && ((reinterpret_cast<uintptr_t>(tx) & 3) == 0);
+
+  // staging pattern: unit e = lane + 32 r (r < CS) of the warp's 32 rows x 4 CS units -> row e / (4 CS), unit e % (4 CS)
+  constexpr int UPR = 4 * kBfCS;              // units per row per chunk
+  constexpr int RPS = 32 / UPR;               // rows covered by one 32-lane pass
+  const int64_t row_units = p.ld_rx / 2;      // ld_rx is even (checked by the launcher)
+  const int64_t last_row = p.B - 1 - wframe0; // rows beyond it are clamped to it (valid memory, never used)
+  const float4* src0 = reinterpret_cast<const float4*>(p.rx) + wframe0 * row_units + (lane % UPR);
+  const int dst0 = (wrow0 + lane / UPR) * kBfPitch + (lane % UPR);
+  auto stage = [&](int buf, int chunk) {
+#pragma unroll
+    for (int r = 0; r < UPR; ++r) {
+      int64_t row = lane / UPR + RPS * r;
+      if (row > last_row) row = last_row;
+      cp_async_cg16(&tile[buf][dst0 + RPS * r * kBfPitch], src0 + row * row_units + (int64_t)chunk * UPR);
+    }
+    cp_async_commit();
+  };
+
+  float pm[NS];
+#pragma unroll
+  for (int s = 0; s < NS; ++s) pm[s] = 0.f;
+  unsigned sym_err = 0, compared = 0;
+  const float2* tap2 = reinterpret_cast<const float2*>(tp.t);
+
+  // release the symbols of steps [lo, hi) found by tracing state `s` back from step t
+  auto trace_release = [&](int t, int s, int lo, int hi) {
+    unsigned long long bitsw = 0ull;  // bit (tau - lo) = decided symbol index of step tau
+    for (int tau = t; tau >= lo; --tau) {
+      const unsigned long long w = tb[(tau & (RING - 1)) * kBfThreads + tid];
+      const unsigned b = (unsigned)(w >> (s < 32 ? 31 - s : 71 - s)) & 1u;  // which predecessor won
+      if (tau < hi) bitsw |= (unsigned long long)(s & 1) << (tau - lo);
+      int vp = (s >> 1) - (b ? D1 : D0);
+      vp += vp < 0 ? P2 : 0;
+      s = 2 * vp + (int)b;
+    }
+    const int n = hi - lo;
+    if (out)
+      for (int j = 0; j < n; ++j) out[lo + j] = (int8_t)(2 * (int)((bitsw >> j) & 1ull) - 1);
+    if (tx) {
+      for (int j0 = 0; j0 < n; j0 += 4) {
+        const int k = lo + j0;
+        unsigned txb = 0, msk = 0;
+        if (tx_vec && (k & 3) == 0 && j0 + 4 <= n && k + 4 <= S) {
+          const uint32_t wv = ~*reinterpret_cast<const uint32_t*>(tx + k);  // +1 -> sign bit clear -> 1 after the inversion
+          txb = ((wv >> 7) & 1u) | ((wv >> 14) & 2u) | ((wv >> 21) & 4u) | ((wv >> 28) & 8u);
+#pragma unroll
+          for (int e = 0; e < 4; ++e) msk |= (k + e >= cmp_lo && k + e < cmp_hi) ? (1u << e) : 0u;
+        } else {
+          for (int e = 0; e < 4 && j0 + e < n; ++e) {
+            if (k + e >= cmp_lo && k + e < cmp_hi) {
+              msk |= 1u << e;
+              txb |= (unsigned)(((int)tx[k + e] + 1) >> 1) << e;
+            }
+          }
+        }
+        sym_err += __popc(((unsigned)(bitsw >> j0) ^ txb) & msk);
+        compared += __popc(msk);
+      }
+    }
+  };
+
+  const int n_chunks = (n_steps + kBfCS - 1) / kBfCS;
+  if (n_chunks > 0) stage(0, 0);
+  float2 carry = make_float2(0.f, 0.f);  // sample 8 i - 1 (zero before the frame)
+  int released = 0;
+  for (int c = 0; c < n_chunks; ++c) {
+    if (c + 1 < n_chunks) {
+      stage((c + 1) & 1, c + 1);
+      cp_async_wait<1>();
+    } else {
+      cp_async_wait<0>();
+    }
+    __syncwarp();
+    const float4* row = &tile[c & 1][tid * kBfPitch];
+#pragma unroll
+    for (int u = 0; u < kBfCS; ++u) {
+      const int i = c * kBfCS + u;
+      if (i < n_steps) {
+        // ---- the step's window and its four correlations --------------------------------------
+        float2 w[8];
+        w[0] = carry;
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+          const float4 v = row[4 * u + q];
+          if (q < 3) { w[2 * q + 1] = make_float2(v.x, v.y); w[2 * q + 2] = make_float2(v.z, v.w); }
+          else { w[7] = make_float2(v.x, v.y); carry = make_float2(v.z, v.w); }
+        }
+        float zx[4], zy[4];
+#pragma unroll
+        for (int pr = 0; pr < 2; ++pr) {
+          float2 ac = make_float2(0.f, 0.f), eb = make_float2(0.f, 0.f);
+#pragma unroll
+          for (int k = 0; k < 8; ++k) {
+            ac = ffma2(w[k], tap2[(pr * 8 + k) * 2 + 0], ac);
+            eb = ffma2(w[k], tap2[(pr * 8 + k) * 2 + 1], eb);
+          }
+          zx[pr] = ac.x - eb.y; zy[pr] = eb.x + ac.y;          // filter pr
+          zx[3 - pr] = ac.x + eb.y; zy[3 - pr] = ac.y - eb.x;  // its conjugate partner
+        }
+        // ---- Re{e^{-j pi k/p} z_f}, k < p (the other half of the circle is the negative) ---------
+        float r[HP][4];
+#pragma unroll
+        for (int k = 0; k < HP; ++k)
+#pragma unroll
+          for (int f = 0; f < 4; ++f)
+            r[k][f] = k == 0 ? zx[f] : ((2 * k == HP) ? zy[f] : rot.c[k] * zx[f] + rot.s[k] * zy[f]);
+        // ---- add-compare-select: one decision bit per state -------------------------------------
+        float pn[NS];
+        uint32_t w0 = 0, w1 = 0;
+#pragma unroll
+        for (int s = 0; s < NS; ++s) {
+          const int vnew = s >> 1, hnew = s & 1;
+          const int vp0 = (vnew - D0 + 2 * P2) % P2, vp1 = (vnew - D1 + 2 * P2) % P2;
+          const int f0 = hnew * 2, f1 = hnew * 2 + 1;
+          const float c0 = vp0 < HP ? pm[2 * vp0] + r[vp0 % HP][f0] : pm[2 * vp0] - r[vp0 % HP][f0];
+          const float c1 = vp1 < HP ? pm[2 * vp1 + 1] + r[vp1 % HP][f1] : pm[2 * vp1 + 1] - r[vp1 % HP][f1];
+          const float d = c0 - c1;  // negative <=> c1 > c0: strict, so the lower x keeps ties
+          pn[s] = fmaxf(c0, c1);
+          if (s < 32) w0 = funnel_l1(w0, __float_as_uint(d));
+          else w1 = funnel_l1(w1, __float_as_uint(d));
+        }
+        tb[(i & (RING - 1)) * kBfThreads + tid] = (unsigned long long)w0 | ((unsigned long long)w1 << 32);
+        const bool rel = ((i + 1) % D == 0 && i + 1 >= 2 * D) || i == n_steps - 1;
+        if (rel || NORM == 1 || (i % NORM) == NORM - 1) {
+          float wmax = pn[0];
+#pragma unroll
+          for (int s = 1; s < NS; ++s) wmax = fmaxf(wmax, pn[s]);
+          if (rel) {
+            int best_s = NS - 1;
+#pragma unroll
+            for (int s = NS - 2; s >= 0; --s) best_s = (pn[s] == wmax) ? s : best_s;  // lowest index wins
+            if ((i + 1) % D == 0 && i + 1 >= 2 * D) {
+              trace_release(i, best_s, released, i + 1 - D);
+              released = i + 1 - D;
+            }
+            if (i == n_steps - 1) trace_release(i, best_s, released, n_steps);
+          }
+#pragma unroll
+          for (int s = 0; s < NS; ++s) pm[s] = pn[s] - wmax;
+        } else {
+#pragma unroll
+          for (int s = 0; s < NS; ++s) pm[s] = pn[s];
+        }
+      }
+    }
+    __syncwarp();  // all lanes are done with tile[c & 1] before chunk c + 2 is staged into it
+  }
+  if (p.counters) {
+    // binary alphabet: bit errors = symbol errors; one atomic triple per warp when the points agree
+    const uint32_t full = 0xFFFFFFFFu;
+    const int32_t pt = (active && p.point) ? p.point[frame] : 0;
+    const int32_t pt0 = __shfl_sync(full, pt, 0);
+    unsigned long long se = active ? sym_err : 0u, nc = active ? compared : 0u;
+    if (__all_sync(full, !active || pt == pt0)) {
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) {
+        se += __shfl_xor_sync(full, se, o);
+        nc += __shfl_xor_sync(full, nc, o);
+      }
+      if (lane == 0) {
+        atomicAdd(&p.counters[3 * (int64_t)pt0 + 0], se);
+        atomicAdd(&p.counters[3 * (int64_t)pt0 + 1], se);
+        atomicAdd(&p.counters[3 * (int64_t)pt0 + 2], nc);
+      }
+    } else if (active) {
+      atomicAdd(&p.counters[3 * (int64_t)pt + 0], se);
+      atomicAdd(&p.counters[3 * (int64_t)pt + 1], se);
+      atomicAdd(&p.counters[3 * (int64_t)pt + 2], nc);
+    }
+  }
+}
+
+// ---------------------------------------------------------------------------
+// M = 4, memory 2, 2p = 32 phase states, two modulation indices (ARTM CPM: h = {4, 5}/16 -> 128 states),
+// straight from the received samples.  One WARP per frame, lane = phase state v, the M history states of a
+// lane in REGISTERS (for Lp = 2 the predecessor of (v, h_new) through oldest symbol x is (v - delta[x], x)
+// for every h_new: M metric shuffles per step with per-lane source lanes).
+//  * Bank fused in: only the step's OWN modulation-index parity is computed (16 of the 32 filters), and
+//    only 8 of those -- hypothesis 15 - f is the complex conjugate of f.  Lane = (pair q, which, half):
+//    4 samples x one packed FFMA2 each, (A, C) += x (c_re, c_re) for which = 0, (E, B) += x (c_im, c_im)
+//    for which = 1; two shuffles add the halves, two more swap (A, C) <-> (E, B), and the lane forms
+//    z_q = (A - B, E + C) or z_{15-q} = (A + B, C - E).  The 16 outputs go to shared memory as
+//    (re_x, re_x+1, im_x, im_x+1) quads, so the rotation + add of TWO candidates is one FMUL2 + FFMA2 + FADD2.
+//  * Samples: a 256-sample warp-private ring filled by cp.async, 64 samples (one 16-byte unit per lane)
+//    per chunk, two chunks ahead.
+//  * Survivors: two decision bits per state -- one byte per lane per step -- in a shared-memory ring of RING
+//    steps; every D steps the whole warp walks the best state's path back 2 D steps (warp-uniform: broadcast
+//    byte load, two integer ops per step) and releases D symbols, lane j comparing / storing symbol j.
+// ---------------------------------------------------------------------------
+constexpr int kLfWarps = 4;
+constexpr int kLfRingSamples = 256;
+
+struct CpmLaneTaps {  // conj(template) of filters 0..7 for both parities: [parity][filter][u][re, im]
+  float t[2][8][8][2];
+};
+
+template <int RING, int NORM>
+__global__ void __launch_bounds__(kLfWarps * 32)
+cpm_detect_lanev_kernel(const __grid_constant__ CpmParams p, const __grid_constant__ CpmRot rot,
+                        const __grid_constant__ CpmLaneTaps tp) {
+  constexpr int M = 4, NHH = 2, BITS = 2;
+  __align__(16) __shared__ float2 ring_s[kLfWarps][kLfRingSamples];
+  __align__(16) __shared__ float4 zq_s[kLfWarps][8];          // (re_x, re_x+1, im_x, im_x+1), index 2 h_new + x / 2
+  __shared__ uint8_t tb_s[kLfWarps][RING * 32];
   const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
-  const int64_t frame = (int64_t)blockIdx.x * kLvWarps + wid;
+  const int64_t frame = (int64_t)blockIdx.x * kLfWarps + wid;
   if (frame >= p.B) return;  // whole warp; only warp-level synchronisation below
 
   const int D = p.depth;
-  const unsigned long long hmask = (D * BITS >= 64) ? ~0ull : ((1ull << (D * BITS)) - 1ull);
-  const int n_cols = p.n_cols;
+  const int n_steps = (int)p.n_steps, S = (int)p.S, Tn = (int)p.Tn;
   const int8_t* tx = p.tx_syms ? p.tx_syms + frame * p.S : nullptr;
   int8_t* out = p.dec_syms ? p.dec_syms + frame * p.n_steps : nullptr;
-  const int n_steps = (int)p.n_steps, S = (int)p.S;  // < 2^31 (checked by the launcher): 32-bit index arithmetic
   const int cmp_lo = (int)p.skip_head, cmp_hi = min(S, n_steps) - (int)p.skip_tail;
-  const int sh_old = (D - 1) * BITS;  // position of the oldest symbol of a survivor word
+  const float2* rxrow = reinterpret_cast<const float2*>(p.rx) + frame * p.ld_rx;
+  float2* ring = ring_s[wid];
+  float* zs = reinterpret_cast<float*>(zq_s[wid]);
+  const float4* zq = zq_s[wid];
+  uint8_t* tb = tb_s[wid];
 
-  // per-lane transition tables for each modulation-index parity
+  // per-lane transition tables for each modulation-index parity, as register PAIRS (x, x + 1)
   int src[NHH][M];
-  float rc[NHH][M], rs[NHH][M];
+  float2 rc2[NHH][M / 2], rs2[NHH][M / 2];
 #pragma unroll
   for (int h = 0; h < NHH; ++h)
 #pragma unroll
     for (int x = 0; x < M; ++x) {
       src[h][x] = (lane - p.delta[h][x]) & 31;
-      rc[h][x] = rot.c[src[h][x]];
-      rs[h][x] = rot.s[src[h][x]];
-#ifndef WF_HOSTEMU
-      // pin the values in registers: left alone, the compiler re-reads rot.c[src] in the loop, a
-      // lane-divergent constant-bank access that serialises 32 ways (13 stall cycles per issue in ncu)
-      asm volatile("" : "+r"(src[h][x]), "+f"(rc[h][x]), "+f"(rs[h][x]));
-#endif
+      const float c = rot.c[src[h][x]], s = rot.s[src[h][x]];
+      if (x & 1) { rc2[h][x / 2].y = c; rs2[h][x / 2].y = s; }
+      else { rc2[h][x / 2].x = c; rs2[h][x / 2].x = s; }
     }
+#ifndef WF_HOSTEMU
+  // pin the values in registers: left alone, the compiler re-reads rot.c[src] in the loop, a
+  // lane-divergent constant-bank access that serialises 32 ways
+#pragma unroll
+  for (int h = 0; h < NHH; ++h)
+#pragma unroll
+    for (int j = 0; j < M / 2; ++j)
+      asm volatile("" : "+f"(rc2[h][j].x), "+f"(rc2[h][j].y), "+f"(rs2[h][j].x), "+f"(rs2[h][j].y));
+#pragma unroll
+  for (int h = 0; h < NHH; ++h)
+#pragma unroll
+    for (int x = 0; x < M; ++x) asm volatile("" : "+r"(src[h][x]));
+#endif
+  // bank role of this lane
+  const int bq = lane >> 2, bwhich = (lane >> 1) & 1, bhalf = lane & 1;
+  float2 tapd[NHH][4];
+#pragma unroll
+  for (int h = 0; h < NHH; ++h)
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const float t = tp.t[h][bq][4 * bhalf + j][bwhich];
+      tapd[h][j] = make_float2(t, t);
+    }
+#ifndef WF_HOSTEMU
+#pragma unroll
+  for (int h = 0; h < NHH; ++h)
+#pragma unroll
+    for (int j = 0; j < 4; ++j) asm volatile("" : "+f"(tapd[h][j].x), "+f"(tapd[h][j].y));
+#endif
+  const int bf = bwhich ? 15 - bq : bq;              // the filter this lane finishes
+  const int zword = 4 * (bf >> 1) + (bf & 1);        // its re slot; im is two words further on
 
   float pm[M];
-  unsigned long long sv[M];
 #pragma unroll
-  for (int h = 0; h < M; ++h) { pm[h] = 0.f; sv[h] = 0ull; }
-
-  // Decisions come out in ascending order, one per step: lane (idx mod 32) keeps decision idx, and once
-  // a group of 32 is complete every lane stores / compares ITS symbol (one coalesced 32-byte store and
-  // one 32-byte load per 32 steps; no per-step divergent branch, byte store or shuffle).
+  for (int h = 0; h < M; ++h) pm[h] = 0.f;
   unsigned sym_err = 0, bit_err = 0, compared = 0;  // per lane, reduced at the end
-  unsigned dec_reg = 0;
-  auto flush_group = [&](int last_idx) {  // decisions (last_idx & ~31) .. last_idx are in the lanes' dec_reg
-    const int k = (last_idx & ~31) + lane;
-    if (k <= last_idx) {
-      if (out) out[k] = (int8_t)(2 * (int)dec_reg - (M - 1));
+
+  // chunk c = samples [64 c - 8, 64 c + 56) -> ring slots (64 c + j) & 255; lane l moves unit l
+  auto stage = [&](int c) {
+    const int n = 64 * c - 8 + 2 * lane;
+    float2* d = ring + ((64 * c + 2 * lane) & (kLfRingSamples - 1));
+    if (n >= 0 && n + 1 < Tn) {
+      cp_async_cg16(d, rxrow + n);
+    } else {
+      d[0] = (n >= 0 && n < Tn) ? rxrow[n] : make_float2(0.f, 0.f);
+      d[1] = make_float2(0.f, 0.f);
+    }
+    cp_async_commit();
+  };
+
+  // walk the path of state (v, hn) back from step t; release steps [lo, hi): lane j handles symbol lo + j (+ 32)
+  auto trace_release = [&](int t, int v, int hn, int lo, int hi) {
+    unsigned long long w0 = 0ull, w1 = 0ull;  // 2 bits per released symbol: the first 32 in w0, the rest in w1
+    for (int tau = t; tau >= lo; --tau) {
+      const unsigned b = tb[(tau & (RING - 1)) * 32 + v];
+      const int x = (int)(b >> (2 * hn)) & 3;
+      if (tau < hi) {
+        const int j = tau - lo;
+        if (j < 32) w0 |= (unsigned long long)hn << (2 * j);
+        else w1 |= (unsigned long long)hn << (2 * (j - 32));
+      }
+      v = (v - p.delta[(tau + 1) & 1][x]) & 31;  // transition parity (tau - Lp + 1) % 2
+      hn = x;
+    }
+    const int n = hi - lo;
+    for (int j = lane; j < n; j += 32) {
+      const unsigned dec = (unsigned)((j < 32 ? w0 >> (2 * j) : w1 >> (2 * (j - 32))) & 3ull);
+      const int k = lo + j;
+      if (out) out[k] = (int8_t)(2 * (int)dec - (M - 1));
       if (tx && k >= cmp_lo && k < cmp_hi) {
-        const unsigned t = (unsigned)(((int)tx[k] + (M - 1)) >> 1);
-        sym_err += (t != dec_reg) ? 1u : 0u;
-        bit_err += __popc((t ^ dec_reg) & (unsigned)(M - 1));
+        const unsigned tt = (unsigned)(((int)tx[k] + (M - 1)) >> 1);
+        sym_err += (tt != dec) ? 1u : 0u;
+        bit_err += __popc((tt ^ dec) & (unsigned)(M - 1));
         compared += BITS;  // column 2 counts compared BITS for every waveform
       }
     }
   };
-  auto emit = [&](int idx, unsigned v) {  // executed by every lane with the same (idx, v)
-    dec_reg = (lane == (idx & 31)) ? v : dec_reg;
-    if ((idx & 31) == 31 || idx == n_steps - 1) flush_group(idx);
-  };
 
-  // bank outputs of step j: NF complex64 at column (j mod NHH) NF of row j; 16 bytes per lane, NF/2 lanes
-  const float2* zst = reinterpret_cast<const float2*>(p.z) + frame * p.ld_z * n_cols + 2 * lane;
-  float2* zdst = &z_s[wid][0][2 * lane];
-  int st_j = 0;  // next step to stage
-  auto stage = [&](int par) {
-    if (st_j < n_steps && lane < NF / 2) cp_async_cg16(zdst + (st_j & (kLvRing - 1)) * NF, zst + par * NF);
-    cp_async_commit();
-    zst += n_cols;
-    ++st_j;
-  };
-  static_assert((kLvRing & (kLvRing - 1)) == 0 && kLvRing % NHH == 0, "ring slots: power of two, multiple of the h period");
+  stage(0);
+  stage(1);
+  int released = 0;
+  for (int i0 = 0; i0 < n_steps; i0 += 8) {
+    // group g = i0 / 8 reads chunks g and g + 1; chunk g + 2 replaces chunk g - 2 (last read by step i0 - 1)
+    __syncwarp();
+    stage((i0 >> 3) + 2);
+    cp_async_wait<1>();
+    __syncwarp();
 #pragma unroll
-  for (int k = 0; k < kLvRing - 1; ++k) stage(k % NHH);
-
-  for (int i0 = 0; i0 < n_steps; i0 += NHH) {
-#pragma unroll
-    for (int hp = 0; hp < NHH; ++hp) {
-      const int i = i0 + hp;
+    for (int u = 0; u < 8; ++u) {
+      const int i = i0 + u;
       if (i >= n_steps) break;
-      // parity of the filters is i % NHH = hp (i0 is a multiple of NHH); of the transition (i - Lp + 1) % NHH
       constexpr int dummy = 0; (void)dummy;
-      const int lp = (hp + NHH - 1) % NHH;
-      __syncwarp();              // every lane has finished reading the slot that is staged next
-      stage((hp + kLvRing - 1) % NHH);
-      cp_async_wait<kLvRing - 1>();
-      __syncwarp();              // the step's bank outputs are visible to all lanes
-      const float4* zq = reinterpret_cast<const float4*>(z_s[wid][i & (kLvRing - 1)]);
-      float pmx[M];
-      unsigned long long svx[M];
+      const int hp = u & 1;            // filter parity i % 2 (i0 is a multiple of 8)
+      const int lp = (u + 1) & 1;      // transition parity (i - 1) % 2
+      // ---- bank: this lane's four samples, one FFMA2 each ----------------------------------------
+      const int s0 = 8 * i + 7 + 4 * bhalf;  // ring slot of sample 8 i - 1 + 4 half  (slot(n) = (n + 8) & 255)
+      const float2 x0 = ring[s0 & (kLfRingSamples - 1)];
+      const float4 x12 = *reinterpret_cast<const float4*>(ring + ((s0 + 1) & (kLfRingSamples - 1)));
+      const float2 x3 = ring[(s0 + 3) & (kLfRingSamples - 1)];
+      float2 acc = make_float2(0.f, 0.f);
+      acc = ffma2(x0, tapd[hp][0], acc);
+      acc = ffma2(make_float2(x12.x, x12.y), tapd[hp][1], acc);
+      acc = ffma2(make_float2(x12.z, x12.w), tapd[hp][2], acc);
+      acc = ffma2(x3, tapd[hp][3], acc);
+      acc.x += __shfl_xor_sync(0xFFFFFFFFu, acc.x, 1);
+      acc.y += __shfl_xor_sync(0xFFFFFFFFu, acc.y, 1);
+      const float ox = __shfl_xor_sync(0xFFFFFFFFu, acc.x, 2), oy = __shfl_xor_sync(0xFFFFFFFFu, acc.y, 2);
+      // which = 0: own (A, C), other (E, B) -> z_q = (A - B, E + C);  which = 1: own (E, B), other (A, C) -> z_{15-q} = (A + B, C - E)
+      const float zr = bwhich ? ox + acc.y : acc.x - oy;
+      const float zi = bwhich ? oy - acc.x : ox + acc.y;
+      __syncwarp();  // every lane has finished reading the previous step's outputs
+      if (bhalf == 0) { zs[zword] = zr; zs[zword + 2] = zi; }
+      __syncwarp();
+      // ---- add-compare-select ----------------------------------------------------------------------
+      float2 pmx2[M / 2];
 #pragma unroll
-      for (int x = 0; x < M; ++x) {
-        pmx[x] = __shfl_sync(0xFFFFFFFFu, pm[x], src[lp][x]);
-        svx[x] = __shfl_sync(0xFFFFFFFFu, sv[x], src[lp][x]);
+      for (int j = 0; j < M / 2; ++j) {
+        pmx2[j].x = __shfl_sync(0xFFFFFFFFu, pm[2 * j], src[lp][2 * j]);
+        pmx2[j].y = __shfl_sync(0xFFFFFFFFu, pm[2 * j + 1], src[lp][2 * j + 1]);
       }
+      unsigned dec = 0;
       float lmax = -3.0e38f;
 #pragma unroll
       for (int hn = 0; hn < M; ++hn) {
-        float best = 0.f;
-        unsigned long long bsv = 0ull;
+        float2 c2[M / 2];
 #pragma unroll
-        for (int x = 0; x < M; x += 2) {
-          const float4 q = zq[(hn * M + x) / 2];  // two complex outputs: f = hn M + x, f + 1
-          // pm + Re{e^{-j pi v/p} z} = pm + (cos * zr + sin * zi), evaluated in this order
-          const float ca = pmx[x] + (rc[lp][x] * q.x + rs[lp][x] * q.y);
-          const float cb = pmx[x + 1] + (rc[lp][x + 1] * q.z + rs[lp][x + 1] * q.w);
-          if (x == 0 || ca > best) { best = ca; bsv = svx[x]; }
-          if (cb > best) { best = cb; bsv = svx[x + 1]; }
+        for (int j = 0; j < M / 2; ++j) {
+          const float4 q = zq[2 * hn + j];
+          float2 t2 = fmul2(rc2[lp][j], make_float2(q.x, q.y));
+          t2 = ffma2(rs2[lp][j], make_float2(q.z, q.w), t2);
+          c2[j] = fadd2(pmx2[j], t2);
         }
+        // strict '>' tournament: the lowest x keeps ties
+        const bool b01 = c2[0].y > c2[0].x, b23 = c2[1].y > c2[1].x;
+        const float m01 = fmaxf(c2[0].x, c2[0].y), m23 = fmaxf(c2[1].x, c2[1].y);
+        const bool bf2 = m23 > m01;
+        const float best = fmaxf(m01, m23);
+        const unsigned idx = bf2 ? (2u | (b23 ? 1u : 0u)) : (b01 ? 1u : 0u);
+        dec |= idx << (2 * hn);
         pm[hn] = best;
-        sv[hn] = ((bsv << BITS) | (unsigned long long)hn) & hmask;
-        lmax = best > lmax ? best : lmax;
+        lmax = fmaxf(lmax, best);
       }
-      const float wmax = warp_max_f32(lmax);
-      int best_s = 0x7FFFFFFF;  // lowest state index v M + h with the maximum metric
-      unsigned long long my_sv = 0ull;
+      tb[(i & (RING - 1)) * 32 + lane] = (uint8_t)dec;
+      const bool rel = ((i + 1) % D == 0 && i + 1 >= 2 * D) || i == n_steps - 1;
+      if (rel || NORM == 1 || (u % NORM) == NORM - 1) {
+        const float wmax = warp_max_f32(lmax);
+        if (rel) {
+          int best_s = 0x7FFFFFFF;  // lowest state index v M + h with the maximum metric
 #pragma unroll
-      for (int hn = M - 1; hn >= 0; --hn) {
-        if (pm[hn] == wmax) { best_s = lane * M + hn; my_sv = sv[hn]; }
-        pm[hn] -= wmax;
-      }
-      const int wbest = warp_min_s32(best_s);
-      if (i >= D - 1 || i == n_steps - 1) {
-        const unsigned long long h = __shfl_sync(0xFFFFFFFFu, my_sv, wbest / M);  // the best lane's lowest-h survivor
-        if (i >= D - 1) emit(i - D + 1, (unsigned)(h >> sh_old) & (unsigned)(M - 1));
-        if (i == n_steps - 1)  // flush the tail from the best final survivor
-          for (int d = D - 2 < n_steps - 1 ? D - 2 : n_steps - 1; d >= 0; --d)
-            emit(n_steps - 1 - d, (unsigned)(h >> (d * BITS)) & (unsigned)(M - 1));
+          for (int hn = M - 1; hn >= 0; --hn)
+            if (pm[hn] == wmax) best_s = lane * M + hn;
+          const int wbest = warp_min_s32(best_s);
+          __syncwarp();  // this step's decision bytes are visible to the whole warp
+          if ((i + 1) % D == 0 && i + 1 >= 2 * D) {
+            trace_release(i, wbest >> 2, wbest & 3, released, i + 1 - D);
+            released = i + 1 - D;
+          }
+          if (i == n_steps - 1) trace_release(i, wbest >> 2, wbest & 3, released, n_steps);
+        }
+#pragma unroll
+        for (int hn = 0; hn < M; ++hn) pm[hn] -= wmax;
       }
     }
   }
@@ -433,19 +690,11 @@ viterbi_cpm_lanev_kernel(const __grid_constant__ CpmParams p, const __grid_const
   }
 }
 
-}  // namespace wf
-
-extern "C" int wf_viterbi_cpm(const void* d_z, int dtype, int64_t B, int64_t n_steps, int64_t ld_z, int M, int Lp,
-                              int p, const int32_t* h_num, int n_h, int depth, int8_t* d_dec_syms,
-                              const int8_t* d_tx_syms, int64_t S, int64_t skip_head, int64_t skip_tail,
-                              const int32_t* d_point, int64_t* d_counters, void* stream) {
-  using namespace wf;
-  WF_REQUIRE(B >= 0 && n_steps >= 0 && ld_z >= n_steps, "bad shape");
-  WF_REQUIRE(dtype == WF_F32 || dtype == WF_F64, "dtype must be WF_F32 or WF_F64");
+// ---- host side ------------------------------------------------------------------------------------
+static int fill_cpm_params(CpmParams& q, int M, int Lp, int p, const int32_t* h_num, int n_h, int depth) {
   WF_REQUIRE(M >= 2 && M <= 16 && (M & (M - 1)) == 0, "alphabet size M must be a power of two in 2..16");
   WF_REQUIRE(Lp >= 1 && Lp <= 4 && p >= 1 && 2 * p <= 64, "need 1 <= Lp <= 4 and p <= 32");
   WF_REQUIRE(n_h >= 1 && n_h <= kCpmMaxH && h_num, "n_h outside 1..8");
-  CpmParams q;
   memset(&q, 0, sizeof(q));
   q.M = M; q.Lp = Lp; q.p = p; q.n_h = n_h;
   q.bits = 0;
@@ -457,53 +706,159 @@ extern "C" int wf_viterbi_cpm(const void* d_z, int dtype, int64_t B, int64_t n_s
   q.n_cols = n_h * q.n_filt;
   WF_REQUIRE(q.n_states <= kCpmMaxStates, "trellis has %d states (max %d)", q.n_states, kCpmMaxStates);
   WF_REQUIRE(q.n_cols <= kCpmMaxCols, "bank has %d outputs per step (max %d)", q.n_cols, kCpmMaxCols);
-  q.depth = depth > 0 ? depth : (64 / q.bits < 32 ? 64 / q.bits : 32);  // default: 32 symbols
-  WF_REQUIRE(q.depth >= 1 && q.depth * q.bits <= 64, "survivor depth x bits/symbol exceeds 64");
-  WF_REQUIRE(skip_head >= 0 && skip_tail >= 0, "negative skip");
-  WF_REQUIRE(!d_tx_syms || d_counters, "error counting needs d_counters");
+  int dflt = 32 / q.bits;  // release block D; survivor memory 2 D symbols
+  if (dflt > 16) dflt = 16;
+  q.depth = depth > 0 ? depth : dflt;
   for (int h = 0; h < n_h; ++h)
     for (int x = 0; x < M; ++x) {
       int d = (h_num[h] * (2 * x - (M - 1))) % (2 * p);
       if (d < 0) d += 2 * p;
       q.delta[h][x] = d;
     }
+  return WF_OK;
+}
+
+static void fill_rot(CpmRot& rot, int p) {
+  memset(&rot, 0, sizeof(rot));
+  for (int v = 0; v < 2 * p; ++v) {
+    rot.c[v] = (float)cos(M_PI * (double)v / (double)p);
+    rot.s[v] = (float)sin(M_PI * (double)v / (double)p);
+  }
+}
+
+// which fused kernel (0 = none, 1 = PCM/FM thread-per-frame, 2 = ARTM lane-per-phase-state) covers the shape.
+// taps: [n_h * M^Lp][sps] in wf_mf_bank's convolution form with center = sps - 1 (tap t multiplies rx[c_i + sps-1 - t]).
+static int fused_kind(int dtype, int64_t Tn, int64_t ld_rx, const double* tre, const double* tim, int sps, int64_t first_instant,
+                      int64_t n_steps, const CpmParams& q) {
+  if (dtype != WF_F32 || sps != 8 || first_instant != -1 || !tre || !tim || q.Lp != 2) return 0;
+  if ((ld_rx & 1) || n_steps < 1 || n_steps >= 0x0FFFFFF0 || Tn >= 0x7FFFFFF0) return 0;
+  const int NF = q.n_filt;
+  // hypothesis NF-1-f must be the complex conjugate of f, exactly, in float
+  for (int par = 0; par < q.n_h; ++par)
+    for (int f = 0; f < NF / 2; ++f)
+      for (int t = 0; t < 8; ++t) {
+        const int a = (par * NF + f) * 8 + t, b = (par * NF + NF - 1 - f) * 8 + t;
+        if ((float)tre[a] != (float)tre[b] || (float)tim[a] != -(float)tim[b]) return 0;
+      }
+  if (q.M == 2 && q.n_h == 1 && q.p == 10 && q.delta[0][0] == 13 && q.delta[0][1] == 7 && q.depth <= 32 &&
+      8 * n_steps <= Tn && 8 * ((n_steps + 1) & ~(int64_t)1) <= ld_rx)  // chunks are two steps: the last one may read one step on
+    return 1;
+  if (q.M == 4 && q.n_h == 2 && q.p == 16 && q.depth <= 32) return 2;
+  return 0;
+}
+
+}  // namespace wf
+
+extern "C" int wf_viterbi_cpm(const void* d_z, int dtype, int64_t B, int64_t n_steps, int64_t ld_z, int M, int Lp,
+                              int p, const int32_t* h_num, int n_h, int depth, int8_t* d_dec_syms,
+                              const int8_t* d_tx_syms, int64_t S, int64_t skip_head, int64_t skip_tail,
+                              const int32_t* d_point, int64_t* d_counters, void* stream) {
+  using namespace wf;
+  WF_REQUIRE(B >= 0 && n_steps >= 0 && ld_z >= n_steps, "bad shape");
+  WF_REQUIRE(dtype == WF_F32 || dtype == WF_F64, "dtype must be WF_F32 or WF_F64");
+  CpmParams q;
   int rc;
+  if ((rc = fill_cpm_params(q, M, Lp, p, h_num, n_h, depth))) return rc;
+  WF_REQUIRE(q.depth >= 1 && 2 * q.depth * q.bits <= 64, "survivor memory 2 x depth x bits/symbol exceeds 64 bits");
+  WF_REQUIRE(skip_head >= 0 && skip_tail >= 0, "negative skip");
+  WF_REQUIRE(!d_tx_syms || d_counters, "error counting needs d_counters");
   if ((rc = require_device())) return rc;
   if (B == 0 || n_steps == 0) return WF_OK;
   WF_REQUIRE(d_z, "d_z is NULL");
   q.z = d_z; q.dec_syms = d_dec_syms; q.tx_syms = d_tx_syms; q.point = d_point;
   q.counters = reinterpret_cast<unsigned long long*>(d_counters);
   q.B = B; q.n_steps = n_steps; q.ld_z = ld_z; q.S = S; q.skip_head = skip_head; q.skip_tail = skip_tail;
-  // IRIG PCM/FM shape (binary, memory 2, h = 7/10, 4-complex rows on 16-byte boundaries): thread-per-frame kernel
-  if (dtype == WF_F32 && M == 2 && Lp == 2 && n_h == 1 && p == 10 && q.delta[0][0] == 13 && q.delta[0][1] == 7 &&
-      (reinterpret_cast<uintptr_t>(d_z) & 15) == 0) {
-    CpmRot rot;
-    for (int v = 0; v < 2 * p; ++v) {
-      rot.c[v] = (float)cos(M_PI * (double)v / (double)p);
-      rot.s[v] = (float)sin(M_PI * (double)v / (double)p);
-    }
-    const unsigned g = (unsigned)((B + kM2Threads - 1) / kM2Threads);
-    if (q.depth <= 32) viterbi_cpm_m2l2_kernel<20, 13, 7, uint32_t><<<g, kM2Threads, 0, as_stream(stream)>>>(q, rot);
-    else viterbi_cpm_m2l2_kernel<20, 13, 7, unsigned long long><<<g, kM2Threads, 0, as_stream(stream)>>>(q, rot);
-    WF_LAUNCH_CHECK("viterbi_cpm_m2l2_kernel");
-    return WF_OK;
-  }
-  // memory-2 trellis with 32 phase states (ARTM multi-h): lane-per-phase-state register kernel
-  if (dtype == WF_F32 && M == 4 && Lp == 2 && p == 16 && n_h == 2 && q.depth * q.bits <= 64 && n_steps < 0x7FFFFF00 && S < 0x7FFFFF00 &&
-      (reinterpret_cast<uintptr_t>(d_z) & 15) == 0) {
-    CpmRot rot;
-    for (int v = 0; v < 2 * p; ++v) {
-      rot.c[v] = (float)cos(M_PI * (double)v / (double)p);
-      rot.s[v] = (float)sin(M_PI * (double)v / (double)p);
-    }
-    const unsigned g = (unsigned)((B + kLvWarps - 1) / kLvWarps);
-    viterbi_cpm_lanev_kernel<4, 2><<<g, kLvWarps * 32, 0, as_stream(stream)>>>(q, rot);
-    WF_LAUNCH_CHECK("viterbi_cpm_lanev_kernel");
-    return WF_OK;
-  }
   const unsigned grid = (unsigned)((B + kCpmWarps - 1) / kCpmWarps);
   if (dtype == WF_F32) viterbi_cpm_kernel<float><<<grid, kCpmWarps * 32, 0, as_stream(stream)>>>(q);
   else viterbi_cpm_kernel<double><<<grid, kCpmWarps * 32, 0, as_stream(stream)>>>(q);
   WF_LAUNCH_CHECK("viterbi_cpm_kernel");
+  return WF_OK;
+}
+
+extern "C" int wf_cpm_detect_supported(int dtype, int64_t T, int64_t ld_rx, const double* taps_re, const double* taps_im,
+                                       int sps, int64_t first_instant, int64_t n_steps, int M, int Lp, int p,
+                                       const int32_t* h_num, int n_h, int depth) {
+  using namespace wf;
+  CpmParams q;
+  if (fill_cpm_params(q, M, Lp, p, h_num, n_h, depth)) return 0;
+  return fused_kind(dtype, T, ld_rx, taps_re, taps_im, sps, first_instant, n_steps, q) != 0;
+}
+
+extern "C" int wf_cpm_detect(const void* d_rx, int dtype, int64_t B, int64_t T, int64_t ld_rx, const double* taps_re,
+                             const double* taps_im, int sps, int64_t first_instant, int64_t n_steps, int M, int Lp,
+                             int p, const int32_t* h_num, int n_h, int depth, int8_t* d_dec_syms,
+                             const int8_t* d_tx_syms, int64_t S, int64_t skip_head, int64_t skip_tail,
+                             const int32_t* d_point, int64_t* d_counters, int tune, void* stream) {
+  using namespace wf;
+  WF_REQUIRE(B >= 0 && n_steps >= 0 && T >= 0 && ld_rx >= T, "bad shape");
+  WF_REQUIRE(dtype == WF_F32 || dtype == WF_F64, "dtype must be WF_F32 or WF_F64");
+  CpmParams q;
+  int rc;
+  if ((rc = fill_cpm_params(q, M, Lp, p, h_num, n_h, depth))) return rc;
+  WF_REQUIRE(skip_head >= 0 && skip_tail >= 0, "negative skip");
+  WF_REQUIRE(!d_tx_syms || d_counters, "error counting needs d_counters");
+  const int kind = fused_kind(dtype, T, ld_rx, taps_re, taps_im, sps, first_instant, n_steps, q);
+  if (!kind)
+    return fail(WF_ERR_UNSUPPORTED, "wf_cpm_detect: shape not covered by a fused kernel (see wf_cpm_detect_supported); "
+                                    "run wf_mf_bank + wf_viterbi_cpm");
+  if ((rc = require_device())) return rc;
+  if (B == 0 || n_steps == 0) return WF_OK;
+  WF_REQUIRE(d_rx, "d_rx is NULL");
+  WF_REQUIRE((reinterpret_cast<uintptr_t>(d_rx) & 15) == 0, "d_rx must be 16-byte aligned");
+  q.rx = d_rx; q.dec_syms = d_dec_syms; q.tx_syms = d_tx_syms; q.point = d_point;
+  q.counters = reinterpret_cast<unsigned long long*>(d_counters);
+  q.B = B; q.n_steps = n_steps; q.S = S; q.skip_head = skip_head; q.skip_tail = skip_tail; q.Tn = T; q.ld_rx = ld_rx;
+  CpmRot rot;
+  fill_rot(rot, p);
+  cudaStream_t st = as_stream(stream);
+  const int norm_every = tune > 0 ? tune : 1;  // path-metric normalisation every `tune` steps (1, 2, 4 or 8)
+  if (kind == 1) {
+    CpmPairTaps tp;
+    for (int pr = 0; pr < 2; ++pr)
+      for (int u = 0; u < 8; ++u) {  // ct[f][u] = taps[f][7 - u]
+        const float cr = (float)taps_re[pr * 8 + 7 - u], ci = (float)taps_im[pr * 8 + 7 - u];
+        tp.t[pr][u][0][0] = tp.t[pr][u][0][1] = cr;
+        tp.t[pr][u][1][0] = tp.t[pr][u][1][1] = ci;
+      }
+    const unsigned g = (unsigned)((B + kBfThreads - 1) / kBfThreads);
+#define WF_BF_LAUNCH(RING_, NORM_)                                                                            \
+  do {                                                                                                        \
+    const size_t sm = (size_t)RING_ * kBfThreads * sizeof(unsigned long long);                                \
+    auto kfn = cpm_detect_m2l2_kernel<20, 13, 7, RING_, NORM_>;                                               \
+    cudaError_t e = cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm);          \
+    if (e != cudaSuccess) return cuda_fail(e, "cudaFuncSetAttribute(cpm_detect_m2l2_kernel)");                \
+    kfn<<<g, kBfThreads, sm, st>>>(q, rot, tp);                                                               \
+  } while (0)
+    if (q.depth <= 16) {
+      if (norm_every >= 4) WF_BF_LAUNCH(32, 4);
+      else if (norm_every == 2) WF_BF_LAUNCH(32, 2);
+      else WF_BF_LAUNCH(32, 1);
+    } else {
+      if (norm_every >= 4) WF_BF_LAUNCH(64, 4);
+      else if (norm_every == 2) WF_BF_LAUNCH(64, 2);
+      else WF_BF_LAUNCH(64, 1);
+    }
+#undef WF_BF_LAUNCH
+    WF_LAUNCH_CHECK("cpm_detect_m2l2_kernel");
+    return WF_OK;
+  }
+  CpmLaneTaps tp;
+  for (int par = 0; par < 2; ++par)
+    for (int f = 0; f < 8; ++f)
+      for (int u = 0; u < 8; ++u) {
+        tp.t[par][f][u][0] = (float)taps_re[(par * 16 + f) * 8 + 7 - u];
+        tp.t[par][f][u][1] = (float)taps_im[(par * 16 + f) * 8 + 7 - u];
+      }
+  const unsigned g = (unsigned)((B + kLfWarps - 1) / kLfWarps);
+  if (q.depth <= 16) {
+    if (norm_every >= 4) cpm_detect_lanev_kernel<32, 4><<<g, kLfWarps * 32, 0, st>>>(q, rot, tp);
+    else if (norm_every == 2) cpm_detect_lanev_kernel<32, 2><<<g, kLfWarps * 32, 0, st>>>(q, rot, tp);
+    else cpm_detect_lanev_kernel<32, 1><<<g, kLfWarps * 32, 0, st>>>(q, rot, tp);
+  } else {
+    if (norm_every >= 4) cpm_detect_lanev_kernel<64, 4><<<g, kLfWarps * 32, 0, st>>>(q, rot, tp);
+    else if (norm_every == 2) cpm_detect_lanev_kernel<64, 2><<<g, kLfWarps * 32, 0, st>>>(q, rot, tp);
+    else cpm_detect_lanev_kernel<64, 1><<<g, kLfWarps * 32, 0, st>>>(q, rot, tp);
+  }
+  WF_LAUNCH_CHECK("cpm_detect_lanev_kernel");
   return WF_OK;
 }

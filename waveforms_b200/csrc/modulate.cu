@@ -658,6 +658,284 @@ cpm_modulate_f32s8_kernel(const __grid_constant__ ModParams<float> p,
 }
 
 // ---------------------------------------------------------------------------
+// Warp-autonomous fused modulate -> AWGN -> PAM bank (wf_cpm_modulate_bank, tune >= 1).
+// Same arithmetic per sample and per (call, filter) as the block kernel above -- so z is still bit-identical
+// to wf_cpm_modulate + wf_mf_bank -- but ONE WARP owns a frame and there is no block barrier anywhere:
+//   * the frame is walked in chunks of CH = 32 R symbol intervals; per chunk the warp (a) scans the chunk's
+//     symbols into w_k / F (a 5-step 64-bit shuffle scan; exact fixed point, so chunking changes nothing),
+//     (b) produces the chunk's 8 CH samples into its private shared-memory tile with the 4-lanes-per-interval
+//     register-window loop of the fast modulator (R / 2 passes of 8 intervals per lane), (c) runs the bank on
+//     R consecutive calls per lane (all 32 lanes; R 8 + 2-sample segments, 16-byte pad: LDS.128 conflict free)
+//     and stores 16 R bytes per lane straight to HBM, (d) carries the newest LB samples to the tile front.
+//   * only __syncwarp orders the phases, so the warps of an SM drift apart and the schedulers always see a mix
+//     of MUFU / integer work (produce) and FFMA2 streams (bank); nobody idles at a barrier and no warp waits
+//     for another frame's scan.
+//   * w_k / F live in a padded ring (one pad word per 8 slots): the 8 interval groups of a warp read their
+//     windows from 8 different banks.
+// Shared memory per warp: 6.3 KB (R = 2) or 10.9 KB (R = 4).
+// ---------------------------------------------------------------------------
+constexpr int kFwWarps = 4;
+template <int R> struct FwGeom {
+  static constexpr int CH = 32 * R;                                   // intervals (= calls) per chunk
+  static constexpr int RS = 8 * R;                                    // samples per lane segment
+  __host__ __device__ static constexpr int pos(int m) { return m + 2 * (int)((unsigned)m / (unsigned)RS); }
+  static constexpr int SLOTS = kFLB + CH + 8;                         // w / F ring slots
+  static constexpr int RINGW = SLOTS + SLOTS / 8 + 2;                 // + one pad word per 8 slots
+  static constexpr int RINGW4 = (RINGW + 3) & ~3;
+  static constexpr int TILE = ((kFzLBMax + 8 * CH) + 2 * ((kFzLBMax + 8 * CH) / RS) + 4 + 1) & ~1;  // float2 slots
+  static constexpr size_t WARP_BYTES = (size_t)TILE * 8 + (size_t)RINGW4 * 8;
+};
+__device__ __forceinline__ int fw_pad(int s) { return s + (s >> 3); }
+
+template <int R>
+static __device__ __forceinline__ void fw_bank_phase(const FuseParams& fz, const float2* tile, int t, int cbase, float2* zrow) {
+  using G = FwGeom<R>;
+  const int c0 = cbase + R * t;
+  if (c0 + R - 1 < 0 || c0 >= fz.n_calls) return;
+  constexpr int NV = (R - 1) * 8 + kFzNT;
+  const float2* tap2 = reinterpret_cast<const float2*>(fz.tap2);
+  float2 y[R][kFzNF];
+#pragma unroll
+  for (int e = 0; e < R; ++e)
+#pragma unroll
+    for (int f = 0; f < kFzNF; ++f) y[e][f] = make_float2(0.f, 0.f);
+  const float2* seg = tile + t * (G::RS + 2);
+#pragma unroll
+  for (int v = 0; v < NV; v += 2) {
+    float4 xx;
+    if (v + 1 < NV) {
+      xx = *reinterpret_cast<const float4*>(seg + G::pos(v));
+    } else {
+      const float2 x1 = seg[G::pos(v)];
+      xx = make_float4(x1.x, x1.y, 0.f, 0.f);
+    }
+#pragma unroll
+    for (int s = 0; s < 2; ++s) {
+      if (v + s < NV) {
+        const float2 x = s ? make_float2(xx.z, xx.w) : make_float2(xx.x, xx.y);
+#pragma unroll
+        for (int e = 0; e < R; ++e) {
+          const int u = v + s - e * 8;
+          if (u >= 0 && u < kFzNT) {
+#pragma unroll
+            for (int f = 0; f < kFzNF; ++f) y[e][f] = ffma2(x, tap2[f * kFzNT + kFzNT - 1 - u], y[e][f]);
+          }
+        }
+      }
+    }
+  }
+#pragma unroll
+  for (int e = 0; e < R; ++e) {
+    const int c = c0 + e;
+    if ((unsigned)c < (unsigned)fz.n_calls)
+      *reinterpret_cast<float4*>(zrow + 2 * (int64_t)c) = make_float4(y[e][0].x, y[e][0].y, y[e][1].x, y[e][1].y);
+  }
+}
+
+template <bool NOISE, int R, int MINB>
+__global__ void __launch_bounds__(kFwWarps * 32, MINB)
+cpm_modulate_bank_warp_kernel(const __grid_constant__ ModParams<float> p, const __grid_constant__ FuseParams fz, int n_chunks) {
+  using G = FwGeom<R>;
+  constexpr int JT = 8, RUN = 8;
+  constexpr int PASSES = G::CH / (8 * RUN);   // 8 interval groups per warp x RUN intervals per pass
+  constexpr int PER = G::CH / 32;             // symbols per lane per chunk scan
+  static_assert(kFLB - JT == 8 && PASSES >= 1 && PER >= 2 && PER <= 4, "window bases must stay multiples of 8");
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+  const int64_t frame = (int64_t)blockIdx.x * kFwWarps + wid;
+  if (frame >= p.B) return;  // whole warp; only __syncwarp below
+  unsigned char* wbase = smem_raw + (size_t)wid * G::WARP_BYTES;
+  float2* tile = reinterpret_cast<float2*>(wbase);
+  float* w_s = reinterpret_cast<float*>(wbase + (size_t)G::TILE * 8);     // padded slot(k) = fw_pad(k - K0 + kFLB) holds w_k
+  uint32_t* f_s = reinterpret_cast<uint32_t*>(w_s + G::RINGW4);            // same slot holds F[k + 1]
+
+  const int off = p.off;
+  const int S = (int)p.S, Ti = (int)p.Tn;
+  const int8_t* sy = p.syms + frame * (int64_t)S;
+  float2* zrow = fz.z + frame * fz.ld_z * kFzNF;
+  const bool one_h = (p.n_h == 1);
+
+  // samples before the frame (tile look-back of chunk 0) are zero
+  for (int m = 2 * lane; m < kFzLBMax + 16; m += 64) *reinterpret_cast<float4*>(tile + G::pos(m)) = make_float4(0.f, 0.f, 0.f, 0.f);
+
+  // per-frame constant folded into the prefix sum (see the block kernel): computed by lane 0, broadcast
+  uint64_t carry = 0;
+  if (lane == 0) {
+    float c0 = 0.f;
+    for (int k = 0; k < S && (k + 1) * 8 < off; ++k) {
+      int idx = off - (k + 1) * 8;
+      if (idx > p.K) idx = p.K;
+      c0 = fmaf((float)sy[k] * p.hw[k % p.n_h], p.q[idx], c0);
+    }
+    float t = fmaf(c0, -0.125f, p.phase0_turns);
+    t -= rintf(t);
+    carry = (uint64_t)(int64_t)llrintf(t * 4611686018427387904.0f) << 2;
+  }
+  carry = __shfl_sync(0xFFFFFFFFu, carry, 0);
+  if (lane < kFLB) { w_s[fw_pad(lane)] = 0.f; f_s[fw_pad(lane)] = (uint32_t)(carry >> 32); }  // symbols k < 0, F[k <= 0]
+
+  NoiseCoef ncoef = noise_coef(0.f);
+  u32x4 ctr;
+  ctr.x = 0; ctr.y = 0; ctr.z = 0; ctr.w = 0;
+  if (NOISE) {
+    ncoef = noise_coef(p.sigma[frame]);
+    const uint64_t gframe = p.frame_ids ? p.frame_ids[frame] : p.first_frame + (uint64_t)frame;
+    ctr.y = (uint32_t)gframe; ctr.z = (uint32_t)(gframe >> 32);
+    ctr.w = p.point ? (uint32_t)p.point[frame] : 0u;
+  }
+  const int sub = lane & 3, grp = lane >> 2;
+  const int rho = 2 * sub;
+  const int qa0 = rho + 1, qb0 = rho + 2;
+  const int A_last = (Ti - 1 + off) >> 3;
+  float qa[JT], qb[JT];
+#pragma unroll
+  for (int j = 0; j < JT; ++j) {
+    qa[j] = p.q[qa0 + 8 * j] * 0.78539816339744831f;  // Q * 2 pi / sps  (radians per unit w)
+    qb[j] = p.q[qb0 + 8 * j] * 0.78539816339744831f;
+  }
+
+  // symbols of the chunk this lane scans: PER consecutive bytes, fetched one chunk ahead
+  auto fetch = [&](int K0) {
+    uint32_t v = 0u;
+    const int k0 = K0 + PER * lane;
+#pragma unroll
+    for (int i = 0; i < PER; ++i)
+      if (k0 + i < S) v |= (uint32_t)(uint8_t)sy[k0 + i] << (8 * i);
+    return v;
+  };
+  uint32_t sv_next = fetch(0);
+
+  for (int jc = 0; jc < n_chunks; ++jc) {
+    const int K0 = jc * G::CH;
+    // ---- (a) scan: w_k and F[k + 1] for k in [K0, K0 + CH) ---------------------------------------
+    const uint32_t sv = sv_next;
+    sv_next = fetch(K0 + G::CH);
+    if (jc > 0) {  // the newest kFLB slots of the previous chunk become the look-back (its readers are done: (e) ended with a __syncwarp)
+      float wv = 0.f; uint32_t fv = 0;
+      if (lane < kFLB) { wv = w_s[fw_pad(G::CH + lane)]; fv = f_s[fw_pad(G::CH + lane)]; }
+      __syncwarp();
+      if (lane < kFLB) { w_s[fw_pad(lane)] = wv; f_s[fw_pad(lane)] = fv; }
+    }
+    {
+      const int k0 = K0 + PER * lane;
+      int hi = one_h ? 0 : k0 % p.n_h;
+      uint64_t run = 0;
+      int hh = hi;
+#pragma unroll
+      for (int i = 0; i < PER; ++i) {
+        const int a = (int8_t)((sv >> (8 * i)) & 0xFF);
+        run += (uint64_t)((int64_t)a) * p.hfix[hh];
+        if (!one_h && ++hh == p.n_h) hh = 0;
+      }
+      uint64_t incl = run;
+#pragma unroll
+      for (int s = 1; s < 32; s <<= 1) {
+        const uint64_t t = __shfl_up_sync(0xFFFFFFFFu, incl, s);
+        if (lane >= s) incl += t;
+      }
+      uint64_t base = carry + (incl - run);
+      carry += __shfl_sync(0xFFFFFFFFu, incl, 31);
+#pragma unroll
+      for (int i = 0; i < PER; ++i) {
+        const int a = (int8_t)((sv >> (8 * i)) & 0xFF);
+        base += (uint64_t)((int64_t)a) * p.hfix[hi];
+        const int slot = fw_pad(kFLB + PER * lane + i);
+        w_s[slot] = (float)a * p.hw[hi];
+        f_s[slot] = (uint32_t)(base >> 32);  // F[k + 1]
+        if (!one_h && ++hi == p.n_h) hi = 0;
+      }
+    }
+    __syncwarp();
+    // ---- (b) produce the chunk's samples into the tile -----------------------------------------
+#pragma unroll 1
+    for (int ps = 0; ps < PASSES; ++ps) {
+      const int r0 = ps * 8 * RUN + grp * RUN;       // first interval of this lane's run, relative to K0
+      const bool live = K0 + r0 <= A_last;
+      const int mb = fz.LB + 8 * r0 + 2 * sub;       // tile sample index of this lane's first pair
+      if (live) {
+        const int wb = fw_pad(r0 - JT + kFLB);       // a multiple of 9: symbols A0-JT .. sit at wb + j + (j >> 3)
+        const int fb = r0 - JT - 1 + kFLB;           // == 7 (mod 8): F[A0-JT + i] at fw_pad(fb + i)
+        float w[JT + RUN - 1];
+#pragma unroll
+        for (int j = 0; j < JT + RUN - 1; ++j) w[j] = w_s[wb + j + (j >> 3)];
+        uint32_t fpv[RUN];
+#pragma unroll
+        for (int i = 0; i < RUN; ++i) fpv[i] = f_s[fw_pad(fb + i)];
+        const int n0 = 8 * (K0 + r0) + rho - off;    // first sample of the first pair (< 0 before the frame starts)
+        const int P0 = n0 >> 1;
+        const uint32_t c0 = (uint32_t)(((P0 >> 3) << 2) | (P0 & 3));
+        u32x4 r;
+        r.x = r.y = r.z = r.w = 0;
+        uint32_t m_min = 0xFFFFu;
+#pragma unroll
+        for (int i = 0; i < RUN; ++i) {
+          float2 acc = make_float2(0.f, 0.f);
+#pragma unroll
+          for (int j = 0; j < JT; ++j) {
+            const float wj = w[i + JT - 1 - j];  // symbol A-1-j
+            acc = ffma2(make_float2(wj, wj), make_float2(qa[j], qb[j]), acc);
+          }
+          const float old = (float)(int32_t)fpv[i] * 1.4629180792671596e-09f;  // F[A-JT] in radians, [-pi, pi)
+          float c0f, s0f, c1f, s1f;
+          __sincosf(acc.x + old, &s0f, &c0f);
+          __sincosf(acc.y + old, &s1f, &c1f);
+          if (NOISE) {
+            if ((i & 1) == 0) {
+              ctr.x = c0 + 2u * (uint32_t)i;
+              r = philox4x32_10_rk(ctr, p.rk);
+            }
+            const uint32_t wa = (i & 1) ? r.z : r.x, wbw = (i & 1) ? r.w : r.y;
+            m_min = min(m_min, min(wa & 0xFFFFu, wbw & 0xFFFFu));
+            const float2 g0 = box_muller16(wa, noise_lgt(wa), ncoef), g1 = box_muller16(wbw, noise_lgt(wbw), ncoef);
+            c0f += g0.x; s0f += g0.y; c1f += g1.x; s1f += g1.y;
+          }
+          const bool in = (unsigned)(n0 + 8 * i) < (unsigned)Ti;
+          const int m = mb + 8 * i;
+          *reinterpret_cast<float4*>(tile + G::pos(m)) = in ? make_float4(c0f, s0f, c1f, s1f) : make_float4(0.f, 0.f, 0.f, 0.f);
+        }
+        if (NOISE && m_min == 0u) {  // some radius uniform of this run needs its tail refined: redo those pairs
+#pragma unroll 1
+          for (int i = 0; i < RUN; ++i) {
+            ctr.x = c0 + 4u * (uint32_t)(i >> 1);
+            const u32x4 rr = philox4x32_10_rk(ctr, p.rk);
+            const uint32_t wa = (i & 1) ? rr.z : rr.x, wbw = (i & 1) ? rr.w : rr.y;
+            if (((wa & 0xFFFFu) == 0u || (wbw & 0xFFFFu) == 0u) && (unsigned)(n0 + 8 * i) < (unsigned)Ti) {
+              float wl[JT];
+#pragma unroll
+              for (int j = 0; j < JT; ++j) wl[j] = w_s[fw_pad(r0 - JT + kFLB + i + j)];
+              const uint32_t fv = f_s[fw_pad(fb + i)];
+              const float4 v4 = mod_f32s8_slow_pair<JT>(p, wl, wl, fv, fv, qa0, qb0, ctr, i & 1, ncoef);
+              *reinterpret_cast<float4*>(tile + G::pos(mb + 8 * i)) = v4;
+            }
+          }
+        }
+      } else {  // run past the end of the frame: its samples are zeros for the bank
+#pragma unroll
+        for (int i = 0; i < RUN; ++i) *reinterpret_cast<float4*>(tile + G::pos(mb + 8 * i)) = make_float4(0.f, 0.f, 0.f, 0.f);
+      }
+    }
+    __syncwarp();  // the chunk's samples (and the carried look-back) are in the tile
+    // ---- (c) bank: R consecutive calls per lane, straight to HBM ---------------------------------
+    fw_bank_phase<R>(fz, tile, lane, K0 - fz.CB, zrow);
+    // ---- (d) carry the newest LB samples to the front of the tile -------------------------------
+    float4 keep[(kFzLBMax / 2 + 31) / 32];
+#pragma unroll
+    for (int q = 0; q < (kFzLBMax / 2 + 31) / 32; ++q) {
+      const int u = lane + 32 * q;
+      keep[q] = make_float4(0.f, 0.f, 0.f, 0.f);
+      if (2 * u < fz.LB) keep[q] = *reinterpret_cast<const float4*>(tile + G::pos(8 * G::CH + 2 * u));
+    }
+    __syncwarp();  // bank reads done: the front of the tile may take the next chunk's look-back
+#pragma unroll
+    for (int q = 0; q < (kFzLBMax / 2 + 31) / 32; ++q) {
+      const int u = lane + 32 * q;
+      if (2 * u < fz.LB) *reinterpret_cast<float4*>(tile + G::pos(2 * u)) = keep[q];
+    }
+    __syncwarp();
+  }
+}
+
+// ---------------------------------------------------------------------------
 // Stand-alone AWGN: in-place add / fill.  One thread per Philox call (= the two sample
 // pairs p, p + 4 that share it, see common.cuh), grid-stride.
 // ---------------------------------------------------------------------------
@@ -871,7 +1149,7 @@ static int launch_modulate_bank(const int8_t* d_syms, int64_t B, int64_t S, cons
                                 const float* d_sigma, const int32_t* d_point, uint64_t seed, uint64_t first_frame,
                                 const uint64_t* d_frame_ids,
                                 const double* taps_re, int n_filt, int n_taps, int center, int64_t first_instant,
-                                int64_t n_calls, void* d_z, int64_t ld_z, cudaStream_t stream) {
+                                int64_t n_calls, void* d_z, int64_t ld_z, int tune, cudaStream_t stream) {
   int CB = 0, LB = 0;
   if (!fuse_geometry(K, sps, n_filt, n_taps, center, first_instant, S, n_calls, CB, LB)) {
     return fail(WF_ERR_UNSUPPORTED, "wf_cpm_modulate_bank: shape not covered by the fused kernel (see wf_cpm_modulate_bank_supported)");
@@ -884,6 +1162,27 @@ static int launch_modulate_bank(const int8_t* d_syms, int64_t B, int64_t S, cons
   memset(&fz, 0, sizeof(fz));
   fz.z = reinterpret_cast<float2*>(d_z); fz.ld_z = ld_z; fz.n_calls = (int)n_calls; fz.CB = CB; fz.LB = LB;
   for (int i = 0; i < kFzNF * kFzNT; ++i) fz.tap2[2 * i] = fz.tap2[2 * i + 1] = (float)taps_re[i];
+  if (tune >= 1) {  // warp-autonomous kernel: 1 = R 2 (64-interval chunks, 8 blocks of 4 warps per SM), 2 = R 4 (128, 5 blocks)
+    const int R = tune == 2 ? 4 : 2, CH = 32 * R;
+    const int64_t A_last = ((S + 1) * 8 - 1 + p.off) >> 3;
+    int64_t nch = A_last / CH + 1;
+    const int64_t need = (n_calls + CB + CH - 1) / CH;
+    if (need > nch) nch = need;
+    const dim3 gridw((unsigned)((B + kFwWarps - 1) / kFwWarps)), blockw(kFwWarps * 32);
+#define WF_FW_LAUNCH(NOISE_, R_, MINB_)                                                                           \
+  do {                                                                                                            \
+    auto kfn = cpm_modulate_bank_warp_kernel<NOISE_, R_, MINB_>;                                                   \
+    const size_t sm = FwGeom<R_>::WARP_BYTES * kFwWarps;                                                          \
+    cudaError_t e = cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm);              \
+    if (e != cudaSuccess) return cuda_fail(e, "cudaFuncSetAttribute(cpm_modulate_bank_warp_kernel)");             \
+    kfn<<<gridw, blockw, sm, stream>>>(p, fz, (int)nch);                                                           \
+  } while (0)
+    if (R == 2) { if (d_sigma) WF_FW_LAUNCH(true, 2, 8); else WF_FW_LAUNCH(false, 2, 8); }
+    else { if (d_sigma) WF_FW_LAUNCH(true, 4, 5); else WF_FW_LAUNCH(false, 4, 5); }
+#undef WF_FW_LAUNCH
+    WF_LAUNCH_CHECK("cpm_modulate_bank_warp_kernel");
+    return WF_OK;
+  }
   const dim3 grid((unsigned)B), block(kModThreads);
   // 2048-interval scan segments keep the scan arrays at 16.6 KB (8 B per symbol interval): with the 35.7 KB sample
   // tile that is 52 KB per block, four blocks per SM at 64 registers -- the occupancy the produce phase wants.
@@ -919,7 +1218,7 @@ int wf_cpm_modulate_bank(const int8_t* d_syms, int64_t B, int64_t S, const doubl
                          const float* d_sigma, const int32_t* d_point, uint64_t seed, uint64_t first_frame,
                          const uint64_t* d_frame_ids,
                          const double* taps_re, int n_filt, int n_taps, int center, int64_t first_instant,
-                         int64_t n_calls, void* d_z, int64_t ld_z, void* stream) {
+                         int64_t n_calls, void* d_z, int64_t ld_z, int tune, void* stream) {
   using namespace wf;
   WF_REQUIRE(B >= 0 && S >= 0 && n_calls >= 0, "negative shape");
   WF_REQUIRE(K >= 1 && pulse, "empty pulse filter");
@@ -934,7 +1233,7 @@ int wf_cpm_modulate_bank(const int8_t* d_syms, int64_t B, int64_t S, const doubl
   WF_REQUIRE((reinterpret_cast<uintptr_t>(d_z) & 15) == 0, "d_z must be 16-byte aligned");
   return launch_modulate_bank(d_syms, B, S, mod_index, n_h, pulse, K, sps, initial_phase, derotate, d_sigma, d_point, seed,
                               first_frame, d_frame_ids, taps_re, n_filt, n_taps, center, first_instant, n_calls, d_z, ld_z,
-                              as_stream(stream));
+                              tune, as_stream(stream));
 }
 
 int wf_cpm_modulate(const int8_t* d_syms, int64_t B, int64_t S, const double* mod_index, int n_h,

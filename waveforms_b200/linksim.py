@@ -106,6 +106,8 @@ class LinkSimulator:
             _ffi.lib().wf_cpm_modulate_bank_supported(int(self.pulse.size), cfg.sps, int(self._taps.shape[0]),
                                                       int(self._taps.shape[1]), (int(self._taps.shape[1]) - 1) // 2,
                                                       int(self.first_instant), int(self.n_sym), int(self.n_calls)))
+        # which fused kernel: 0 = one block per frame, 1 / 2 = one warp per frame with 64- / 128-interval chunks
+        self.fused_tune = int(cfg.extra.get("fused_tune", 1))
         self.stage_names = (("prbs_encode", "modulate_awgn_bank", "viterbi_bert") if self.fused
                             else ("prbs_encode", "modulate_awgn", "mf_bank", "viterbi_bert"))
         self.max_batch = 0
@@ -132,7 +134,15 @@ class LinkSimulator:
         self._comb_re = self._comb_im = None
         self._n_out = self._taps.shape[0]
         self.fused = False
-        self.stage_names = ("prbs_encode", "modulate_awgn", "mf_bank", "viterbi_bert")
+        # wf_cpm_detect: the hypothesis bank runs inside the detector kernel (no bank launch, no z array);
+        # taken whenever the library covers the shape (the two IRIG waveforms at sps 8, complex64);
+        # extra["unfused_detector"] = True keeps wf_mf_bank + wf_viterbi_cpm (the generic, parity path)
+        T = self.n_samples
+        self.detect_fused = (not bool(cfg.extra.get("unfused_detector", False))) and self.det.supports_fused(
+            cfg.dtype, T, (T + 1) & ~1, self.n_calls)
+        self.tune = int(cfg.extra.get("tune", 0))
+        self.stage_names = (("prbs_encode", "modulate_awgn", "detect_fused") if self.detect_fused
+                            else ("prbs_encode", "modulate_awgn", "mf_bank", "viterbi_bert"))
         self.max_batch = 0
         self._alloc(int(self._max_batch_arg))
         self.launches = 0
@@ -147,7 +157,8 @@ class LinkSimulator:
         self.packed = torch.zeros((max_batch, self.ld_words), dtype=torch.int32, device=dev)
         self.syms = torch.empty((max_batch, self.n_sym), dtype=torch.int8, device=dev)
         self.rx = None if self.fused else torch.empty((max_batch, self.ld_rx), dtype=cfg.dtype, device=dev)
-        self.z = torch.empty((max_batch, self.ld_z, self._n_out), dtype=cfg.dtype, device=dev)
+        no_z = (not self.soqpsk) and self.detect_fused
+        self.z = None if no_z else torch.empty((max_batch, self.ld_z, self._n_out), dtype=cfg.dtype, device=dev)
 
     def workspace_bytes(self) -> int:
         return sum(t.numel() * t.element_size() for t in (self.packed, self.syms, self.rx, self.z) if t is not None)
@@ -193,7 +204,7 @@ class LinkSimulator:
                                                     -math.pi / 4, _dev.ptr(sigma), _dev.ptr(point), seed, int(first_frame),
                                                     fid, _dev.f64_ptr(self._tap_re), self._taps.shape[0], self._taps.shape[1],
                                                     (self._taps.shape[1] - 1) // 2, self.first_instant, self.n_calls,
-                                                    _dev.ptr(self.z), self.ld_z, st))
+                                                    _dev.ptr(self.z), self.ld_z, self.fused_tune, st))
                 mark()
                 _ffi.check(lib.wf_viterbi_soqpsk_combined(_dev.ptr(self.z), dt, B, self.n_calls, self.ld_z, 2,
                                                           _dev.f64_ptr(self._comb_re), _dev.f64_ptr(self._comb_im),
@@ -207,6 +218,15 @@ class LinkSimulator:
                                            dt, _dev.ptr(self.rx), self.ld_rx, _dev.ptr(sigma), _dev.ptr(point), seed,
                                            int(first_frame), fid, st))
             mark()
+            if not self.soqpsk and self.detect_fused:
+                d = self.det
+                _ffi.check(lib.wf_cpm_detect(_dev.ptr(self.rx), dt, B, self.n_samples, self.ld_rx, _dev.f64_ptr(self._tap_re),
+                                             _dev.f64_ptr(self._tap_im), cfg.sps, self.first_instant, self.n_calls, d.M, d.Lp,
+                                             d.p, d.h_num.ctypes.data, d.n_h, d.depth, None, _dev.ptr(self.syms), self.n_sym,
+                                             self.skip, self.skip, _dev.ptr(point), _dev.ptr(counters), self.tune, st))
+                mark()
+                self.launches += 3
+                return
             _ffi.check(lib.wf_mf_bank(_dev.ptr(self.rx), dt, B, self.n_samples, self.ld_rx, _dev.f64_ptr(self._tap_re),
                                       None if self._tap_im is None else _dev.f64_ptr(self._tap_im),
                                       self._taps.shape[0], self._taps.shape[1],

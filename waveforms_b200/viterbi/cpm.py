@@ -62,6 +62,47 @@ class CPMTrellisDetector:
         return filter_bank(rx, self.taps, sps=self.sps, first_instant=self.first_instant, n_calls=n_steps,
                            center=self.sps - 1, n_samples=n_samples)
 
+    def supports_fused(self, rx_dtype, n_samples: int, ld_rx: int, n_steps: int) -> bool:
+        """True when wf_cpm_detect has a fused bank+detector kernel for this trellis and signal shape."""
+        if rx_dtype not in _dev.COMPLEX:
+            return False
+        tr, ti = _dev.host_f64(self.taps.real.ravel()), _dev.host_f64(self.taps.imag.ravel())
+        return bool(_ffi.lib().wf_cpm_detect_supported(_dev.COMPLEX[rx_dtype], int(n_samples), int(ld_rx), _dev.f64_ptr(tr),
+                                                       _dev.f64_ptr(ti), self.sps, self.first_instant, int(n_steps), self.M,
+                                                       self.Lp, self.p, self.h_num.ctypes.data, self.n_h, self.depth))
+
+    def detect_rx(self, rx: torch.Tensor, n_steps: int, *, n_samples: int | None = None,
+                  tx_symbols: torch.Tensor | None = None, skip_head: int = 4, skip_tail: int = 4,
+                  point: torch.Tensor | None = None, counters: torch.Tensor | None = None, return_decisions: bool = True,
+                  tune: int = 0):
+        """Detection straight from the received samples rx complex64[B, ld >= T] (wf_cpm_detect): the
+        hypothesis bank runs inside the detector kernel.  Same outputs as ``detect(bank(rx, n_steps))``;
+        raises _ffi.WfError for shapes without a fused kernel (see ``supports_fused``)."""
+        rx = _dev.require_cuda(rx, "rx")
+        if rx.dtype not in _dev.COMPLEX or rx.dim() != 2:
+            raise TypeError("rx must be complex[B, T]")
+        B, ld = rx.shape
+        T = ld if n_samples is None else int(n_samples)
+        dec = torch.empty((B, n_steps), dtype=torch.int8, device=rx.device) if return_decisions else None
+        S = 0
+        if tx_symbols is not None:
+            tx_symbols = _dev.require_cuda(tx_symbols, "tx_symbols", torch.int8)
+            S = tx_symbols.shape[1]
+            if counters is None:
+                raise ValueError("tx_symbols given without counters")
+        if counters is not None:
+            counters = _dev.require_cuda(counters, "counters", torch.int64)
+        if point is not None:
+            point = _dev.require_cuda(point, "point", torch.int32)
+        tr, ti = _dev.host_f64(self.taps.real.ravel()), _dev.host_f64(self.taps.imag.ravel())
+        with torch.cuda.device(rx.device):
+            _ffi.check(_ffi.lib().wf_cpm_detect(_dev.ptr(rx), _dev.COMPLEX[rx.dtype], B, T, ld, _dev.f64_ptr(tr), _dev.f64_ptr(ti),
+                                                self.sps, self.first_instant, int(n_steps), self.M, self.Lp, self.p,
+                                                self.h_num.ctypes.data, self.n_h, self.depth, _dev.ptr(dec),
+                                                _dev.ptr(tx_symbols), S, int(skip_head), int(skip_tail), _dev.ptr(point),
+                                                _dev.ptr(counters), int(tune), _dev.stream_ptr(rx.device)))
+        return dec
+
     def detect(self, z: torch.Tensor, *, tx_symbols: torch.Tensor | None = None, skip_head: int = 4, skip_tail: int = 4,
                point: torch.Tensor | None = None, counters: torch.Tensor | None = None, return_decisions: bool = True):
         """z complex[B, n_steps, n_h * M^Lp] -> detected symbols int8[B, n_steps] (alphabet values).
