@@ -78,13 +78,13 @@ class CpmTrellis:
 
     def default_depth(self):
         bits = max(1, (self.M - 1).bit_length())
-        return max(1, 32 // bits)
+        return max(1, min(16, 32 // bits))
 
     def detect(self, z, depth=None, return_margin=False):
         """Viterbi detection maximising sum Re{e^{-j pi v/p} z}.  z complex[n_steps, n_h*n_filt].
         Returns symbol INDICES (0..M-1) uint8[n_steps].  All states start equal (unknown start).
 
-        Decision rule -- BLOCK RELEASE with survivor memory 2 D (D = ``depth``, default 32 / log2 M):
+        Decision rule -- BLOCK RELEASE with survivor memory 2 D (D = ``depth``, default min(16, 32 / log2 M)):
         the add-compare-select of every step stores, per state, which predecessor won; whenever
         (t + 1) is a multiple of D and t + 1 >= 2 D the survivor of the best state at step t (largest
         metric, lowest index on ties) is traced back 2 D steps and the symbols of steps

@@ -249,3 +249,23 @@ def test_soqpsk_a_b_chain(lab):
         assert np.array_equal(r["dec_syms"], g[f"{lab}_{det}_syms"])
         assert [r["bit_errors"], r["sym_errors"], r["compared"]] == list(g[f"{lab}_{det}_counts"])
         np.testing.assert_allclose(r["margin"], g[f"{lab}_{det}_margin"], rtol=0, atol=1e-9)
+
+
+# ---- external anchor for the detectors the reference does not have: minimum Euclidean distance
+def test_minimum_distance_reproduces_published_values():
+    """oracle/cpm_dmin.py against values published for these schemes: binary CPFSK h = 0.715 -> 2.43
+    (Anderson, Aulin & Sundberg 1986, the maximum for binary 1REC); ARTM CPM (M = 4, 3RC, h = 4/16, 5/16) -> 1.29
+    (Perrins & Rice, IEEE Trans. AES 2007, "Reduced-complexity detectors for multi-h CPM in aeronautical
+    telemetry"); IRIG PCM/FM (h = 0.7, Bessel-filtered NRZ) sits a little above CPFSK's 2.42."""
+    from fractions import Fraction
+
+    from oracle.cpm_dmin import dmin2, ebn0_db_for_ber
+
+    rec = np.full(8, 0.5)
+    assert abs(dmin2(rec, [Fraction(143, 200)], 2, 8, span=4)[0] - 2.43) < 0.01
+    d_pcm = dmin2(o.pulse_pcmfm(8, 4), [Fraction(7, 10)], 2, 8, span=5)[0]
+    assert 2.42 < d_pcm < 2.7
+    d_artm, gam, _ = dmin2(o.pulse_multih(8), [Fraction(4, 16), Fraction(5, 16)], 4, 8, span=5)
+    assert abs(d_artm - 1.29) < 0.01 and gam == (2, -4, 6, -4, 2)
+    # the asymptote these distances give at BER 1e-5: 8.5 dB for PCM/FM, 11.5 dB for ARTM CPM
+    assert abs(ebn0_db_for_ber(d_pcm, 1e-5) - 8.5) < 0.1 and abs(ebn0_db_for_ber(d_artm, 1e-5) - 11.5) < 0.1

@@ -3,7 +3,7 @@
 TAG=${1:-r2b}
 OUT=gpurun_out/$TAG
 mkdir -p $OUT
-timeout 1200 python -m pytest tests -m gpu -q -p no:cacheprovider -x -k "cpm or generic or fused or confidence" -s > $OUT/pytest_sel.log 2>&1
+timeout 1200 python -m pytest tests -m gpu -q -p no:cacheprovider -k "cpm or generic or fused or confidence" -s > $OUT/pytest_sel.log 2>&1
 echo "pytest exit $?" | tee -a $OUT/pytest_sel.log
 grep -v "float32 flips" $OUT/pytest_sel.log | tail -60
 for ex in '{"fused": true, "fused_tune": 0}' '{"fused": true, "fused_tune": 1}' '{"fused": true, "fused_tune": 2}' '{}'; do

@@ -46,7 +46,7 @@ def measure(sim, B, reps, cfg):
     out["waveform"] = cfg.waveform
     out["extra"] = {k: v for k, v in cfg.extra.items() if v}
     out["frames"] = B
-    out["total_ms"] = round(sum(v["ms"] for v in out.values() if isinstance(v, dict)), 4)
+    out["total_ms"] = round(sum(out[name]["ms"] for name in sim.stage_names), 4)
     out["bits_per_s"] = round(bits / out["total_ms"] * 1e3, 1)
     return out
 

@@ -19,7 +19,7 @@
 namespace wf {
 
 constexpr int kMfThreads = 128;
-constexpr int kMfMaxTapEntries = 448;  // n_filt * n_taps
+constexpr int kMfMaxTapEntries = 576;  // n_filt * n_taps (x 2 for the duplicated real taps of the tiled kernel)
 constexpr int kMfMaxComb = 96;         // n_out * n_filt
 
 // row stride (complex elements) of the transposed tile; 2*qs*R == 4 (mod 32) words keeps the
@@ -458,7 +458,8 @@ static int launch_mf(const void* d_rx, int64_t B, int64_t Tn, int64_t ld_rx, con
     return WF_OK;                                                                                     \
   } while (0)
     if (tiled_ok) {
-      if (sps == 8 && n_filt == 2 && n_taps == 73 && real_taps) WF_MFT_CASE(8, 2, 73, false, 4);       // PAM bank, TG
+      if (sps == 8 && n_filt == 2 && n_taps == 73 && real_taps) WF_MFT_CASE(8, 2, 73, false, 4);       // PAM bank, TG / A
+      else if (sps == 8 && n_filt == 2 && n_taps == 137 && real_taps) WF_MFT_CASE(8, 2, 137, false, 4);  // PAM bank, SOQPSK-B
       else if (sps == 8 && n_filt == 3 && n_taps == 9 && !real_taps) WF_MFT_CASE(8, 3, 9, true, 4);   // PT bank
       else if (sps == 10 && n_filt == 2 && n_taps == 91 && real_taps) WF_MFT_CASE(10, 2, 91, false, 4);
       else if (sps == 10 && n_filt == 3 && n_taps == 11 && !real_taps) WF_MFT_CASE(10, 3, 11, true, 4);

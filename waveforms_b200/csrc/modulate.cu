@@ -260,7 +260,7 @@ cpm_modulate_kernel(const __grid_constant__ ModParams<T> p) {
 //    is fixed(F) * 2pi/2^32 in [-pi, pi) plus the J-tap partial: no range reduction.
 // ---------------------------------------------------------------------------
 constexpr int kFSeg = 5120;                   // symbol intervals per segment (multiple of 1024)
-constexpr int kFLB = 16;                      // look-back slots in front of a segment (>= J + 2)
+constexpr int kFLB = 24;                      // look-back slots in front of a segment (>= J + 2; J = 16 for SOQPSK-B)
 constexpr int kFSlots = kFLB + kFSeg + 8;     // + spill of the lanes that start one interval late
 constexpr size_t kFSmemBytes = (size_t)kFSlots * 8;
 
@@ -739,7 +739,7 @@ cpm_modulate_bank_warp_kernel(const __grid_constant__ ModParams<float> p, const 
   constexpr int JT = 8, RUN = 8;
   constexpr int PASSES = G::CH / (8 * RUN);   // 8 interval groups per warp x RUN intervals per pass
   constexpr int PER = G::CH / 32;             // symbols per lane per chunk scan
-  static_assert(kFLB - JT == 8 && PASSES >= 1 && PER >= 2 && PER <= 4, "window bases must stay multiples of 8");
+  static_assert((kFLB - JT) % 8 == 0 && PASSES >= 1 && PER >= 2 && PER <= 4, "window bases must stay multiples of 8");
   extern __shared__ __align__(16) unsigned char smem_raw[];
   const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
   const int64_t frame = (int64_t)blockIdx.x * kFwWarps + wid;
@@ -1097,7 +1097,7 @@ static int launch_modulate(const int8_t* d_syms, int64_t B, int64_t S, const dou
     if (noise) cpm_modulate_kernel<T, SPS_, JT_, true><<<grid, block, 0, stream>>>(p);     \
     else cpm_modulate_kernel<T, SPS_, JT_, false><<<grid, block, 0, stream>>>(p);          \
   } while (0)
-  if (sizeof(T) == 4 && ((fast8 && (p.J == 8 || p.J == 3 || p.J == 1)) || fast8_odd) && (ld_out & 1) == 0 &&
+  if (sizeof(T) == 4 && ((fast8 && (p.J == 16 || p.J == 8 || p.J == 3 || p.J == 1)) || fast8_odd) && (ld_out & 1) == 0 &&
       (reinterpret_cast<uintptr_t>(d_out) & 15) == 0 && p.Tn < 0x7FFFF000) {
     const ModParams<float>& pf = reinterpret_cast<const ModParams<float>&>(p);  // T == float on this branch
 #define WF_MODF_LAUNCH(JT_, RUN_, MINB_, ODD_)                                                                   \
@@ -1108,6 +1108,7 @@ static int launch_modulate(const int8_t* d_syms, int64_t B, int64_t S, const dou
     // RUN = 8 intervals per thread at 4 resident blocks/SM (64 registers) measured fastest on B200
     // among RUN in {4, 8, 16} x blocks/SM in {3, 4, 5} (profiles/r1f_kbench_mod_variants.log)
     if (fast8_odd) WF_MODF_LAUNCH(3, 8, 4, true);
+    else if (p.J == 16) WF_MODF_LAUNCH(16, 8, 2, false);  // SOQPSK-B (129-tap pulse): 32 Q coefficients per thread, 2 blocks/SM
     else if (p.J == 8) WF_MODF_LAUNCH(8, 8, 4, false);
     else if (p.J == 3) WF_MODF_LAUNCH(3, 8, 4, false);
     else WF_MODF_LAUNCH(1, 8, 4, false);
