@@ -42,7 +42,7 @@ METRIC = "viterbi_decoded_bits_per_s_soqpsk_tg"
 ALGO_BYTES_PER_BIT = {"prbs_encode": 1.125, "modulate_awgn": 65.0, "mf_bank": 80.0, "viterbi_bert": 16.125,
                       "modulate_awgn_bank": 17.0}
 # what ncu shows each stage is limited by (profiles/*_ncu_full_summary.csv)
-DEFAULT_FUSED = False
+DEFAULT_FUSED = True  # the fused link is the faster one since round 2 (warp-autonomous kernel) and bit-identical
 BOUND = {"prbs_encode": "alu pipe (integer LFSR / precoder work, ~1 B/bit of HBM)",
          "modulate_awgn": "xu pipe + issue (12 MUFU per sample pair: sin/cos of the signal, Box-Muller); HBM write 62 %",
          "mf_bank": "hbm",

@@ -61,7 +61,9 @@ def main():
         for eb, (be, se, n) in zip(a.ebn0, counts.tolist()):
             lo, hi = ber_confidence_interval(int(be), int(n))
             rows.append({"ebn0_db": eb, "bit_errors": int(be), "bits": int(n), "ber": be / n if n else None,
-                         "ci95": [lo, hi]})
+                         "ci95": [lo, hi],
+                         # which bound retired the point (SURVEY 8d stop rule): enough errors, or the bit budget
+                         "stopped_by": "min_errors" if be >= a.min_errors else "max_bits"})
         res = {"waveform": a.waveform, "detector": a.detector, "n_bits": a.n_bits, "n_gpus": world,
                "min_errors": a.min_errors, "max_bits": a.max_bits, "seconds": seconds,
                "simulated_bits": int(np.sum(counts[:, 2])), "bits_per_s": float(np.sum(counts[:, 2]) / seconds),
@@ -71,10 +73,10 @@ def main():
             os.makedirs(os.path.dirname(os.path.abspath(a.out)), exist_ok=True)
             with open(a.out, "w") as f:
                 f.write(text + "\n")
-        sys.stderr.write("Eb/N0  errors         bits        BER        95% interval\n")
+        sys.stderr.write("Eb/N0  errors         bits        BER        95% interval          stopped by\n")
         for r in rows:
-            sys.stderr.write("%5.1f %7d %12.4e %10.3e  [%.3e, %.3e]\n" % (r["ebn0_db"], r["bit_errors"], r["bits"], r["ber"] or 0.0,
-                                                                      r["ci95"][0], r["ci95"][1]))
+            sys.stderr.write("%5.1f %7d %12.4e %10.3e  [%.3e, %.3e]  %s\n" % (r["ebn0_db"], r["bit_errors"], r["bits"], r["ber"] or 0.0,
+                                                                          r["ci95"][0], r["ci95"][1], r["stopped_by"]))
         print(text, flush=True)
     if world > 1:
         dist.barrier(device_ids=[local_rank])

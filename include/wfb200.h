@@ -128,8 +128,8 @@ WF_API int wf_cpm_modulate(const int8_t* d_syms, int64_t B, int64_t S,
  * n_filt == 2 real filters of n_taps == 73; wf_cpm_modulate_bank_supported() says whether a shape is
  * covered (1) or not (0); uncovered shapes return WF_ERR_UNSUPPORTED and the caller runs the two calls.
  * tune selects the kernel (same results, bit for bit): 0 = one BLOCK per frame (512-interval chunks, bank
- * phase on four of eight warps, two block barriers per chunk); 1 / 2 = one WARP per frame, no block barrier
- * (64- / 128-interval chunks, every lane does both phases, 2 / 4 bank calls per lane). */
+ * phase on four of eight warps, two block barriers per chunk); >= 1 = one WARP per frame, no block barrier
+ * (64-interval chunks, every lane does both phases, 2 bank calls per lane). */
 WF_API int wf_cpm_modulate_bank_supported(int K, int sps, int n_filt, int n_taps, int center,
                                           int64_t first_instant, int64_t S, int64_t n_calls);
 WF_API int wf_cpm_modulate_bank(const int8_t* d_syms, int64_t B, int64_t S,

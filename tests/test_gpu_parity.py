@@ -541,7 +541,8 @@ def test_fused_modulate_bank_is_bit_identical_to_the_two_kernel_path(n_bits):
 
 def test_fused_link_covers_soqpsk_tg_and_other_shapes_fall_back_to_four_kernels():
     assert LinkSimulator(LinkConfig(extra={"fused": True}), device=DEV, max_batch=4).fused
-    assert not LinkSimulator(LinkConfig(), device=DEV, max_batch=4).fused
+    assert LinkSimulator(LinkConfig(), device=DEV, max_batch=4).fused            # the default link since round 2
+    assert not LinkSimulator(LinkConfig(extra={"fused": False}), device=DEV, max_batch=4).fused
     for kw in ({"waveform": "soqpsk-mil"}, {"waveform": "soqpsk-a"}, {"detector": "PT"}, {"sps": 10}, {"timing_offset": 3},
                {"waveform": "pcmfm"}, {"extra": {"combine_in_bank": True}}):
         kw = {**kw, "extra": {**kw.get("extra", {}), "fused": True}}

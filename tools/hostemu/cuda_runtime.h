@@ -33,6 +33,8 @@ struct dim3 {
   unsigned x, y, z;
   dim3(unsigned a = 1, unsigned b = 1, unsigned c = 1) : x(a), y(b), z(c) {}
 };
+struct uint3 { uint32_t x, y, z; };
+static inline uint3 make_uint3(uint32_t a, uint32_t b, uint32_t c) { return {a, b, c}; }
 struct uint4 { uint32_t x, y, z, w; };
 struct float2 { float x, y; };
 struct float4 { float x, y, z, w; };

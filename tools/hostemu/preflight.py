@@ -463,7 +463,7 @@ def t_modbank():
         y = np.full((B, ld, 2), np.nan, np.complex64)
         ok(L.wf_mf_bank(ptr(rx), 0, B, T, ldrx, trp, None, 2, taps.shape[1], c, None, None, 2, sps, first, n_calls, ptr(y), ld, None))
         assert L.wf_cpm_modulate_bank_supported(pv.size, sps, 2, taps.shape[1], c, first, S, n_calls) == 1
-        for tune in (0, 1, 2):
+        for tune in (0, 1):
             z = np.full((B, ld, 2), np.nan, np.complex64)
             ok(L.wf_cpm_modulate_bank(ptr(syms), B, S, hp, 1, pp, pv.size, sps, np.pi / 4, -np.pi / 4, ptr(sg), ptr(pts), 77, 0, ptr(fid),
                                       trp, 2, taps.shape[1], c, first, n_calls, ptr(z), ld, tune, None))

@@ -58,10 +58,13 @@ def main():
     ap.add_argument("--detector", default="PAM")
     ap.add_argument("--waveform", default="soqpsk-tg", help="LinkConfig.waveform (algo_gbs figures are SOQPSK/PAM bytes)")
     ap.add_argument("--env", default=None)
-    ap.add_argument("--fused", action="store_true")
+    ap.add_argument("--fused", action="store_true", help="(the fused link is the default; kept for old scripts)")
+    ap.add_argument("--unfused", action="store_true", help="four-kernel SOQPSK link / unfused CPM detector")
     ap.add_argument("--extra", default=None, help="JSON dict merged into LinkConfig.extra (e.g. '{\"tune\": 4}')")
     a = ap.parse_args()
-    extra = {"fused": a.fused}
+    extra = {"fused": True} if a.fused else {}
+    if a.unfused:
+        extra.update({"fused": False, "unfused_detector": True})
     if a.extra:
         extra.update(json.loads(a.extra))
     cfg = LinkConfig(n_bits=4096, detector=a.detector, waveform=a.waveform, extra=extra)

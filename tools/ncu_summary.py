@@ -40,7 +40,9 @@ KEEP = [
     "l1tex__data_bank_conflicts_pipe_lsu_mem_shared.sum",
     "l1tex__data_pipe_lsu_wavefronts_mem_shared.sum",
 ]
-STAGE = {"encode_frames": "prbs_encode", "cpm_modulate": "modulate_awgn", "mf_bank": "mf_bank", "viterbi": "viterbi_bert"}
+# kernel-name fragment -> bench stage; the first match wins (the fused kernel's name contains "cpm_modulate" too)
+STAGE = {"cpm_modulate_bank": "modulate_awgn_bank", "cpm_detect": "detect_fused", "encode_frames": "prbs_encode",
+         "cpm_modulate": "modulate_awgn", "mf_bank": "mf_bank", "viterbi": "viterbi_bert"}
 UNIT_SCALE = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9, "Tbyte": 1e12}
 
 
@@ -67,15 +69,22 @@ def main():
     for r in data:
         name = r[ix["Kernel Name"]]
         for key, stage in STAGE.items():
-            if key in name:
+            if key in name and stage not in traffic:
                 tot = 0.0
                 for m in ("dram__bytes_read.sum", "dram__bytes_write.sum"):
                     tot += float(r[ix[m]]) * UNIT_SCALE[units[ix[m]]]
                 traffic[stage] = {"kernel": name.split("(")[0], "frames": a.frames, "dram_bytes_per_launch": tot,
                                   "source": f"profiles/{a.tag}_ncu_full_summary.csv (ncu --set full, one launch)"}
-    if not a.no_traffic:
-        with open(os.path.join(ROOT, "profiles", "traffic.json"), "w") as f:
-            json.dump(traffic, f, indent=1)
+                break
+    if not a.no_traffic:  # merge: stages this capture does not contain keep their earlier entry
+        tpath = os.path.join(ROOT, "profiles", "traffic.json")
+        merged = {}
+        if os.path.exists(tpath):
+            with open(tpath) as f:
+                merged = json.load(f)
+        merged.update(traffic)
+        with open(tpath, "w") as f:
+            json.dump(merged, f, indent=1)
     print(out)
     print(json.dumps(traffic, indent=1))
 

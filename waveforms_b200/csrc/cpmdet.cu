@@ -253,7 +253,7 @@ __device__ __forceinline__ int warp_min_s32(int v) {
 // Same decisions as oracle/cpm_generic.py up to float32 near-ties (tested with the float64 margins).
 // ---------------------------------------------------------------------------
 constexpr int kBfThreads = 64;  // two autonomous warps
-constexpr int kBfCS = 2;        // steps per staged chunk: 4 CS units of 16 bytes per row
+constexpr int kBfCS = 1;        // steps per staged chunk: 4 CS units of 16 bytes per row (CS = 2 measured 6.0 ms at 12 warps / SM)
 constexpr int kBfPitch = 4 * kBfCS + 1;
 
 struct CpmPairTaps {  // [pair][sample u][0: (c_re, c_re), 1: (c_im, c_im)] of the conj(template) of filters 0 and 1
@@ -345,6 +345,7 @@ cpm_detect_m2l2_kernel(const __grid_constant__ CpmParams p, const __grid_constan
   if (n_chunks > 0) stage(0, 0);
   float2 carry = make_float2(0.f, 0.f);  // sample 8 i - 1 (zero before the frame)
   int released = 0;
+  int next_rel = 2 * D - 1;  // the next step that ends a release block
   for (int c = 0; c < n_chunks; ++c) {
     if (c + 1 < n_chunks) {
       stage((c + 1) & 1, c + 1);
@@ -402,8 +403,9 @@ cpm_detect_m2l2_kernel(const __grid_constant__ CpmParams p, const __grid_constan
           else w1 = funnel_l1(w1, __float_as_uint(d));
         }
         tb[(i & (RING - 1)) * kBfThreads + tid] = (unsigned long long)w0 | ((unsigned long long)w1 << 32);
-        const bool rel = ((i + 1) % D == 0 && i + 1 >= 2 * D) || i == n_steps - 1;
-        if (rel || NORM == 1 || (i % NORM) == NORM - 1) {
+        const bool blk = i == next_rel;
+        const bool rel = blk || i == n_steps - 1;
+        if (rel || NORM == 1 || (i & (NORM - 1)) == NORM - 1) {
           float wmax = pn[0];
 #pragma unroll
           for (int s = 1; s < NS; ++s) wmax = fmaxf(wmax, pn[s]);
@@ -411,9 +413,10 @@ cpm_detect_m2l2_kernel(const __grid_constant__ CpmParams p, const __grid_constan
             int best_s = NS - 1;
 #pragma unroll
             for (int s = NS - 2; s >= 0; --s) best_s = (pn[s] == wmax) ? s : best_s;  // lowest index wins
-            if ((i + 1) % D == 0 && i + 1 >= 2 * D) {
+            if (blk) {
               trace_release(i, best_s, released, i + 1 - D);
               released = i + 1 - D;
+              next_rel += D;
             }
             if (i == n_steps - 1) trace_release(i, best_s, released, n_steps);
           }
@@ -476,13 +479,58 @@ struct CpmLaneTaps {  // conj(template) of filters 0..7 for both parities: [pari
   float t[2][8][8][2];
 };
 
+// Walk the path of state (v, hn) back from step t to step lo and release steps [lo, hi): lane j handles symbol
+// lo + j (+ 32).  Warp-uniform.  Per step: one broadcast byte load, the winning predecessor symbol x from two
+// bits of it, the phase step of (parity, x) by PRMT from a packed register, and a 2-bit shift-in of h_new.
+// Returns this lane's (symbol errors, bit errors, compared bits).
+template <int RING>
+static __device__ __noinline__ uint3 lanev_trace_release(const uint8_t* tb, uint32_t dl0, uint32_t dl1, int t, int v, int hn, int lo,
+                                                         int hi, int lane, int8_t* out, const int8_t* tx, int cmp_lo, int cmp_hi) {
+  constexpr int M = 4, BITS = 2;
+  unsigned long long w0 = 0ull, w1 = 0ull;  // 2 bits per released symbol, symbol lo in the lowest bits of w0
+  int hn2 = 2 * hn;
+  auto back = [&](int tau) {
+    const unsigned b = tb[((tau & (RING - 1)) << 5) + v];
+    const unsigned x = (b >> hn2) & 3u;
+    const uint32_t dl = (tau & 1) ? dl0 : dl1;  // transition parity (tau - Lp + 1) % 2 = (tau + 1) & 1
+#ifdef WF_HOSTEMU
+    const uint32_t dv = (dl >> (8 * x)) & 0xFFu;
+#else
+    const uint32_t dv = __byte_perm(dl, 0u, 0x4440u | x);
+#endif
+    v = (v - (int)dv) & 31;
+    hn2 = (int)(2u * x);
+  };
+  int tau = t;
+  for (; tau >= hi; --tau) back(tau);                  // merge part: nothing released
+  if (hi - lo <= 32) {
+    for (; tau >= lo; --tau) { w0 = (w0 << 2) | (unsigned long long)(hn2 >> 1); back(tau); }
+  } else {
+    for (; tau >= lo; --tau) { w1 = (w1 << 2) | (w0 >> 62); w0 = (w0 << 2) | (unsigned long long)(hn2 >> 1); back(tau); }
+  }
+  uint3 r = make_uint3(0u, 0u, 0u);
+  const int n = hi - lo;
+  for (int j = lane; j < n; j += 32) {
+    const unsigned dec = (unsigned)((j < 32 ? w0 >> (2 * j) : w1 >> (2 * (j - 32))) & 3ull);
+    const int k = lo + j;
+    if (out) out[k] = (int8_t)(2 * (int)dec - (M - 1));
+    if (tx && k >= cmp_lo && k < cmp_hi) {
+      const unsigned tt = (unsigned)(((int)tx[k] + (M - 1)) >> 1);
+      r.x += (tt != dec) ? 1u : 0u;
+      r.y += __popc((tt ^ dec) & (unsigned)(M - 1));
+      r.z += BITS;  // column 2 counts compared BITS for every waveform
+    }
+  }
+  return r;
+}
+
 template <int RING, int NORM>
 __global__ void __launch_bounds__(kLfWarps * 32)
 cpm_detect_lanev_kernel(const __grid_constant__ CpmParams p, const __grid_constant__ CpmRot rot,
                         const __grid_constant__ CpmLaneTaps tp) {
   constexpr int M = 4, NHH = 2, BITS = 2;
   __align__(16) __shared__ float2 ring_s[kLfWarps][kLfRingSamples];
-  __align__(16) __shared__ float4 zq_s[kLfWarps][8];          // (re_x, re_x+1, im_x, im_x+1), index 2 h_new + x / 2
+  __align__(16) __shared__ float4 zq_s[kLfWarps][2][2][8];    // [buffer][step of the pair][(re_x, re_x+1, im_x, im_x+1) at 2 h_new + x / 2]
   __shared__ uint8_t tb_s[kLfWarps][RING * 32];
   const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
   const int64_t frame = (int64_t)blockIdx.x * kLfWarps + wid;
@@ -495,8 +543,6 @@ cpm_detect_lanev_kernel(const __grid_constant__ CpmParams p, const __grid_consta
   const int cmp_lo = (int)p.skip_head, cmp_hi = min(S, n_steps) - (int)p.skip_tail;
   const float2* rxrow = reinterpret_cast<const float2*>(p.rx) + frame * p.ld_rx;
   float2* ring = ring_s[wid];
-  float* zs = reinterpret_cast<float*>(zq_s[wid]);
-  const float4* zq = zq_s[wid];
   uint8_t* tb = tb_s[wid];
 
   // per-lane transition tables for each modulation-index parity, as register PAIRS (x, x + 1)
@@ -506,11 +552,14 @@ cpm_detect_lanev_kernel(const __grid_constant__ CpmParams p, const __grid_consta
   for (int h = 0; h < NHH; ++h)
 #pragma unroll
     for (int x = 0; x < M; ++x) {
-      src[h][x] = (lane - p.delta[h][x]) & 31;
-      const float c = rot.c[src[h][x]], s = rot.s[src[h][x]];
+      src[h][x] = lane - p.delta[h][x];  // SHFL.IDX uses the source lane modulo 32: no mask needed
+      const float c = rot.c[src[h][x] & 31], s = rot.s[src[h][x] & 31];
       if (x & 1) { rc2[h][x / 2].y = c; rs2[h][x / 2].y = s; }
       else { rc2[h][x / 2].x = c; rs2[h][x / 2].x = s; }
     }
+  // phase steps of both parities packed one per byte: the traceback picks byte x with one PRMT
+  const uint32_t dl0 = (uint32_t)p.delta[0][0] | ((uint32_t)p.delta[0][1] << 8) | ((uint32_t)p.delta[0][2] << 16) | ((uint32_t)p.delta[0][3] << 24);
+  const uint32_t dl1 = (uint32_t)p.delta[1][0] | ((uint32_t)p.delta[1][1] << 8) | ((uint32_t)p.delta[1][2] << 16) | ((uint32_t)p.delta[1][3] << 24);
 #ifndef WF_HOSTEMU
   // pin the values in registers: left alone, the compiler re-reads rot.c[src] in the loop, a
   // lane-divergent constant-bank access that serialises 32 ways
@@ -524,24 +573,21 @@ cpm_detect_lanev_kernel(const __grid_constant__ CpmParams p, const __grid_consta
 #pragma unroll
     for (int x = 0; x < M; ++x) asm volatile("" : "+r"(src[h][x]));
 #endif
-  // bank role of this lane
-  const int bq = lane >> 2, bwhich = (lane >> 1) & 1, bhalf = lane & 1;
-  float2 tapd[NHH][4];
+  // bank role of this lane: it serves the step of ITS parity (steps come in pairs (even, odd)), filter pair q,
+  // and accumulates either (A, C) (which = 0, taps c_re) or (E, B) (which = 1, taps c_im) over all 8 samples
+  const int bstep = lane >> 4, bq = (lane >> 1) & 7, bwhich = lane & 1;
+  float2 tapd[8];
 #pragma unroll
-  for (int h = 0; h < NHH; ++h)
-#pragma unroll
-    for (int j = 0; j < 4; ++j) {
-      const float t = tp.t[h][bq][4 * bhalf + j][bwhich];
-      tapd[h][j] = make_float2(t, t);
-    }
+  for (int k = 0; k < 8; ++k) {
+    const float t = tp.t[bstep][bq][k][bwhich];
+    tapd[k] = make_float2(t, t);
+  }
 #ifndef WF_HOSTEMU
 #pragma unroll
-  for (int h = 0; h < NHH; ++h)
-#pragma unroll
-    for (int j = 0; j < 4; ++j) asm volatile("" : "+f"(tapd[h][j].x), "+f"(tapd[h][j].y));
+  for (int k = 0; k < 8; ++k) asm volatile("" : "+f"(tapd[k].x), "+f"(tapd[k].y));
 #endif
   const int bf = bwhich ? 15 - bq : bq;              // the filter this lane finishes
-  const int zword = 4 * (bf >> 1) + (bf & 1);        // its re slot; im is two words further on
+  const int zword = 32 * bstep + 4 * (bf >> 1) + (bf & 1);  // its re slot inside a buffer (floats); im is two words further on
 
   float pm[M];
 #pragma unroll
@@ -561,37 +607,17 @@ cpm_detect_lanev_kernel(const __grid_constant__ CpmParams p, const __grid_consta
     cp_async_commit();
   };
 
-  // walk the path of state (v, hn) back from step t; release steps [lo, hi): lane j handles symbol lo + j (+ 32)
+  // traceback + release live out of line (lanev_trace_release): the unrolled step loop stays small enough for the
+  // instruction cache (inlined eight times it cost 0.9 stall cycles per issue in "no instruction")
   auto trace_release = [&](int t, int v, int hn, int lo, int hi) {
-    unsigned long long w0 = 0ull, w1 = 0ull;  // 2 bits per released symbol: the first 32 in w0, the rest in w1
-    for (int tau = t; tau >= lo; --tau) {
-      const unsigned b = tb[(tau & (RING - 1)) * 32 + v];
-      const int x = (int)(b >> (2 * hn)) & 3;
-      if (tau < hi) {
-        const int j = tau - lo;
-        if (j < 32) w0 |= (unsigned long long)hn << (2 * j);
-        else w1 |= (unsigned long long)hn << (2 * (j - 32));
-      }
-      v = (v - p.delta[(tau + 1) & 1][x]) & 31;  // transition parity (tau - Lp + 1) % 2
-      hn = x;
-    }
-    const int n = hi - lo;
-    for (int j = lane; j < n; j += 32) {
-      const unsigned dec = (unsigned)((j < 32 ? w0 >> (2 * j) : w1 >> (2 * (j - 32))) & 3ull);
-      const int k = lo + j;
-      if (out) out[k] = (int8_t)(2 * (int)dec - (M - 1));
-      if (tx && k >= cmp_lo && k < cmp_hi) {
-        const unsigned tt = (unsigned)(((int)tx[k] + (M - 1)) >> 1);
-        sym_err += (tt != dec) ? 1u : 0u;
-        bit_err += __popc((tt ^ dec) & (unsigned)(M - 1));
-        compared += BITS;  // column 2 counts compared BITS for every waveform
-      }
-    }
+    const uint3 r = lanev_trace_release<RING>(tb, dl0, dl1, t, v, hn, lo, hi, lane, out, tx, cmp_lo, cmp_hi);
+    sym_err += r.x; bit_err += r.y; compared += r.z;
   };
 
   stage(0);
   stage(1);
   int released = 0;
+  int next_rel = 2 * D - 1;  // the next step that ends a release block
   for (int i0 = 0; i0 < n_steps; i0 += 8) {
     // group g = i0 / 8 reads chunks g and g + 1; chunk g + 2 replaces chunk g - 2 (last read by step i0 - 1)
     __syncwarp();
@@ -599,79 +625,93 @@ cpm_detect_lanev_kernel(const __grid_constant__ CpmParams p, const __grid_consta
     cp_async_wait<1>();
     __syncwarp();
 #pragma unroll
-    for (int u = 0; u < 8; ++u) {
-      const int i = i0 + u;
-      if (i >= n_steps) break;
-      constexpr int dummy = 0; (void)dummy;
-      const int hp = u & 1;            // filter parity i % 2 (i0 is a multiple of 8)
-      const int lp = (u + 1) & 1;      // transition parity (i - 1) % 2
-      // ---- bank: this lane's four samples, one FFMA2 each ----------------------------------------
-      const int s0 = 8 * i + 7 + 4 * bhalf;  // ring slot of sample 8 i - 1 + 4 half  (slot(n) = (n + 8) & 255)
-      const float2 x0 = ring[s0 & (kLfRingSamples - 1)];
-      const float4 x12 = *reinterpret_cast<const float4*>(ring + ((s0 + 1) & (kLfRingSamples - 1)));
-      const float2 x3 = ring[(s0 + 3) & (kLfRingSamples - 1)];
-      float2 acc = make_float2(0.f, 0.f);
-      acc = ffma2(x0, tapd[hp][0], acc);
-      acc = ffma2(make_float2(x12.x, x12.y), tapd[hp][1], acc);
-      acc = ffma2(make_float2(x12.z, x12.w), tapd[hp][2], acc);
-      acc = ffma2(x3, tapd[hp][3], acc);
-      acc.x += __shfl_xor_sync(0xFFFFFFFFu, acc.x, 1);
-      acc.y += __shfl_xor_sync(0xFFFFFFFFu, acc.y, 1);
-      const float ox = __shfl_xor_sync(0xFFFFFFFFu, acc.x, 2), oy = __shfl_xor_sync(0xFFFFFFFFu, acc.y, 2);
-      // which = 0: own (A, C), other (E, B) -> z_q = (A - B, E + C);  which = 1: own (E, B), other (A, C) -> z_{15-q} = (A + B, C - E)
-      const float zr = bwhich ? ox + acc.y : acc.x - oy;
-      const float zi = bwhich ? oy - acc.x : ox + acc.y;
-      __syncwarp();  // every lane has finished reading the previous step's outputs
-      if (bhalf == 0) { zs[zword] = zr; zs[zword + 2] = zi; }
-      __syncwarp();
-      // ---- add-compare-select ----------------------------------------------------------------------
-      float2 pmx2[M / 2];
-#pragma unroll
-      for (int j = 0; j < M / 2; ++j) {
-        pmx2[j].x = __shfl_sync(0xFFFFFFFFu, pm[2 * j], src[lp][2 * j]);
-        pmx2[j].y = __shfl_sync(0xFFFFFFFFu, pm[2 * j + 1], src[lp][2 * j + 1]);
+    for (int up = 0; up < 4; ++up) {
+      if (i0 + 2 * up >= n_steps) break;
+      // ---- bank of the step pair (i0 + 2 up, + 1): 8 samples, one FFMA2 each, two chains ------------------
+      {
+        const int s0 = 8 * (i0 + 2 * up + bstep) + 7;  // ring slot of sample 8 i - 1  (slot(n) = (n + 8) & 255)
+        const float2 x0 = ring[s0 & (kLfRingSamples - 1)];
+        const float4 x12 = *reinterpret_cast<const float4*>(ring + ((s0 + 1) & (kLfRingSamples - 1)));
+        const float4 x34 = *reinterpret_cast<const float4*>(ring + ((s0 + 3) & (kLfRingSamples - 1)));
+        const float4 x56 = *reinterpret_cast<const float4*>(ring + ((s0 + 5) & (kLfRingSamples - 1)));
+        const float2 x7 = ring[(s0 + 7) & (kLfRingSamples - 1)];
+        float2 a0 = make_float2(0.f, 0.f), a1 = make_float2(0.f, 0.f);
+        a0 = ffma2(x0, tapd[0], a0);
+        a1 = ffma2(make_float2(x12.x, x12.y), tapd[1], a1);
+        a0 = ffma2(make_float2(x12.z, x12.w), tapd[2], a0);
+        a1 = ffma2(make_float2(x34.x, x34.y), tapd[3], a1);
+        a0 = ffma2(make_float2(x34.z, x34.w), tapd[4], a0);
+        a1 = ffma2(make_float2(x56.x, x56.y), tapd[5], a1);
+        a0 = ffma2(make_float2(x56.z, x56.w), tapd[6], a0);
+        a1 = ffma2(x7, tapd[7], a1);
+        const float2 acc = fadd2(a0, a1);
+        const float ox = __shfl_xor_sync(0xFFFFFFFFu, acc.x, 1), oy = __shfl_xor_sync(0xFFFFFFFFu, acc.y, 1);
+        // which = 0: own (A, C), other (E, B) -> z_q = (A - B, E + C);  which = 1: own (E, B), other (A, C) -> z_{15-q} = (A + B, C - E)
+        const float zr = bwhich ? ox + acc.y : acc.x - oy;
+        const float zi = bwhich ? oy - acc.x : ox + acc.y;
+        float* zs = reinterpret_cast<float*>(zq_s[wid][up & 1]);  // double buffered: the readers of this buffer are two pairs back
+        zs[zword] = zr;
+        zs[zword + 2] = zi;
+        __syncwarp();
       }
-      unsigned dec = 0;
-      float lmax = -3.0e38f;
 #pragma unroll
-      for (int hn = 0; hn < M; ++hn) {
-        float2 c2[M / 2];
+      for (int us = 0; us < 2; ++us) {
+        const int u = 2 * up + us;
+        const int i = i0 + u;
+        if (i >= n_steps) break;
+        const int lp = (us + 1) & 1;      // transition parity (i - 1) % 2  (i0 is a multiple of 8: i % 2 = us)
+        const float4* zq = zq_s[wid][up & 1][us];
+        // ---- add-compare-select ----------------------------------------------------------------------
+        float2 pmx2[M / 2];
 #pragma unroll
         for (int j = 0; j < M / 2; ++j) {
-          const float4 q = zq[2 * hn + j];
-          float2 t2 = fmul2(rc2[lp][j], make_float2(q.x, q.y));
-          t2 = ffma2(rs2[lp][j], make_float2(q.z, q.w), t2);
-          c2[j] = fadd2(pmx2[j], t2);
+          pmx2[j].x = __shfl_sync(0xFFFFFFFFu, pm[2 * j], src[lp][2 * j]);
+          pmx2[j].y = __shfl_sync(0xFFFFFFFFu, pm[2 * j + 1], src[lp][2 * j + 1]);
         }
-        // strict '>' tournament: the lowest x keeps ties
-        const bool b01 = c2[0].y > c2[0].x, b23 = c2[1].y > c2[1].x;
-        const float m01 = fmaxf(c2[0].x, c2[0].y), m23 = fmaxf(c2[1].x, c2[1].y);
-        const bool bf2 = m23 > m01;
-        const float best = fmaxf(m01, m23);
-        const unsigned idx = bf2 ? (2u | (b23 ? 1u : 0u)) : (b01 ? 1u : 0u);
-        dec |= idx << (2 * hn);
-        pm[hn] = best;
-        lmax = fmaxf(lmax, best);
-      }
-      tb[(i & (RING - 1)) * 32 + lane] = (uint8_t)dec;
-      const bool rel = ((i + 1) % D == 0 && i + 1 >= 2 * D) || i == n_steps - 1;
-      if (rel || NORM == 1 || (u % NORM) == NORM - 1) {
-        const float wmax = warp_max_f32(lmax);
-        if (rel) {
-          int best_s = 0x7FFFFFFF;  // lowest state index v M + h with the maximum metric
+        unsigned dec = 0;
+        float lmax = -3.0e38f;
 #pragma unroll
-          for (int hn = M - 1; hn >= 0; --hn)
-            if (pm[hn] == wmax) best_s = lane * M + hn;
-          const int wbest = warp_min_s32(best_s);
-          __syncwarp();  // this step's decision bytes are visible to the whole warp
-          if ((i + 1) % D == 0 && i + 1 >= 2 * D) {
-            trace_release(i, wbest >> 2, wbest & 3, released, i + 1 - D);
-            released = i + 1 - D;
+        for (int hn = 0; hn < M; ++hn) {
+          float2 c2[M / 2];
+#pragma unroll
+          for (int j = 0; j < M / 2; ++j) {
+            const float4 q = zq[2 * hn + j];
+            float2 t2 = fmul2(rc2[lp][j], make_float2(q.x, q.y));
+            t2 = ffma2(rs2[lp][j], make_float2(q.z, q.w), t2);
+            c2[j] = fadd2(pmx2[j], t2);
           }
-          if (i == n_steps - 1) trace_release(i, wbest >> 2, wbest & 3, released, n_steps);
+          // strict '>' tournament: the lowest x keeps ties
+          const bool b01 = c2[0].y > c2[0].x, b23 = c2[1].y > c2[1].x;
+          const float m01 = fmaxf(c2[0].x, c2[0].y), m23 = fmaxf(c2[1].x, c2[1].y);
+          const bool bf2 = m23 > m01;
+          const float best = fmaxf(m01, m23);
+          const unsigned idx = bf2 ? (2u | (b23 ? 1u : 0u)) : (b01 ? 1u : 0u);
+          dec |= idx << (2 * hn);
+          pm[hn] = best;
+          lmax = fmaxf(lmax, best);
         }
+        tb[((i & (RING - 1)) << 5) + lane] = (uint8_t)dec;
+        const bool blk = i == next_rel;
+        const bool rel = blk || i == n_steps - 1;
+        if (rel || NORM == 1 || (u % NORM) == NORM - 1) {
+          const float wmax = warp_max_f32(lmax);
+          if (rel) {
+            int best_s = 0x7FFFFFFF;  // lowest state index v M + h with the maximum metric
 #pragma unroll
-        for (int hn = 0; hn < M; ++hn) pm[hn] -= wmax;
+            for (int hn = M - 1; hn >= 0; --hn)
+              if (pm[hn] == wmax) best_s = lane * M + hn;
+            const int wbest = warp_min_s32(best_s);
+            __syncwarp();  // this step's decision bytes are visible to the whole warp
+            if (blk) {
+              trace_release(i, wbest >> 2, wbest & 3, released, i + 1 - D);
+              released = i + 1 - D;
+              next_rel += D;
+            }
+            if (i == n_steps - 1) trace_release(i, wbest >> 2, wbest & 3, released, n_steps);
+          }
+#pragma unroll
+          for (int hn = 0; hn < M; ++hn) pm[hn] -= wmax;
+        }
       }
     }
   }
@@ -741,7 +781,7 @@ static int fused_kind(int dtype, int64_t Tn, int64_t ld_rx, const double* tre, c
         if ((float)tre[a] != (float)tre[b] || (float)tim[a] != -(float)tim[b]) return 0;
       }
   if (q.M == 2 && q.n_h == 1 && q.p == 10 && q.delta[0][0] == 13 && q.delta[0][1] == 7 && q.depth <= 32 &&
-      8 * n_steps <= Tn && 8 * ((n_steps + 1) & ~(int64_t)1) <= ld_rx)  // chunks are two steps: the last one may read one step on
+      8 * n_steps <= Tn && 8 * ((n_steps + kBfCS - 1) / kBfCS) * kBfCS <= ld_rx)  // whole chunks are staged
     return 1;
   if (q.M == 4 && q.n_h == 2 && q.p == 16 && q.depth <= 32) return 2;
   return 0;

@@ -687,7 +687,9 @@ template <int R> struct FwGeom {
 };
 __device__ __forceinline__ int fw_pad(int s) { return s + (s >> 3); }
 
-template <int R>
+// NT1: taps of the second filter that can be non-zero (rho_1 is 65 taps zero-padded to 73: a zero tap adds
+// exactly nothing, fma(x, 0, y) == y, so skipping it keeps the outputs bit-identical)
+template <int R, int NT1>
 static __device__ __forceinline__ void fw_bank_phase(const FuseParams& fz, const float2* tile, int t, int cbase, float2* zrow) {
   using G = FwGeom<R>;
   const int c0 = cbase + R * t;
@@ -718,7 +720,8 @@ static __device__ __forceinline__ void fw_bank_phase(const FuseParams& fz, const
           const int u = v + s - e * 8;
           if (u >= 0 && u < kFzNT) {
 #pragma unroll
-            for (int f = 0; f < kFzNF; ++f) y[e][f] = ffma2(x, tap2[f * kFzNT + kFzNT - 1 - u], y[e][f]);
+            for (int f = 0; f < kFzNF; ++f)
+              if (f == 0 || u >= kFzNT - NT1) y[e][f] = ffma2(x, tap2[f * kFzNT + kFzNT - 1 - u], y[e][f]);
           }
         }
       }
@@ -732,7 +735,7 @@ static __device__ __forceinline__ void fw_bank_phase(const FuseParams& fz, const
   }
 }
 
-template <bool NOISE, int R, int MINB>
+template <bool NOISE, int R, int MINB, int NT1>
 __global__ void __launch_bounds__(kFwWarps * 32, MINB)
 cpm_modulate_bank_warp_kernel(const __grid_constant__ ModParams<float> p, const __grid_constant__ FuseParams fz, int n_chunks) {
   using G = FwGeom<R>;
@@ -916,7 +919,7 @@ cpm_modulate_bank_warp_kernel(const __grid_constant__ ModParams<float> p, const 
     }
     __syncwarp();  // the chunk's samples (and the carried look-back) are in the tile
     // ---- (c) bank: R consecutive calls per lane, straight to HBM ---------------------------------
-    fw_bank_phase<R>(fz, tile, lane, K0 - fz.CB, zrow);
+    fw_bank_phase<R, NT1>(fz, tile, lane, K0 - fz.CB, zrow);
     // ---- (d) carry the newest LB samples to the front of the tile -------------------------------
     float4 keep[(kFzLBMax / 2 + 31) / 32];
 #pragma unroll
@@ -1163,23 +1166,26 @@ static int launch_modulate_bank(const int8_t* d_syms, int64_t B, int64_t S, cons
   memset(&fz, 0, sizeof(fz));
   fz.z = reinterpret_cast<float2*>(d_z); fz.ld_z = ld_z; fz.n_calls = (int)n_calls; fz.CB = CB; fz.LB = LB;
   for (int i = 0; i < kFzNF * kFzNT; ++i) fz.tap2[2 * i] = fz.tap2[2 * i + 1] = (float)taps_re[i];
-  if (tune >= 1) {  // warp-autonomous kernel: 1 = R 2 (64-interval chunks, 8 blocks of 4 warps per SM), 2 = R 4 (128, 5 blocks)
-    const int R = tune == 2 ? 4 : 2, CH = 32 * R;
+  if (tune >= 1) {  // warp-autonomous kernel: R = 2 calls per lane, 64-interval chunks, 8 blocks of 4 warps per SM
+    // (R = 4 / 128-interval chunks / 5 blocks per SM measured the same: 7.00 against 6.94 ms per 65536 frames, r2c)
+    const int R = 2, CH = 32 * R;
+    bool pad8 = true;  // the second filter ends in 8 exact zeros (rho_1 padded to rho_0's length)?
+    for (int t = kFzNT - 8; t < kFzNT; ++t) pad8 = pad8 && (float)taps_re[kFzNT + t] == 0.0f;
     const int64_t A_last = ((S + 1) * 8 - 1 + p.off) >> 3;
     int64_t nch = A_last / CH + 1;
     const int64_t need = (n_calls + CB + CH - 1) / CH;
     if (need > nch) nch = need;
     const dim3 gridw((unsigned)((B + kFwWarps - 1) / kFwWarps)), blockw(kFwWarps * 32);
-#define WF_FW_LAUNCH(NOISE_, R_, MINB_)                                                                           \
+#define WF_FW_LAUNCH(NOISE_, R_, MINB_, NT1_)                                                                     \
   do {                                                                                                            \
-    auto kfn = cpm_modulate_bank_warp_kernel<NOISE_, R_, MINB_>;                                                   \
+    auto kfn = cpm_modulate_bank_warp_kernel<NOISE_, R_, MINB_, NT1_>;                                             \
     const size_t sm = FwGeom<R_>::WARP_BYTES * kFwWarps;                                                          \
     cudaError_t e = cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm);              \
     if (e != cudaSuccess) return cuda_fail(e, "cudaFuncSetAttribute(cpm_modulate_bank_warp_kernel)");             \
     kfn<<<gridw, blockw, sm, stream>>>(p, fz, (int)nch);                                                           \
   } while (0)
-    if (R == 2) { if (d_sigma) WF_FW_LAUNCH(true, 2, 8); else WF_FW_LAUNCH(false, 2, 8); }
-    else { if (d_sigma) WF_FW_LAUNCH(true, 4, 5); else WF_FW_LAUNCH(false, 4, 5); }
+    if (pad8) { if (d_sigma) WF_FW_LAUNCH(true, 2, 8, kFzNT - 8); else WF_FW_LAUNCH(false, 2, 8, kFzNT - 8); }
+    else { if (d_sigma) WF_FW_LAUNCH(true, 2, 8, kFzNT); else WF_FW_LAUNCH(false, 2, 8, kFzNT); }
 #undef WF_FW_LAUNCH
     WF_LAUNCH_CHECK("cpm_modulate_bank_warp_kernel");
     return WF_OK;
