@@ -272,6 +272,23 @@ WF_API int wf_cpm_detect(const void* d_rx, int dtype, int64_t B, int64_t T, int6
                          int64_t skip_head, int64_t skip_tail,
                          const int32_t* d_point, int64_t* d_counters, int tune, void* stream);
 
+/* ---- signal diagnostics as CUDA reductions (the reference only plots these:
+ *      waveforms/viz/*.py, matplotlib; the figures are unavailable on this box, the arrays are not) ---- */
+/* viz/psd.py:16-54 = matplotlib.mlab.psd(x * amplitude, NFFT = nfft, noverlap = 0, window = hanning,
+ * scale_by_freq = False), two-sided and fft-shifted: d_out float[B][nfft] = mean over the T / nfft whole
+ * segments of |FFT(hann * x)|^2 / (sum hann)^2, bin nfft/2 = DC.  d_sig complex64[B][ld].  nfft: power of two <= 4096. */
+WF_API int wf_welch_psd(const void* d_sig, int64_t B, int64_t T, int64_t ld, int nfft, double amplitude,
+                        float* d_out, void* stream);
+/* viz/eye.py:39-56: d_out complex64[B][(T-1)/span][span+1], trace i = sig[i*span .. i*span+span] (span = sps * modulo) */
+WF_API int wf_eye_traces(const void* d_sig, int64_t B, int64_t T, int64_t ld, int span, void* d_out, void* stream);
+/* viz/tree.py:64-71: d_out float[B][T/span][span] = np.unwrap(np.angle(chunk)) - (use_off ? off : chunk's first value) */
+WF_API int wf_phase_tree(const void* d_sig, int64_t B, int64_t T, int64_t ld, int span, int use_off, double off,
+                         float* d_out, void* stream);
+/* replacement for the hard-coded timing offsets of examples/soqpsk_detection.py:183-192: d_out float[B][sps] =
+ * mean |y[n]|^2 over n = phase (mod sps) of a full-rate matched-filter output d_y complex64[B][ld]; the best
+ * sampling phase maximises it (timing_offset = -phase in the script's sign convention). */
+WF_API int wf_timing_metric(const void* d_y, int64_t B, int64_t T, int64_t ld, int sps, float* d_out, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -50,6 +50,9 @@ def main():
         out = {k: sum(r[k] for r in reps) for k in keys}
         for k in ("pt_errors", "pam_errors", "pt_m1_errors"):
             out[k + "_by_replicate"] = np.stack([r[k] for r in reps])
+        withf = [r for r in reps if "errors_by_frame" in r.files]
+        if withf:  # [replicate][point][frame][PT, PAM, PT@-1] of the replicates that recorded it
+            out["errors_by_frame"] = np.stack([r["errors_by_frame"] for r in withf])
         np.savez_compressed(a.out, ebn0_db=reps[0]["ebn0_db"], frames=reps[0]["frames"], replicates=np.array(len(reps)),
                             salts=np.array([int(r["salt"]) if "salt" in r.files else 0 for r in reps]), **out)
         for e in range(13):
@@ -64,6 +67,9 @@ def main():
     n = np.zeros(13, dtype=np.int64)
     ptm1 = np.zeros(13, dtype=np.int64)
     nm1 = np.zeros(13, dtype=np.int64)
+    # per-frame error counts (task order = point-major, frame-minor): bit errors come in bursts, so the
+    # honest variance of a point's error count is the between-frame one, not the binomial one
+    by_frame = np.array([[r[1], r[2], r[4]] for r in res], dtype=np.int32).reshape(13, a.frames, 3)
     for e, a_pt, a_pam, c, a_ptm1, cm1 in res:
         pt[e] += a_pt
         pam[e] += a_pam
@@ -73,7 +79,8 @@ def main():
     # pt_m1_*: the PT detector at timing offset -1, the operating point the shipped example uses
     # for TG (soqpsk_detection.py:184-185); pt_errors / pam_errors are at offset 0.
     np.savez_compressed(a.out, ebn0_db=np.array(pts), pt_errors=pt, pam_errors=pam, compared=n,
-                        pt_m1_errors=ptm1, pt_m1_compared=nm1, frames=np.array(a.frames), salt=np.array(a.salt))
+                        pt_m1_errors=ptm1, pt_m1_compared=nm1, frames=np.array(a.frames), salt=np.array(a.salt),
+                        errors_by_frame=by_frame)  # [point][frame][PT, PAM, PT@-1]
     for e in pts:
         print(e, pt[e], pam[e], n[e], ptm1[e], nm1[e])
 

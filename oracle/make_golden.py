@@ -281,6 +281,37 @@ def main():
     g11["sigma"] = float(np.sqrt(8 / (2 * 10 ** 0.6)))
     sv("g11_soqpsk_ab.npz", **g11)
 
+    # G12: phase trees (viz/tree.py:89-146).  tree.py imports matplotlib (absent), so its arithmetic is replayed
+    # with the reference's own TrellisEncoder and cpm_modulate: sequences (:110-126), modulation + slicing
+    # (:128-140), unwrap per chunk (:64-71).
+    g12 = {}
+    for lab, tre, h, pf in (("pcmfm", tm.SimpleTrellis2, PCMFM_NUMER / PCMFM_DENOM, freq_pulse_pcmfm(8, 4)),
+                            ("multih", tm.SimpleTrellis4, MULTIH_IRIG_NUMER / MULTIH_IRIG_DENOM, freq_pulse_multih_irig(8)),
+                            ("mil", tm.SOQPSKTrellis4x2DiffEncoded, 0.25, freq_pulse_soqpsk_mil(8)),
+                            ("tg", tm.SOQPSKTrellis4x2DiffEncoded, 0.25, freq_pulse_soqpsk_tg(8))):
+        enc = TrellisEncoder(tre)
+        bps, length = enc.input_cardinality, int(pf.size // 8)
+        packed_len = bps * length
+        seqs = []
+        for i in range(2 ** packed_len):
+            enc.state = 0
+            seq = [(i >> j) & 1 for j in range(packed_len)]
+            seqs.append(tuple(enc.encode(np.array([0] * packed_len + seq, dtype=np.uint8))))
+        seqs = sorted(set(seqs))
+        plotted = np.zeros(len(seqs) * length * 8 + 1, dtype=np.complex128)
+        for i, sy in enumerate(seqs):
+            _t, tmp = cpm_modulate(np.array(sy, dtype=np.int8), mod_index=h, pulse_filter=pf, sps=8)
+            plotted[i * length * 8:(i + 1) * length * 8] = tmp[length * 8 - 1:2 * length * 8 - 1]
+        phase = np.angle(plotted)
+        rows = []
+        for chunk in range(phase.size // (8 * length)):
+            sl = np.unwrap(phase[chunk * length * 8:(chunk + 1) * length * 8])
+            rows.append(sl - sl[0])
+        g12[f"{lab}_symbols"] = np.array(seqs, dtype=np.int8)
+        g12[f"{lab}_phases"] = np.stack(rows)
+        print("phase tree", lab, len(seqs), "sequences x", length * 8, "samples")
+    sv("g12_phase_tree.npz", **g12)
+
     if not a.skip_example:
         # G8: the example exactly as shipped: sps 10, sigma sqrt(2)/2, MIL then TG
         # from ONE rng (soqpsk_detection.py:26,38-41,66-70,183-187)

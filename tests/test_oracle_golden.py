@@ -269,3 +269,45 @@ def test_minimum_distance_reproduces_published_values():
     assert abs(d_artm - 1.29) < 0.01 and gam == (2, -4, 6, -4, 2)
     # the asymptote these distances give at BER 1e-5: 8.5 dB for PCM/FM, 11.5 dB for ARTM CPM
     assert abs(ebn0_db_for_ber(d_pcm, 1e-5) - 8.5) < 0.1 and abs(ebn0_db_for_ber(d_artm, 1e-5) - 11.5) < 0.1
+
+
+# ---- diagnostics arrays (oracle/viz_ref.py) --------------------------------------------
+@pytest.mark.parametrize("lab", ["pcmfm", "multih", "mil", "tg"])
+def test_phase_tree_restatement_vs_reference(lab):
+    """G12 = viz/tree.py:89-146 replayed with the reference's own encoder and modulator: the oracle's
+    phase_tree on the oracle's modulated branches reproduces it."""
+    from oracle import viz_ref as vr
+
+    g = golden("g12_phase_tree.npz")
+    hh, pf = {"pcmfm": ([0.7], o.pulse_pcmfm(8, 4)), "multih": ([4 / 16, 5 / 16], o.pulse_multih(8)),
+              "mil": ([0.25], o.pulse_soqpsk_mil(8)), "tg": ([0.25], o.pulse_soqpsk_tg(8))}[lab]
+    syms = g[f"{lab}_symbols"]
+    length = pf.size // 8
+    plotted = np.zeros(syms.shape[0] * length * 8 + 1, dtype=np.complex128)
+    for i, q in enumerate(syms):
+        plotted[i * length * 8:(i + 1) * length * 8] = o.cpm_modulate(q, np.array(hh), pf, 8)[1][length * 8 - 1:2 * length * 8 - 1]
+    t, ph = vr.phase_tree(plotted, 8, modulo=length)
+    assert ph.shape == g[f"{lab}_phases"].shape and t.size == length * 8
+    assert np.max(np.abs(ph - g[f"{lab}_phases"])) < 1e-9
+
+
+def test_psd_restatement_properties():
+    """mlab.psd restated (parity unpinned against matplotlib, which is absent): a complex tone on a bin centre
+    puts its power in that bin with the Hann leakage pattern (1, 1/4, 1/4), white noise integrates to its
+    variance x sum(w^2)/sum(w)^2 x nfft, and the bps scaling multiplies power by bps."""
+    from oracle import viz_ref as vr
+
+    nfft, n = 256, 256 * 40
+    k = np.arange(n)
+    f, p = vr.psd(np.exp(2j * np.pi * 32 / nfft * k), 8, 1, nfft)
+    pk = int(np.argmax(p))
+    assert f[pk] == pytest.approx(32 / nfft * 8) and p[pk] == pytest.approx(1.0, rel=2e-2)
+    assert p[pk - 1] == pytest.approx(p[pk] / 4, rel=5e-2) and p[pk + 1] == pytest.approx(p[pk] / 4, rel=5e-2)
+    rng = np.random.default_rng(1)
+    x = (rng.normal(size=n * 8) + 1j * rng.normal(size=n * 8)) / np.sqrt(2)
+    w = np.hanning(nfft)
+    _f, pn = vr.psd(x, 8, 1, nfft)
+    assert np.sum(pn) == pytest.approx(nfft * np.sum(w ** 2) / np.sum(w) ** 2, rel=3e-2)
+    assert np.allclose(vr.psd(x, 8, 2, nfft)[1], 2 * pn)
+    lpf = vr.kaiser_fir_lpf(8, 1.0)
+    assert abs(lpf.sum() - 1) < 1e-9 and np.allclose(lpf, lpf[::-1])

@@ -137,6 +137,8 @@ static inline int __all_sync(unsigned mk, int pred) { return __ballot_sync(mk, p
 static inline int __any_sync(unsigned mk, int pred) { return __ballot_sync(mk, pred) != 0u; }
 
 static inline float fmaxf_emu(float a, float b) { return a > b ? a : b; }
+static inline unsigned __brev(unsigned v) { unsigned r = 0; for (int i = 0; i < 32; ++i) r |= ((v >> i) & 1u) << (31 - i); return r; }
+static inline double cospi(double a) { return cos(M_PI * a); }
 static inline int __popc(unsigned v) { return __builtin_popcount(v); }
 static inline int __ffs(unsigned v) { return __builtin_ffs((int)v); }
 static inline uint32_t __umulhi(uint32_t a, uint32_t b) { return (uint32_t)(((uint64_t)a * b) >> 32); }

@@ -473,6 +473,57 @@ def t_modbank():
             assert same, (B, S, tune)
 
 
+def t_diag():
+    """csrc/diag.cu (Welch PSD, eye traces, phase tree, timing metric) vs oracle/viz_ref.py and golden G12"""
+    from oracle import viz_ref as vr
+    rng = np.random.default_rng(8)
+    g = G("g12_phase_tree.npz")
+    pulse = o.pulse_soqpsk_tg(8)
+    sy = o.fsm_encode(o.TRELLISES["SOQPSKTrellis4x2DiffEncoded"], rng.integers(0, 2, 700).astype(np.uint8))
+    s = o.cpm_modulate_closed_form(sy, 0.25, pulse, 8)
+    sig = np.ascontiguousarray(np.stack([s, s * np.exp(0.3j) + 0.05 * (rng.normal(size=s.size) + 1j * rng.normal(size=s.size))]).astype(np.complex64))
+    B, T = sig.shape
+    for nfft in (64, 1024):
+        out = np.zeros((B, nfft), np.float32)
+        ok(L.wf_welch_psd(ptr(sig), B, T, T, nfft, float(np.sqrt(2)), ptr(out), None))
+        for b in range(B):
+            _f, ref = vr.psd(sig[b].astype(np.complex128), 8, 2, nfft)
+            rel = np.max(np.abs(out[b] - ref) / (ref + 1e-9 * ref.max()))
+            assert rel < 2e-3, (nfft, b, rel)
+    span = 32
+    n_tr = (T - 1) // span
+    eye = np.zeros((B, n_tr, span + 1), np.complex64)
+    ok(L.wf_eye_traces(ptr(sig), B, n_tr * span + 1, T, span, ptr(eye), None))
+    for b in range(B):
+        _t, ref = vr.eye_traces(np.arange(T) / 8.0, sig[b], 8, 4)
+        assert np.array_equal(eye[b], ref)
+    for span, off in ((32, None), (24, 0.25), (100, None)):
+        nc = T // span
+        ph = np.zeros((B, nc, span), np.float32)
+        ok(L.wf_phase_tree(ptr(sig), B, T, T, span, int(off is not None), float(off or 0.0), ptr(ph), None))
+        for b in range(B):
+            phase = np.angle(sig[b].astype(np.complex128))
+            for c in range(nc):
+                sl = np.unwrap(phase[c * span:(c + 1) * span])
+                ref = sl - (off if off is not None else sl[0])
+                assert np.max(np.abs(ph[b, c] - ref)) < 2e-5, (span, b, c)
+    for lab, hh, pf in (("pcmfm", [0.7], o.pulse_pcmfm(8, 4)), ("multih", [4 / 16, 5 / 16], o.pulse_multih(8))):
+        syms = g[f"{lab}_symbols"]
+        length = pf.size // 8
+        plotted = np.zeros(syms.shape[0] * length * 8 + 1, np.complex64)
+        for i, q in enumerate(syms):
+            plotted[i * length * 8:(i + 1) * length * 8] = o.cpm_modulate_closed_form(q, np.array(hh), pf, 8)[length * 8 - 1:2 * length * 8 - 1]
+        nc = plotted.size // (length * 8)
+        ph = np.zeros((1, nc, length * 8), np.float32)
+        ok(L.wf_phase_tree(ptr(plotted), 1, plotted.size, plotted.size, length * 8, 0, 0.0, ptr(ph), None))
+        assert np.max(np.abs(ph[0] - g[f"{lab}_phases"])) < 1e-4, lab
+    for sps in (8, 10, 3):
+        met = np.zeros((B, sps), np.float32)
+        ok(L.wf_timing_metric(ptr(sig), B, T, T, sps, ptr(met), None))
+        for b in range(B):
+            assert np.max(np.abs(met[b] - vr.timing_metric(sig[b].astype(np.complex128), sps))) < 1e-5
+
+
 def t_cpm():
     """generic CPM detector (PCM/FM, multi-h) vs oracle/cpm_generic.py, bank + trellis"""
     from oracle.cpm_generic import CpmTrellis
@@ -562,7 +613,7 @@ def t_cpmfused():
         assert L.wf_cpm_detect_supported(0, 808, 808, ptr(bad), ptr(tim), 8, tr.first_instant, 100, M, 2, p, ptr(hn), len(hnum), 0) == 0
 
 
-TESTS = {"lfsr": t_lfsr, "prbs": t_prbs, "mod": t_mod, "modedge": t_modedge, "mf": t_mf, "vit": t_vit, "noise": t_noise, "stream": t_stream, "lean": t_lean, "rawbank": t_rawbank, "cpm": t_cpm, "cpmfused": t_cpmfused, "modbank": t_modbank}
+TESTS = {"lfsr": t_lfsr, "prbs": t_prbs, "mod": t_mod, "modedge": t_modedge, "mf": t_mf, "vit": t_vit, "noise": t_noise, "stream": t_stream, "lean": t_lean, "rawbank": t_rawbank, "cpm": t_cpm, "cpmfused": t_cpmfused, "modbank": t_modbank, "diag": t_diag}
 
 if __name__ == "__main__":
     names = sys.argv[1:] or list(TESTS)

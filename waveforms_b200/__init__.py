@@ -8,6 +8,8 @@ simulation hot path of mcdiarmid/waveforms, behind the reference's Python API:
     waveforms_b200.viterbi   SOQPSKTrellisDetector            (waveforms/viterbi)
     waveforms_b200.bert      count_errors                     (examples/soqpsk_detection.py:200-209)
     waveforms_b200.linksim   LinkSimulator: the batched chain + multi-GPU sweep
+    waveforms_b200.viz       PSD / eye / constellation / phase-tree ARRAYS (waveforms/viz, figures unavailable)
+    waveforms_b200.filters   kaiser_fir_lpf + batched FIR + sampling-phase estimate (waveforms/filters)
 
 Per-frame work runs in hand-written CUDA kernels (libwfb200.so, C ABI in
 include/wfb200.h) on torch CUDA tensors; there is no CPU fallback.
@@ -23,7 +25,8 @@ _SUBMODULES = (
     "glfsr", "glfsr.glfsr", "glfsr.pn", "cpm", "cpm.helpers", "cpm.modulate", "cpm.pamapprox", "cpm.trellis",
     "cpm.trellis.model", "cpm.trellis.encoder", "cpm.soqpsk", "cpm.soqpsk.precoder", "cpm.soqpsk.pulse_filters",
     "cpm.pcmfm", "cpm.pcmfm.precoder", "cpm.pcmfm.pulse_filters", "cpm.multih", "cpm.multih.precoder",
-    "cpm.multih.pulse_filters", "noise", "viterbi", "viterbi.algorithm", "bert", "mfbank", "linksim",
+    "cpm.multih.pulse_filters", "noise", "viterbi", "viterbi.algorithm", "bert", "mfbank", "linksim", "viz", "viz.psd", "viz.eye",
+    "viz.constellation", "viz.tree", "filters", "filters.lpf",
 )
 
 

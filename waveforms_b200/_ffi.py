@@ -47,6 +47,10 @@ PROTOTYPES = {
     "wf_cpm_detect_supported": (_i32, [_i32, _i64, _i64, _vp, _vp, _i32, _i64, _i64, _i32, _i32, _i32, _vp, _i32, _i32]),
     "wf_cpm_detect": (_i32, [_vp, _i32, _i64, _i64, _i64, _vp, _vp, _i32, _i64, _i64, _i32, _i32, _i32, _vp, _i32, _i32,
                              _vp, _vp, _i64, _i64, _i64, _vp, _vp, _i32, _vp]),
+    "wf_welch_psd": (_i32, [_vp, _i64, _i64, _i64, _i32, _dbl, _vp, _vp]),
+    "wf_eye_traces": (_i32, [_vp, _i64, _i64, _i64, _i32, _vp, _vp]),
+    "wf_phase_tree": (_i32, [_vp, _i64, _i64, _i64, _i32, _i32, _dbl, _vp, _vp]),
+    "wf_timing_metric": (_i32, [_vp, _i64, _i64, _i64, _i32, _vp, _vp]),
     "wf_bert": (_i32, [_vp, _vp, _i64, _vp, _vp, _i64, _i64, _i64, _i64, _vp, _vp, _vp]),
 }
 
