@@ -113,6 +113,26 @@ class ClockSampler:
                 "samples": len(sm), "reasons": sorted(reasons)}
 
 
+def unmodified_reference_line():
+    """VERDICT r1 #9 / BASELINE.md section 3: the UNMODIFIED reference (baseline/_ref, staged by
+    __graft_entry__.build()) timed on this box's host cores through oracle/ref_bench.py -- single process (upstream is
+    single-threaded) and multiprocessing.Pool(all cores) over independent frames; a few frames each (~0.3 s per
+    frame per core), so ~10 s in all.  Reported beside cpu_baseline (the vectorised oracle port, which is ~4x faster on
+    the same cores and therefore the conservative denominator); says "unavailable" when the package is not staged."""
+    try:
+        from oracle import ref_bench
+        if ref_bench.locate() is None:
+            return {"unavailable": "baseline/_ref not staged (run __graft_entry__.build() in the build container)"}
+        r = ref_bench.measure(frames_single=4, frames_pool_per_core=4, ebn0=EBN0_DB, detector=DETECTOR)
+        return {"kind": "reference", "unit": "bits/s", "cores": r["cores"], "cpu_model": r["cpu_model"],
+                "single_process": r["single_process"]["bits_per_s"], "pool_all_cores": r["pool_all_cores"]["bits_per_s"],
+                "sample": f"{r['single_process']['frames']} frames single-process, {r['pool_all_cores']['frames']} frames on "
+                          f"{r['cores']} processes, {N_BITS} bits each, Eb/N0 {EBN0_DB} dB, {DETECTOR} bank; the reference's own "
+                          "functions driven by the headless replay of examples/soqpsk_detection.py:45-209"}
+    except Exception as e:  # noqa: BLE001  (a baseline leg must never take the bench line down)
+        return {"unavailable": f"{type(e).__name__}: {e}"[:300]}
+
+
 def cpu_reference_line(args, as_main):
     """The reference arm / cpu_baseline leg: the oracle port of the reference's numpy chain on
     all host cores, bounded sample of the same workload."""
@@ -262,9 +282,10 @@ def main():
         return
 
     # the CPU baseline forks worker processes: take it BEFORE this process owns a CUDA context
-    cpu_line = None
+    cpu_line = ref_line = None
     if world == 1 and rank == 0 and not args.no_cpu_baseline and not args.sweep:
         cpu_line = cpu_reference_line(args, as_main=False)
+        ref_line = unmodified_reference_line()
 
     import torch
     import torch.distributed as dist
@@ -406,6 +427,8 @@ def main():
         }
         if cpu_line is not None:
             line["cpu_baseline"] = cpu_line
+        if ref_line is not None:
+            line["cpu_baseline_reference"] = ref_line
         emit(line)
     if world > 1:
         dist.barrier(device_ids=[local_rank])

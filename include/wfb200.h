@@ -272,6 +272,33 @@ WF_API int wf_cpm_detect(const void* d_rx, int dtype, int64_t B, int64_t T, int6
                          int64_t skip_head, int64_t skip_tail,
                          const int32_t* d_point, int64_t* d_counters, int tune, void* stream);
 
+/* ---- Whole-chain entry point (SURVEY 8(b) export list): one C call per batch of the SOQPSK Monte-Carlo link,
+ *      i.e. examples/soqpsk_detection.py:45-216 for B frames at once.  Equivalent, counters bit for bit, to
+ *      wf_prbs_encode -> wf_cpm_modulate_bank -> wf_viterbi_soqpsk_combined on the same arguments; the
+ *      packed bits, symbols and raw bank outputs live in ONE caller-provided workspace. ---------------- */
+typedef struct wf_link_cfg {
+  /* source: PN bits + precode (wf_prbs_encode) */
+  uint64_t mask; uint64_t init_state; uint64_t period; int32_t degree; int32_t encoder; /* WF_ENC_SOQPSK_DIFF | WF_ENC_SOQPSK */
+  int64_t n_bits;                       /* bits (= symbols) per frame */
+  /* modulator + AWGN (wf_cpm_modulate) */
+  const double* mod_index; const double* pulse; int32_t n_h; int32_t K; int32_t sps; int32_t tune;
+  double initial_phase; double derotate; uint64_t seed;
+  /* PAM bank (wf_mf_bank): taps_re HOST double[n_filt][n_taps], n_filt == 2 */
+  const double* taps_re; int32_t n_filt; int32_t n_taps; int32_t center; int32_t diff;
+  int64_t first_instant; int64_t n_calls;
+  /* detector: conj(pseudo-symbol) combine HOST double[3][n_filt] (wf_viterbi_soqpsk_combined) */
+  const double* combine_re; const double* combine_im;
+} wf_link_cfg;
+/* bytes of workspace wf_link_sim_fused needs for B frames (negative wf_status on a bad cfg) */
+WF_API int64_t wf_link_sim_workspace_bytes(const wf_link_cfg* cfg, int64_t B);
+/* d_sigma float[B], d_point int32[B] (NULL = row 0), d_frame_ids / d_bit_offsets uint64[B] (both or neither;
+ * NULL = frames first_frame + b, bits (first_frame + b) * n_bits into the stream), d_workspace 256-byte aligned
+ * device memory of at least wf_link_sim_workspace_bytes(cfg, B); adds (bit errors, symbol errors, compared bits)
+ * to d_counters int64[n_points][3].  Shapes wf_cpm_modulate_bank does not cover return WF_ERR_UNSUPPORTED. */
+WF_API int wf_link_sim_fused(const wf_link_cfg* cfg, int64_t B, uint64_t first_frame, const uint64_t* d_frame_ids,
+                             const uint64_t* d_bit_offsets, const float* d_sigma, const int32_t* d_point,
+                             void* d_workspace, int64_t workspace_bytes, int64_t* d_counters, void* stream);
+
 /* ---- signal diagnostics as CUDA reductions (the reference only plots these:
  *      waveforms/viz/*.py, matplotlib; the figures are unavailable on this box, the arrays are not) ---- */
 /* viz/psd.py:16-54 = matplotlib.mlab.psd(x * amplitude, NFFT = nfft, noverlap = 0, window = hanning,
@@ -284,9 +311,10 @@ WF_API int wf_eye_traces(const void* d_sig, int64_t B, int64_t T, int64_t ld, in
 /* viz/tree.py:64-71: d_out float[B][T/span][span] = np.unwrap(np.angle(chunk)) - (use_off ? off : chunk's first value) */
 WF_API int wf_phase_tree(const void* d_sig, int64_t B, int64_t T, int64_t ld, int span, int use_off, double off,
                          float* d_out, void* stream);
-/* replacement for the hard-coded timing offsets of examples/soqpsk_detection.py:183-192: d_out float[B][sps] =
- * mean |y[n]|^2 over n = phase (mod sps) of a full-rate matched-filter output d_y complex64[B][ld]; the best
- * sampling phase maximises it (timing_offset = -phase in the script's sign convention). */
+/* replacement for the hard-coded timing offsets of examples/soqpsk_detection.py:183-192: d_out float[B][sps],
+ * d_out[b][ph] = | mean_i (-1)^i y[ph + sps i]^2 | of a full-rate matched-filter output d_y complex64[B][ld] of an
+ * offset-QPSK-like CPM signal (y^2 alternates in sign between I and Q bits at the right sampling phase; the
+ * envelope is flat).  The best sampling phase maximises it (timing_offset = -phase in the script's convention). */
 WF_API int wf_timing_metric(const void* d_y, int64_t B, int64_t T, int64_t ld, int sps, float* d_out, void* stream);
 
 #ifdef __cplusplus

@@ -66,8 +66,14 @@ def kaiser_fir_lpf(sps, f_cutoff, width=None, ripple_db=80.0):
 
 
 def timing_metric(y, sps):
-    """mean |y[n]|^2 per sampling phase n mod sps (the build's replacement for the hard-coded timing
-    offsets of examples/soqpsk_detection.py:183-192; no reference implementation)."""
+    """|mean_i (-1)^i y[ph + sps i]^2| per sampling phase ph (the build's replacement for the hard-coded timing
+    offsets of examples/soqpsk_detection.py:183-192; no reference implementation).  For offset-QPSK-like CPM the
+    matched-filter output alternates between the I and the Q axis from bit to bit at the right sampling phase, so
+    y^2 alternates in sign there; |y|^2 itself is flat (constant envelope) and carries no timing information."""
     y = np.asarray(y)
-    return np.array([np.mean(np.abs(y[ph::sps]) ** 2) for ph in range(sps)])
-
+    out = []
+    for ph in range(sps):
+        v = y[ph::sps] ** 2
+        sign = 1.0 - 2.0 * (np.arange(v.size) & 1)
+        out.append(abs(np.sum(sign * v)) / max(v.size, 1))
+    return np.array(out)

@@ -95,8 +95,9 @@ def test_generate_cpm_phase_tree_vs_reference(lab):
 def test_kaiser_lpf_front_end_and_timing_estimate():
     """filters/lpf.py:13-34 design (identical taps), its batched application (np.convolve 'same' per frame), and
     the sampling-phase estimate that replaces the hard-coded offsets of soqpsk_detection.py:183-192: on a
-    noiseless SOQPSK-TG frame delayed by d samples the estimate moves by d, and the offset it returns for the
-    undelayed frame is one the reference's noiseless replay decodes without error (0 .. -2 for PAM)."""
+    noiseless SOQPSK-TG frame delayed by d samples the estimate moves by d, the peak of the undelayed frame is within
+    one sample of the reference's offset 0 with the reference's 0 / -1 on its shoulder, and noise at the link's
+    operating point does not move it."""
     taps = kaiser_fir_lpf(8, 1.0)
     assert np.array_equal(taps, vr.kaiser_fir_lpf(8, 1.0))
     _t, s = _tg_signal(2048, 2)
@@ -113,9 +114,19 @@ def test_kaiser_lpf_front_end_and_timing_estimate():
         delayed = torch.roll(rx, d, dims=1)
         mf = fir_filter(delayed, rho0)
         off, met = estimate_timing_offset(mf, 8)
-        assert np.allclose(met.cpu().numpy(), np.stack([vr.timing_metric(m, 8) for m in mf.cpu().numpy().astype(np.complex128)]), rtol=1e-4)
+        assert np.allclose(met.cpu().numpy(), np.stack([vr.timing_metric(m, 8) for m in mf.cpu().numpy().astype(np.complex128)]),
+                           rtol=1e-4, atol=1e-6)
         ph = (-off) % 8
         if base is None:
             base = ph
-            assert torch.all((off == 0) | (off == -1) | (off == -2)), off
+            # the peak sits within one sample of the reference's offset 0 (the 'same' convolution puts it just
+            # before n = 0), and the reference's hard-coded 0 and -1 are on its shoulder, well above the trough
+            assert torch.all((off == 0) | (off == 1)), off
+            m = met.cpu().numpy()
+            assert np.all(m[:, 0] > 0.85 * m.max(axis=1)) and np.all(m[:, 1] > 0.6 * m.max(axis=1)), m
+            assert np.all(m.min(axis=1) < 0.25 * m.max(axis=1)), m
         assert torch.all(ph == (base + d) % 8), (d, ph, base)
+    # the estimate holds at Eb/N0 = 6 dB (sigma 1.0 per component at sps 8 ... ~0 dB per sample)
+    noisy_rx = rx + torch.from_numpy((1.0 * (rng.normal(size=tuple(rx.shape)) + 1j * rng.normal(size=tuple(rx.shape)))).astype(np.complex64)).to(DEV)
+    off_n, _ = estimate_timing_offset(fir_filter(noisy_rx.contiguous(), rho0), 8)
+    assert torch.all((-off_n) % 8 == base), (off_n, base)

@@ -157,6 +157,28 @@ def test_fused_modulate_bank_shape_query():
         assert rc == -2  # WF_ERR_DEVICE
 
 
+
+def test_link_cfg_struct_and_workspace_query():
+    """struct wf_link_cfg is part of the ABI: the ctypes mirror has the C layout (static_assert in csrc/link.cu says
+    152 bytes), and wf_link_sim_workspace_bytes is pure host arithmetic (packed bits | symbols | raw bank outputs,
+    each rounded up to 256 bytes); bad configurations come back as negative wf_status with a message."""
+    lib = _ffi.lib()
+    assert ctypes.sizeof(_ffi.LinkCfg) == 152
+    one = np.ones(6)
+    cfg = _ffi.LinkCfg(mask=0x6000, init_state=32767, period=32767, degree=15, encoder=_ffi.ENC_SOQPSK_DIFF, n_bits=4096,
+                       n_filt=2, n_taps=73, center=36, n_calls=4097, sps=8, combine_re=one.ctypes.data,
+                       combine_im=one.ctypes.data)
+    up = lambda v: (v + 255) // 256 * 256  # noqa: E731
+    for B in (0, 1, 7, 4096):
+        want = up(B * 128 * 4) + up(B * 4096) + up(B * 4100 * 16)
+        assert lib.wf_link_sim_workspace_bytes(ctypes.byref(cfg), B) == want, B
+    cfg.encoder = _ffi.ENC_QUATERNARY
+    assert lib.wf_link_sim_workspace_bytes(ctypes.byref(cfg), 4) == -1 and b"SOQPSK" in lib.wf_last_error_string()
+    cfg.encoder, cfg.n_filt = _ffi.ENC_SOQPSK, 3
+    assert lib.wf_link_sim_workspace_bytes(ctypes.byref(cfg), 4) == -1 and b"PAM bank" in lib.wf_last_error_string()
+    assert lib.wf_link_sim_workspace_bytes(None, 4) == -1
+
+
 # ---- sweep arithmetic ---------------------------------------------------------------------
 def test_shard_range_partitions():
     for n in (0, 1, 7, 8, 65536, 1000003):

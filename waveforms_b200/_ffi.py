@@ -17,6 +17,20 @@ ENC_SOQPSK_DIFF, ENC_SOQPSK, ENC_BINARY, ENC_QUATERNARY, ENC_SOQPSK_TERNARY = ra
 
 _vp, _i32, _i64, _u64, _dbl = C.c_void_p, C.c_int, C.c_int64, C.c_uint64, C.c_double
 
+
+
+class LinkCfg(C.Structure):
+    """struct wf_link_cfg of include/wfb200.h (field order and types exactly as declared there)."""
+    _fields_ = [("mask", C.c_uint64), ("init_state", C.c_uint64), ("period", C.c_uint64), ("degree", C.c_int32),
+                ("encoder", C.c_int32), ("n_bits", C.c_int64),
+                ("mod_index", C.c_void_p), ("pulse", C.c_void_p), ("n_h", C.c_int32), ("K", C.c_int32),
+                ("sps", C.c_int32), ("tune", C.c_int32),
+                ("initial_phase", C.c_double), ("derotate", C.c_double), ("seed", C.c_uint64),
+                ("taps_re", C.c_void_p), ("n_filt", C.c_int32), ("n_taps", C.c_int32), ("center", C.c_int32),
+                ("diff", C.c_int32), ("first_instant", C.c_int64), ("n_calls", C.c_int64),
+                ("combine_re", C.c_void_p), ("combine_im", C.c_void_p)]
+
+
 # name -> (restype, argtypes); order and meaning exactly as in include/wfb200.h
 PROTOTYPES = {
     "wf_abi_version": (_i32, []),
@@ -52,6 +66,8 @@ PROTOTYPES = {
     "wf_phase_tree": (_i32, [_vp, _i64, _i64, _i64, _i32, _i32, _dbl, _vp, _vp]),
     "wf_timing_metric": (_i32, [_vp, _i64, _i64, _i64, _i32, _vp, _vp]),
     "wf_bert": (_i32, [_vp, _vp, _i64, _vp, _vp, _i64, _i64, _i64, _i64, _vp, _vp, _vp]),
+    "wf_link_sim_workspace_bytes": (_i64, [_vp, _i64]),
+    "wf_link_sim_fused": (_i32, [_vp, _i64, _u64, _vp, _vp, _vp, _vp, _vp, _i64, _vp, _vp]),
 }
 
 

@@ -11,7 +11,7 @@
 //   phase_tree_kernel     viz/tree.py:64-71: per chunk of `span` samples np.unwrap(np.angle(.)) minus an offset
 //                         (the chunk's first value unless `off` is given).
 //   timing_metric_kernel  a replacement for the hard-coded timing offsets of examples/soqpsk_detection.py:
-//                         183-192: mean |y[n]|^2 of a matched-filter output per sampling phase n mod sps.
+//                         183-192: |mean (-1)^i y[ph + sps i]^2| of a matched-filter output per sampling phase ph.
 #include "common.cuh"
 #include <math.h>
 
@@ -155,24 +155,34 @@ phase_tree_kernel(const float2* __restrict__ sig, int64_t B, int64_t ld, int n_c
   }
 }
 
-// mean |y[n]|^2 per sampling phase n mod sps, one block per frame; deterministic (fixed summation tree)
+// Sampling-phase metric for offset-QPSK-like CPM (SOQPSK), one block per frame:
+//   m[ph] = | (1 / cnt) sum_i (-1)^i y[ph + sps i]^2 |,   cnt = number of samples at phase ph.
+// The envelope |y|^2 of a constant-envelope signal carries no timing information; y^2 does: at the right
+// sampling phase the matched-filter output alternates between the I axis (y^2 = +1) and the Q axis (y^2 = -1)
+// from bit to bit, so the sign-alternated sum adds coherently there and the magnitude makes it independent of
+// the carrier phase.  Deterministic (fixed summation tree).
 __global__ void __launch_bounds__(256)
 timing_metric_kernel(const float2* __restrict__ y, int64_t ld, int T, int sps, float* __restrict__ out) {
-  __shared__ float red[256];
+  __shared__ float red_re[256], red_im[256];
   const int tid = threadIdx.x;
   const int G = 256 / sps;              // sample groups walked in parallel
   const int phase = tid % sps, g = tid / sps;
   const float2* row = y + (int64_t)blockIdx.x * ld;
-  float acc = 0.f;
+  float re = 0.f, im = 0.f;
   if (g < G)
-    for (int n = phase + sps * g; n < T; n += sps * G) { const float2 v = row[n]; acc = fmaf(v.x, v.x, fmaf(v.y, v.y, acc)); }
-  red[tid] = acc;
+    for (int i = g; phase + (int64_t)sps * i < T; i += G) {
+      const float2 v = row[phase + sps * i];
+      const float sq_re = fmaf(v.x, v.x, -v.y * v.y), sq_im = 2.f * v.x * v.y;
+      if (i & 1) { re -= sq_re; im -= sq_im; } else { re += sq_re; im += sq_im; }
+    }
+  red_re[tid] = re;
+  red_im[tid] = im;
   __syncthreads();
   if (tid < sps) {
-    float s = 0.f;
-    for (int k = 0; k < G; ++k) s += red[tid + k * sps];
+    float sr = 0.f, si = 0.f;
+    for (int k = 0; k < G; ++k) { sr += red_re[tid + k * sps]; si += red_im[tid + k * sps]; }
     const int cnt = (T - tid + sps - 1) / sps;
-    out[(int64_t)blockIdx.x * sps + tid] = cnt > 0 ? s / (float)cnt : 0.f;
+    out[(int64_t)blockIdx.x * sps + tid] = cnt > 0 ? sqrtf(sr * sr + si * si) / (float)cnt : 0.f;
   }
 }
 

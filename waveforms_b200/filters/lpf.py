@@ -30,15 +30,21 @@ def fir_filter(signal: torch.Tensor, taps) -> torch.Tensor:
 
 
 def estimate_timing_offset(y: torch.Tensor, sps: int):
-    """Sampling phase of a full-rate matched-filter output y complex64[B, T] (or [T]): the phase n mod sps
-    that maximises the mean |y[n]|^2 (wf_timing_metric).  Returns (timing_offset int tensor [B] in the
-    reference's sign convention -- the detector uses samples with (n + timing_offset) % sps == 0, so
-    timing_offset = -phase -- and the metric float32 [B, sps])."""
+    """Sampling phase of a full-rate matched-filter output y complex64[B, T] (or [T]) of an offset-QPSK-like
+    CPM signal (SOQPSK): the phase ph = n mod sps that maximises |mean_i (-1)^i y[ph + sps i]^2| (wf_timing_metric;
+    the envelope of a constant-envelope signal is flat, the sign alternation of y^2 between I and Q bits is not).
+    Returns (timing_offset int tensor [B], metric float32 [B, sps]).  timing_offset is in the reference's sign
+    convention -- the detector uses samples with (n + timing_offset) % sps == 0 -- as the representative of -ph
+    nearest to zero, in [-sps/2, sps/2): the hard-coded values of examples/soqpsk_detection.py:183-192 (0, -1, -2)
+    sit on the late shoulder of the same peak (the even-length 'same' convolution puts it half a sample before
+    n = 0).  A POSITIVE value means the first usable instant is sps - offset, one bit period into the frame:
+    the driver then loses the frame's first decision (skip one more in the tally)."""
     y = _dev.require_cuda(y, "y", torch.complex64)
     rows, was_1d = _dev.as_batch(y)
     B, T = rows.shape
     out = torch.empty((B, sps), dtype=torch.float32, device=rows.device)
     with torch.cuda.device(rows.device):
         _ffi.check(_ffi.lib().wf_timing_metric(_dev.ptr(rows), B, T, T, int(sps), _dev.ptr(out), _dev.stream_ptr(rows.device)))
-    off = -torch.argmax(out, dim=1)
+    ph = torch.argmax(out, dim=1)
+    off = torch.where(ph > sps // 2, sps - ph, -ph)
     return (off[0] if was_1d else off), (out[0] if was_1d else out)

@@ -14,6 +14,7 @@ number of GPUs.
 """
 from __future__ import annotations
 
+import ctypes as C
 import math
 from dataclasses import dataclass, field
 
@@ -109,6 +110,7 @@ class LinkSimulator:
                                                       int(self.first_instant), int(self.n_sym), int(self.n_calls)))
         # which fused kernel: 0 = one block per frame, 1 / 2 = one warp per frame with 64- / 128-interval chunks
         self.fused_tune = int(cfg.extra.get("fused_tune", 1))
+        self.one_call = bool(cfg.extra.get("one_call", True))  # False: three C calls instead of wf_link_sim_fused
         self.stage_names = (("prbs_encode", "modulate_awgn_bank", "viterbi_bert") if self.fused
                             else ("prbs_encode", "modulate_awgn", "mf_bank", "viterbi_bert"))
         self.max_batch = 0
@@ -155,13 +157,48 @@ class LinkSimulator:
         self.ld_words = (cfg.n_bits + 31) // 32
         self.ld_rx = (self.n_samples + 1) & ~1
         self.ld_z = (self.n_calls + 3) & ~3 if self.soqpsk else self.n_calls
+        self._ws = None
+        if self.soqpsk and self.fused:
+            # ONE workspace in the layout of wf_link_sim_fused (packed bits | symbols | raw bank outputs, each
+            # 256-byte aligned); packed / syms / z are views of it, so the one-call path (run_batch without
+            # per-kernel events) and the three-call path share the memory
+            self._link_cfg = self._make_link_cfg()
+            total = int(_ffi.lib().wf_link_sim_workspace_bytes(C.byref(self._link_cfg), max_batch))
+            if total < 0:
+                _ffi.check(total)
+            up = lambda v: (v + 255) // 256 * 256  # noqa: E731
+            n_p, n_s = max_batch * self.ld_words * 4, max_batch * self.n_sym
+            n_z = max_batch * self.ld_z * self._n_out * 8
+            o_s = up(n_p)
+            o_z = o_s + up(n_s)
+            assert o_z + up(n_z) == total, (o_z + up(n_z), total)
+            self._ws = torch.empty(max(total, 1), dtype=torch.uint8, device=dev)
+            self.packed = self._ws[:n_p].view(torch.int32).view(max_batch, self.ld_words)
+            self.syms = self._ws[o_s:o_s + n_s].view(torch.int8).view(max_batch, self.n_sym)
+            self.z = self._ws[o_z:o_z + n_z].view(cfg.dtype).view(max_batch, self.ld_z, self._n_out)
+            self.rx = None
+            return
         self.packed = torch.zeros((max_batch, self.ld_words), dtype=torch.int32, device=dev)
         self.syms = torch.empty((max_batch, self.n_sym), dtype=torch.int8, device=dev)
         self.rx = None if self.fused else torch.empty((max_batch, self.ld_rx), dtype=cfg.dtype, device=dev)
         no_z = (not self.soqpsk) and self.detect_fused
         self.z = None if no_z else torch.empty((max_batch, self.ld_z, self._n_out), dtype=cfg.dtype, device=dev)
 
+    def _make_link_cfg(self):
+        """struct wf_link_cfg for this simulator (the host tables it points to are kept alive by self)."""
+        cfg = self.cfg
+        nt = int(self._taps.shape[1])
+        return _ffi.LinkCfg(
+            mask=self.mask, init_state=self.period, period=self.period, degree=cfg.pn_degree, encoder=self.encoder,
+            n_bits=cfg.n_bits, mod_index=_dev.f64_ptr(self.h), pulse=_dev.f64_ptr(self.pulse), n_h=int(self.h.size),
+            K=int(self.pulse.size), sps=cfg.sps, tune=self.fused_tune, initial_phase=math.pi / 4, derotate=-math.pi / 4,
+            seed=cfg.seed & (2**64 - 1), taps_re=_dev.f64_ptr(self._tap_re), n_filt=int(self._taps.shape[0]), n_taps=nt,
+            center=(nt - 1) // 2, diff=int(cfg.differential), first_instant=int(self.first_instant),
+            n_calls=int(self.n_calls), combine_re=_dev.f64_ptr(self._comb_re), combine_im=_dev.f64_ptr(self._comb_im))
+
     def workspace_bytes(self) -> int:
+        if self._ws is not None:
+            return self._ws.numel()
         return sum(t.numel() * t.element_size() for t in (self.packed, self.syms, self.rx, self.z) if t is not None)
 
     # ------------------------------------------------------------------ one batch
@@ -194,6 +231,12 @@ class LinkSimulator:
                 events.append(e)
 
         with torch.cuda.device(dev):
+            if self._ws is not None and events is None and self.one_call:
+                # the whole chain in ONE C call (wf_link_sim_fused): same three kernels, same counters
+                _ffi.check(lib.wf_link_sim_fused(C.byref(self._link_cfg), B, int(first_frame), fid, boff, _dev.ptr(sigma),
+                                                 _dev.ptr(point), _dev.ptr(self._ws), self._ws.numel(), _dev.ptr(counters), st))
+                self.launches += 3
+                return
             mark()
             _ffi.check(lib.wf_prbs_encode(self.mask, cfg.pn_degree, self.period, self.period, boff, int(first_frame), B,
                                           cfg.n_bits, self.encoder, None, None, _dev.ptr(self.packed), self.ld_words,
