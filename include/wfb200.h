@@ -317,6 +317,32 @@ WF_API int wf_phase_tree(const void* d_sig, int64_t B, int64_t T, int64_t ld, in
  * envelope is flat).  The best sampling phase maximises it (timing_offset = -phase in the script's convention). */
 WF_API int wf_timing_metric(const void* d_y, int64_t B, int64_t T, int64_t ld, int sps, float* d_out, void* stream);
 
+/* ---- Allocation-free SOQPSK detection.  NO counterpart in the reference: added
+ *      for callers that cannot call cudaMalloc (code under CUDA graph capture, tight
+ *      serving loops, harnesses that forbid it). ------------------------------------------------------- */
+/* wf_soqpsk_detect_static(..) == wf_mf_bank(d_rx, WF_F32, .., combine_re, combine_im, 3, .., z, n_calls, stream)
+ * followed by wf_viterbi_soqpsk(z, WF_F32, B, n_calls, n_calls, diff, length, .., NULL, stream): same arguments,
+ * same decisions and counters bit for bit, but the intermediate z (complex64[B][n_calls][3]) lives in a
+ * file-scope device array inside the library (csrc/noalloc.cu) instead of a caller buffer, and the call
+ * performs no cudaMalloc / cudaFree / allocating library routine.
+ * LIMIT: B * n_calls <= wf_static_scratch_max_calls() = 1 398 101 (a 32 MiB array; every GPU that loads
+ * the library holds it until the process exits); larger launches return WF_ERR_ARG with a message and do
+ * nothing -- split the batch, or use the two-call form with your own buffer.
+ * All calls share the one array (per GPU) and it keeps the last call's contents: the bank overwrites every
+ * element the detector reads, so nothing needs clearing, but two calls that OVERLAP on the same GPU
+ * (different streams without a dependency, or two host threads) race on it -- serialise them.
+ * d_rx complex64[B][ld_rx]; the other arguments as in wf_mf_bank / wf_viterbi_soqpsk
+ * (combine_re[3][n_filt] required unless n_filt == 3, the pulse-truncated bank, whose outputs are used as they are). */
+WF_API int64_t wf_static_scratch_max_calls(void);
+WF_API int wf_soqpsk_detect_static(const void* d_rx, int64_t B, int64_t T, int64_t ld_rx,
+                                   const double* taps_re, const double* taps_im, int n_filt, int n_taps,
+                                   int center, const double* combine_re, const double* combine_im,
+                                   int sps, int64_t first_instant, int64_t n_calls,
+                                   int diff, int length, uint8_t* d_dec_bits, int8_t* d_dec_syms,
+                                   const uint32_t* d_tx_packed, int64_t ld_words,
+                                   const int8_t* d_tx_syms, int64_t S,
+                                   const int32_t* d_point, int64_t* d_counters, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -177,6 +177,7 @@ def test_link_cfg_struct_and_workspace_query():
     cfg.encoder, cfg.n_filt = _ffi.ENC_SOQPSK, 3
     assert lib.wf_link_sim_workspace_bytes(ctypes.byref(cfg), 4) == -1 and b"PAM bank" in lib.wf_last_error_string()
     assert lib.wf_link_sim_workspace_bytes(None, 4) == -1
+    assert lib.wf_static_scratch_max_calls() == (32 << 20) // 24
 
 
 # ---- sweep arithmetic ---------------------------------------------------------------------

@@ -25,7 +25,7 @@
 #define __launch_bounds__(...)
 #define __grid_constant__
 #define __shared__ static
-#define __align__(n) alignas(n)
+#define __align__(n) __attribute__((aligned(n)))
 #define __restrict__
 
 struct uint3e { unsigned x, y, z; };
@@ -50,6 +50,8 @@ enum { cudaSuccess = 0 };
 enum { cudaFuncAttributeMaxDynamicSharedMemorySize = 8 };
 struct cudaDeviceProp { int major, minor, multiProcessorCount; };
 static inline cudaError_t cudaGetLastError() { return 0; }
+// "device" memory is host memory in the emulator, so a __device__ symbol's address is its host address
+template <typename T> static inline cudaError_t cudaGetSymbolAddress(void** p, T& sym) { *p = (void*)&sym; return 0; }
 static inline const char* cudaGetErrorString(cudaError_t) { return "emu"; }
 static inline cudaError_t cudaGetDevice(int* d) { *d = 0; return 0; }
 static inline cudaError_t cudaGetDeviceProperties(cudaDeviceProp* p, int) { p->major = 10; p->minor = 0; p->multiProcessorCount = 4; return 0; }

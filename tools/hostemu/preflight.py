@@ -473,6 +473,72 @@ def t_modbank():
             assert same, (B, S, tune)
 
 
+def t_linkcall():
+    """wf_link_sim_fused == wf_prbs_encode + wf_cpm_modulate_bank + wf_viterbi_soqpsk_combined (counters), and
+    wf_soqpsk_detect_static == wf_mf_bank + wf_viterbi_soqpsk (decisions + counters), twice in a row"""
+    from waveforms_b200 import mfbank as _mf
+    sps, deg = 8, 15
+    pulse = o.pulse_soqpsk_tg(sps)
+    taps, comb = _mf.pam_taps(pulse, 0.25, sps)
+    taps, comb = np.asarray(taps), np.asarray(comb)
+    tr, trp = darr(taps.real.ravel())
+    cr, crp = darr(comb.real.ravel())
+    ci, cip = darr(comb.imag.ravel())
+    hv, hp = darr([0.25])
+    pv, pp = darr(pulse)
+    c = (taps.shape[1] - 1) // 2
+    mask, per = o.pn_mask(deg), (1 << deg) - 1
+    for B, N in ((5, 200), (3, 520), (4, 96)):
+        T = (N + 1) * sps
+        first, n_calls = _mf.symbol_instants(T, sps, 0, 2)
+        ld, ldw = (n_calls + 3) & ~3, (N + 31) // 32
+        sg = np.linspace(0.3, 1.2, B).astype(np.float32)
+        pts = (np.arange(B) % 2).astype(np.int32)
+        fid = (50 + 3 * np.arange(B)).astype(np.uint64)
+        boff = ((fid * N) % per).astype(np.uint64)
+        packed = np.zeros((B, ldw), np.uint32)
+        syms = np.zeros((B, N), np.int8)
+        z = np.zeros((B, ld, 2), np.complex64)
+        want = np.zeros((2, 3), np.int64)
+        ok(L.wf_prbs_encode(mask, deg, per, per, ptr(boff), 0, B, N, 0, None, None, ptr(packed), ldw, ptr(syms), None))
+        ok(L.wf_cpm_modulate_bank(ptr(syms), B, N, hp, 1, pp, pv.size, sps, np.pi / 4, -np.pi / 4, ptr(sg), ptr(pts), 9, 0, ptr(fid),
+                                  trp, 2, taps.shape[1], c, first, n_calls, ptr(z), ld, 1, None))
+        ok(L.wf_viterbi_soqpsk_combined(ptr(z), 0, B, n_calls, ld, 2, crp, cip, 1, ptr(packed), ldw, N, ptr(pts), ptr(want), None))
+        cfg = _ffi.LinkCfg(mask=mask, init_state=per, period=per, degree=deg, encoder=0, n_bits=N, mod_index=hp, pulse=pp, n_h=1,
+                           K=pv.size, sps=sps, tune=1, initial_phase=np.pi / 4, derotate=-np.pi / 4, seed=9, taps_re=trp, n_filt=2,
+                           n_taps=taps.shape[1], center=c, diff=1, first_instant=first, n_calls=n_calls, combine_re=crp,
+                           combine_im=cip)
+        need = L.wf_link_sim_workspace_bytes(C.byref(cfg), B)
+        ws = np.zeros(need + 256, np.uint8)
+        a = (-ws.ctypes.data) % 256
+        got = np.zeros((2, 3), np.int64)
+        ok(L.wf_link_sim_fused(C.byref(cfg), B, 0, ptr(fid), ptr(boff), ptr(sg), ptr(pts), C.c_void_p(ws.ctypes.data + a), need,
+                               ptr(got), None))
+        assert np.array_equal(got, want) and want[:, 2].sum() > 0, (B, N, got, want)
+        assert L.wf_link_sim_fused(C.byref(cfg), B, 0, ptr(fid), ptr(boff), ptr(sg), ptr(pts), C.c_void_p(ws.ctypes.data + a),
+                                   need - 1, ptr(got), None) == -1
+        # static-scratch detector on the noisy frames of the un-fused chain
+        ldrx = T + (T & 1)
+        rx = np.zeros((B, ldrx), np.complex64)
+        ok(L.wf_cpm_modulate(ptr(syms), B, N, hp, 1, pp, pv.size, sps, np.pi / 4, -np.pi / 4, 0, ptr(rx), ldrx, ptr(sg), ptr(pts), 9, 0,
+                             ptr(fid), None))
+        z3 = np.zeros((B, n_calls, 3), np.complex64)
+        wc, wb, wsy = np.zeros((2, 3), np.int64), np.zeros((B, n_calls), np.uint8), np.zeros((B, n_calls), np.int8)
+        ok(L.wf_mf_bank(ptr(rx), 0, B, T, ldrx, trp, None, 2, taps.shape[1], c, crp, cip, 3, sps, first, n_calls, ptr(z3), n_calls, None))
+        ok(L.wf_viterbi_soqpsk(ptr(z3), 0, B, n_calls, n_calls, 1, 2, ptr(wb), ptr(wsy), ptr(packed), ldw, ptr(syms), N, ptr(pts),
+                               ptr(wc), None, None))
+        hc, hb, hsy = np.zeros_like(wc), np.zeros_like(wb), np.zeros_like(wsy)
+        ok(L.wf_soqpsk_detect_static(ptr(rx), B, T, ldrx, trp, None, 2, taps.shape[1], c, crp, cip, sps, first, n_calls, 1, 2, ptr(hb),
+                                     ptr(hsy), ptr(packed), ldw, ptr(syms), N, ptr(pts), ptr(hc), None))
+        assert np.array_equal(hc, wc) and np.array_equal(hb, wb) and np.array_equal(hsy, wsy), (B, N, hc, wc)
+        assert np.array_equal(wc[:, [0, 2]], want[:, [0, 2]])  # and both chains count the same frames identically
+        print(f"  B={B} N={N}: one-call link counters {got.tolist()} == three calls; static-scratch detector == two calls")
+    lim = L.wf_static_scratch_max_calls()
+    assert L.wf_soqpsk_detect_static(None, lim // 100 + 1, 808, 808, trp, None, 2, taps.shape[1], c, crp, cip, sps, 0, 100, 1, 2, None,
+                                     None, None, 0, None, 0, None, None, None) == -1
+    assert b"static scratch" in L.wf_last_error_string()
+
+
 def t_diag():
     """csrc/diag.cu (Welch PSD, eye traces, phase tree, timing metric) vs oracle/viz_ref.py and golden G12"""
     from oracle import viz_ref as vr
@@ -613,7 +679,7 @@ def t_cpmfused():
         assert L.wf_cpm_detect_supported(0, 808, 808, ptr(bad), ptr(tim), 8, tr.first_instant, 100, M, 2, p, ptr(hn), len(hnum), 0) == 0
 
 
-TESTS = {"lfsr": t_lfsr, "prbs": t_prbs, "mod": t_mod, "modedge": t_modedge, "mf": t_mf, "vit": t_vit, "noise": t_noise, "stream": t_stream, "lean": t_lean, "rawbank": t_rawbank, "cpm": t_cpm, "cpmfused": t_cpmfused, "modbank": t_modbank, "diag": t_diag}
+TESTS = {"lfsr": t_lfsr, "prbs": t_prbs, "mod": t_mod, "modedge": t_modedge, "mf": t_mf, "vit": t_vit, "noise": t_noise, "stream": t_stream, "lean": t_lean, "rawbank": t_rawbank, "cpm": t_cpm, "cpmfused": t_cpmfused, "modbank": t_modbank, "diag": t_diag, "linkcall": t_linkcall}
 
 if __name__ == "__main__":
     names = sys.argv[1:] or list(TESTS)

@@ -68,6 +68,9 @@ PROTOTYPES = {
     "wf_bert": (_i32, [_vp, _vp, _i64, _vp, _vp, _i64, _i64, _i64, _i64, _vp, _vp, _vp]),
     "wf_link_sim_workspace_bytes": (_i64, [_vp, _i64]),
     "wf_link_sim_fused": (_i32, [_vp, _i64, _u64, _vp, _vp, _vp, _vp, _vp, _i64, _vp, _vp]),
+    "wf_static_scratch_max_calls": (_i64, []),
+    "wf_soqpsk_detect_static": (_i32, [_vp, _i64, _i64, _i64, _vp, _vp, _i32, _i32, _i32, _vp, _vp, _i32, _i64, _i64,
+                                       _i32, _i32, _vp, _vp, _vp, _i64, _vp, _i64, _vp, _vp, _vp]),
 }
 
 

@@ -19,7 +19,7 @@ CSRC = os.path.join(HERE, "csrc")
 OUT_DIR = os.path.join(HERE, "_lib")
 LIB = os.path.join(OUT_DIR, "libwfb200.so")
 STAMP = os.path.join(OUT_DIR, "libwfb200.stamp")
-SOURCES = ["runtime.cu", "prbs.cu", "modulate.cu", "mfbank.cu", "viterbi.cu", "bert.cu", "cpmdet.cu", "diag.cu", "link.cu"]
+SOURCES = ["runtime.cu", "prbs.cu", "modulate.cu", "mfbank.cu", "viterbi.cu", "bert.cu", "cpmdet.cu", "diag.cu", "link.cu", "noalloc.cu"]
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a",
     "-O3", "-lineinfo", "-std=c++17", "--expt-relaxed-constexpr",
