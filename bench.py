@@ -31,6 +31,7 @@ ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
 N_BITS, SPS, EBN0_DB, DETECTOR = 4096, 8, 6.0, "PAM"
+SM_COUNT = 148  # B200
 FRAMES_PER_GPU = 65536
 METRIC = "viterbi_decoded_bits_per_s_soqpsk_tg"
 # algorithmic bytes per decoded bit (complex64 = 8 B, sps = 8).  The PAM link keeps the
@@ -401,6 +402,20 @@ def main():
             return (f"profiles/traffic.json: ncu --set full, one launch at {tj['frames']} frames "
                     f"({tj.get('source', 'source?')}), scaled x{B / tj['frames']:g} to this batch")
 
+        def issue_roof(stage, ms, sm_mhz):
+            """Issue-slot roofline of an instruction-bound kernel: warp instructions per launch (ncu
+            smsp__inst_executed.sum of the same capture traffic.json comes from, scaled to this batch) over the
+            kernel's live duration, against 148 SMs x 4 schedulers x 1 warp instruction per clock at the SM clock
+            sampled during this run."""
+            tj = tj_all.get(stage)
+            if not (tj and tj.get("warp_instructions_per_launch") and sm_mhz):
+                return None
+            inst = tj["warp_instructions_per_launch"] * (B / tj["frames"])
+            peak_ips = SM_COUNT * 4 * sm_mhz * 1e6
+            return {"warp_instructions": inst, "achieved_per_s": inst / (ms * 1e-3), "peak_per_s": peak_ips,
+                    "frac": inst / (ms * 1e-3) / peak_ips, "ncu_issue_active_pct": tj.get("issue_active_pct"),
+                    "source": tj.get("source")}
+
         traffic = traffic_of(name)
         line = {
             "metric": METRIC, "value": value, "unit": "bits/s", "n_gpus": world, "steps": K, "warmup": W,
@@ -412,13 +427,15 @@ def main():
             "roofline": {"bound": "hbm", "kernel": name, "achieved": achieved, "peak": peak, "unit": "GB/s",
                          "frac": achieved / peak, "traffic": traffic, "traffic_source": traffic_src(name),
                          "peak_source": peak_src,
-                         "algorithmic_bytes_per_bit": ALGO_BYTES_PER_BIT[name], "binding_resource": BOUND[name]},
+                         "algorithmic_bytes_per_bit": ALGO_BYTES_PER_BIT[name], "binding_resource": BOUND[name],
+                         "issue": issue_roof(name, per_kernel_ms[dom], clocks.get("sm_mhz") if clocks else None)},
             "link": "fused (prbs | modulate+awgn+bank | viterbi+bert)" if sim.fused else "four kernels",
             "kernels": {KERNELS[k]: {"ms": per_kernel_ms[k],
                                      "algo_gbs": ALGO_BYTES_PER_BIT[KERNELS[k]] * B * N_BITS / (per_kernel_ms[k] * 1e-3) / 1e9,
                                      "hbm_frac": ALGO_BYTES_PER_BIT[KERNELS[k]] * B * N_BITS / (per_kernel_ms[k] * 1e-3) / 1e9 / peak,
                                      "algorithmic_bytes": ALGO_BYTES_PER_BIT[KERNELS[k]] * B * N_BITS,
                                      "traffic": traffic_of(KERNELS[k]), "bound": BOUND[KERNELS[k]],
+                                     "issue": issue_roof(KERNELS[k], per_kernel_ms[k], clocks.get("sm_mhz") if clocks else None),
                                      "share": per_kernel_ms[k] / sum(per_kernel_ms)} for k in range(NK)},
             "per_kernel_timing": "separate pass of the same K steps with CUDA events between launches (not inside the region `value` is timed over)",
             "clocks": clocks,

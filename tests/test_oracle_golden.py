@@ -311,3 +311,28 @@ def test_psd_restatement_properties():
     assert np.allclose(vr.psd(x, 8, 2, nfft)[1], 2 * pn)
     lpf = vr.kaiser_fir_lpf(8, 1.0)
     assert abs(lpf.sum() - 1) < 1e-9 and np.allclose(lpf, lpf[::-1])
+
+
+def test_oracle_link_reproduces_reference_ber_table_frames():
+    """G10's replicates record the reference's bit-error count of EVERY frame (oracle/make_ber_table.py:
+    errors_by_frame[replicate][point][frame][PT, PAM, PT@-1]).  The oracle chain fed the same PN15 frame and the same
+    PCG64(1000 * EbN0 + frame + salt) noise must reproduce those counts exactly (float64 against float64): this pins
+    oracle.soqpsk_link_frame -- modulator, both banks, detector, tally -- to the reference at the BER-table operating
+    points, frame by frame, not only in aggregate."""
+    g = golden("g10_ber_table.npz")
+    if "errors_by_frame" not in g:
+        pytest.skip("G10 carries no per-frame counts (single-replicate table)")
+    ebf, salts = g["errors_by_frame"], [int(x) for x in g["salts"] if int(x) != 0]
+    assert ebf.shape[0] == len(salts) and ebf.shape[1:] == (13, 1024, 3)
+    pulse = o.pulse_soqpsk_tg(8)
+    checked = 0
+    for rep, salt in enumerate(salts):
+        for ebn0, frame in ((0, 0), (4, 1), (4, 1023), (6, 17), (9, 500), (12, 3)):
+            bits = o.pn_frame_bits(15, frame, 4096)
+            sigma = float(np.sqrt(8 / (2 * 10 ** (ebn0 / 10))))
+            for col, det, off in ((0, "PT", 0), (1, "PAM", 0), (2, "PT", -1)):
+                rng = np.random.Generator(np.random.PCG64(seed=1000 * ebn0 + frame + salt))
+                be, _se, _n = o.soqpsk_link_frame(bits, pulse, 8, sigma, rng=rng, detector=det, timing_offset=off)
+                assert be == int(ebf[rep, ebn0, frame, col]), (salt, ebn0, frame, det, off, be, int(ebf[rep, ebn0, frame, col]))
+                checked += 1
+    assert checked == 18 * len(salts)

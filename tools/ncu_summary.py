@@ -75,6 +75,9 @@ def main():
                     tot += float(r[ix[m]]) * UNIT_SCALE[units[ix[m]]]
                 traffic[stage] = {"kernel": name.split("(")[0], "frames": a.frames, "dram_bytes_per_launch": tot,
                                   "source": f"profiles/{a.tag}_ncu_full_summary.csv (ncu --set full, one launch)"}
+                if "smsp__inst_executed.sum" in ix:  # warp instructions per launch: the issue-slot roofline's numerator
+                    traffic[stage]["warp_instructions_per_launch"] = float(r[ix["smsp__inst_executed.sum"]])
+                    traffic[stage]["issue_active_pct"] = float(r[ix["smsp__issue_active.avg.pct_of_peak_sustained_active"]])
                 break
     if not a.no_traffic:  # merge: stages this capture does not contain keep their earlier entry
         tpath = os.path.join(ROOT, "profiles", "traffic.json")

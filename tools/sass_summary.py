@@ -23,7 +23,8 @@ import subprocess
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 HOT = ("encode_frames_kernel", "cpm_modulate_f32s8_kernel", "mf_bank_f32_kernel", "viterbi_soqpsk_l2_kernel",
-       "viterbi_cpm", "cpm_detect", "cpm_modulate_bank_warp", "link_fused", "welch", "awgn_kernel<float, true>", "diag_")
+       "viterbi_cpm", "cpm_detect", "cpm_modulate_bank_warp", "welch", "phase_tree", "timing_metric", "eye_traces",
+       "awgn_kernel<float, true>")
 WATCH = ["MUFU", "FFMA2", "FFMA", "FADD2", "FMUL2", "FADD", "FMUL", "FMNMX", "FSETP", "FSEL", "SEL", "IMAD", "IADD3", "LOP3",
          "SHF", "PRMT", "POPC", "IDP", "SHFL", "REDUX", "CREDUX", "VOTE", "LDS", "STS", "LDG", "STG", "LDGSTS", "LDGDEPBAR",
          "DEPBAR", "LDC", "LDCU", "ULDC", "UMOV", "MOV", "BAR", "WARPSYNC", "BRA", "LDL", "STL", "ATOM", "RED", "I2F", "F2I",

@@ -129,7 +129,11 @@ mf_bank_kernel(const __grid_constant__ MfParams<T> p) {
   __syncthreads();
 
   // ---- R calls per thread ----------------------------------------------------------
-  constexpr int NFM = CT ? NF : 32;  // run-time shape: up to 32 filters (multi-h bank), accumulators in local memory
+  // run-time tap count: NF > 0 still fixes the filter count at compile time (accumulators in registers, real or
+  // complex taps chosen by CPLX); NF == 0 is the any-shape case: up to 32 filters (multi-h bank), accumulators in
+  // local memory
+  constexpr bool CF = !CT && NF > 0;
+  constexpr int NFM = (CT || CF) ? NF : 32;
   T yr[R][NFM], yi[R][NFM];
 #pragma unroll
   for (int e = 0; e < R; ++e)
@@ -164,6 +168,7 @@ mf_bank_kernel(const __grid_constant__ MfParams<T> p) {
     }
   } else {
     const int nv = (R - 1) * sps + nt;
+#pragma unroll 8
     for (int v = 0; v < nv; ++v) {
       const int r = v % sps, c = v / sps;
       const C x = tile[(r * R + (c % R)) * qs + tid + c / R];
@@ -172,11 +177,26 @@ mf_bank_kernel(const __grid_constant__ MfParams<T> p) {
         const int u = v - e * sps;
         if (u >= 0 && u < nt) {
           const int tt = nt - 1 - u;
-          for (int f = 0; f < nf; ++f) {
-            const T tr = p.tap_re[f * nt + tt];
-            const T ti = p.cplx_taps ? p.tap_im[f * nt + tt] : (T)0;
-            yr[e][f] = fma(x.x, tr, yr[e][f]); yr[e][f] = fma(-x.y, ti, yr[e][f]);
-            yi[e][f] = fma(x.x, ti, yi[e][f]); yi[e][f] = fma(x.y, tr, yi[e][f]);
+          if constexpr (CF) {
+#pragma unroll
+            for (int f = 0; f < NFM; ++f) {
+              const T tr = p.tap_re[f * nt + tt];
+              if (CPLX) {
+                const T ti = p.tap_im[f * nt + tt];
+                yr[e][f] = fma(x.x, tr, yr[e][f]); yr[e][f] = fma(-x.y, ti, yr[e][f]);
+                yi[e][f] = fma(x.x, ti, yi[e][f]); yi[e][f] = fma(x.y, tr, yi[e][f]);
+              } else {
+                yr[e][f] = fma(x.x, tr, yr[e][f]);
+                yi[e][f] = fma(x.y, tr, yi[e][f]);
+              }
+            }
+          } else {
+            for (int f = 0; f < nf; ++f) {
+              const T tr = p.tap_re[f * nt + tt];
+              const T ti = p.cplx_taps ? p.tap_im[f * nt + tt] : (T)0;
+              yr[e][f] = fma(x.x, tr, yr[e][f]); yr[e][f] = fma(-x.y, ti, yr[e][f]);
+              yi[e][f] = fma(x.x, ti, yi[e][f]); yi[e][f] = fma(x.y, tr, yi[e][f]);
+            }
           }
         }
       }
@@ -495,6 +515,9 @@ static int launch_mf(const void* d_rx, int64_t B, int64_t Tn, int64_t ld_rx, con
   else if (sps == 10 && n_filt == 3 && n_taps == 11 && !real_taps) WF_MF_CASE(10, 3, 11, true, 2);
   else if (sps == 8 && n_filt == 4 && n_taps == 8 && !real_taps && !comb_re) WF_MF_CASE(8, 4, 8, true, 2);    // PCM/FM, Lp = 2
   else if (sps == 8 && n_filt == 32 && n_taps == 8 && !real_taps && !comb_re) WF_MF_CASE(8, 32, 8, true, 1);  // multi-h, Lp = 2
+  // any tap count, filter count fixed: every other PAM bank (SOQPSK-B: 137 taps at sps 8, 171 at sps 10) and PT bank
+  else if (n_filt == 2 && real_taps) WF_MF_CASE(0, 2, 0, false, 2);
+  else if (n_filt == 3 && !real_taps) WF_MF_CASE(0, 3, 0, true, 2);
   else WF_MF_CASE(0, 0, 0, true, 1);
 #undef WF_MF_CASE
   WF_LAUNCH_CHECK("mf_bank_kernel");
