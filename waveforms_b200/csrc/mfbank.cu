@@ -58,7 +58,7 @@ mf_bank_kernel(const __grid_constant__ MfParams<T> p) {
   C* tile = reinterpret_cast<C*>(smem_raw);
 
   constexpr bool CT = NT > 0;
-  const int sps = CT ? SPS : p.sps;
+  const int sps = (CT || SPS > 0) ? SPS : p.sps;  // SPS > 0 with NT == 0: divisions by the sample rate become shifts / multiplies
   const int nt = CT ? NT : p.n_taps;
   const int nf = CT ? NF : p.n_filt;
   const int n_out = p.n_out;
@@ -516,6 +516,8 @@ static int launch_mf(const void* d_rx, int64_t B, int64_t Tn, int64_t ld_rx, con
   else if (sps == 8 && n_filt == 4 && n_taps == 8 && !real_taps && !comb_re) WF_MF_CASE(8, 4, 8, true, 2);    // PCM/FM, Lp = 2
   else if (sps == 8 && n_filt == 32 && n_taps == 8 && !real_taps && !comb_re) WF_MF_CASE(8, 32, 8, true, 1);  // multi-h, Lp = 2
   // any tap count, filter count fixed: every other PAM bank (SOQPSK-B: 137 taps at sps 8, 171 at sps 10) and PT bank
+  else if (sps == 8 && n_filt == 2 && real_taps) WF_MF_CASE(8, 2, 0, false, 2);
+  else if (sps == 10 && n_filt == 2 && real_taps) WF_MF_CASE(10, 2, 0, false, 2);
   else if (n_filt == 2 && real_taps) WF_MF_CASE(0, 2, 0, false, 2);
   else if (n_filt == 3 && !real_taps) WF_MF_CASE(0, 3, 0, true, 2);
   else WF_MF_CASE(0, 0, 0, true, 1);

@@ -8,9 +8,15 @@
 // Symbols whose pulse is complete contribute w_k Q[K]: that part is an exact
 // 64-bit fixed-point prefix sum in turns (wraps mod 1 turn, order independent,
 // no drift over long frames); only the J = ceil((K-1)/sps) newest symbols need
-// Q-table terms per sample.  One block per frame walks the frame in chunks of
-// 1024 symbols; threads own sample PAIRS so every store is one 128-bit word and
-// a warp store covers 512 contiguous bytes.
+// Q-table terms per sample.  Three kernels share this arithmetic:
+//   cpm_modulate_kernel<T>            any shape, float / double: one block per frame, 1024-symbol chunks (kChunkSyms),
+//                                     threads own sample PAIRS (one 128-bit store each, 512 contiguous bytes per warp).
+//   cpm_modulate_f32s8_kernel         complex64 at sps 8 (J = 8, 3, 1 or 16): whole-frame scan segments of up to 5120
+//                                     symbols, 8-interval runs per thread, FFMA2 phase sums, one Philox call per two pairs.
+//   cpm_modulate_bank_warp_kernel     the DEFAULT SOQPSK link (wf_cpm_modulate_bank, tune >= 1): one WARP per frame,
+//                                     64-interval chunks, modulator + AWGN phase and PAM-bank phase by the same lanes
+//                                     on a private shared-memory tile, no block barrier.  tune = 0 keeps
+//                                     the one-block-per-frame fused instance of cpm_modulate_f32s8_kernel (FUSE = true).
 #include "common.cuh"
 #include <math.h>
 #include <string.h>
