@@ -664,6 +664,10 @@ def test_ber_waterfall_inside_reference_confidence_intervals():
         confidence region for the reference's waterfall, and EVERY pair must fall inside its interval.  (The number
         of pairs inside the plain per-pair 95 % intervals is printed, not asserted: a perfect simulator misses
         about two of 39.)
+    (For the record: at 4 / 5 dB the table's first two replicates sit 2.7 / 2.8 and 1.2 / 2.2 replicate-sigmas BELOW the mean
+    of 24 further float64 replicates of the same frames, which agrees with this simulator to 1e-4 relative --
+    profiles/r2_ber_replicates_4_5dB.txt.  The table is kept as the reference produced it; pooling three replicates is
+    what makes its interval honest.)
     A second assert guards against a systematic offset that stays inside every interval: the mean z-score over the
     13 points of a row is N(0, 1/13) for an unbiased simulator; |mean z| < 3.5 / sqrt(13) is required."""
     from waveforms_b200.linksim import ber_confidence_interval
