@@ -255,6 +255,8 @@ __device__ __forceinline__ int warp_min_s32(int v) {
 constexpr int kBfThreads = 64;  // two autonomous warps
 constexpr int kBfCS = 1;        // steps per staged chunk: 4 CS units of 16 bytes per row (CS = 2 measured 6.0 ms at 12 warps / SM)
 constexpr int kBfPitch = 4 * kBfCS + 1;
+constexpr int kBfBufs = 3;      // staged chunks in flight: chunk c + 2 is requested while chunk c is consumed (5 KB each: with the
+                                // 16 KB decision ring, seven blocks still fit an SM, which one wave of 65 536 frames needs)
 
 struct CpmPairTaps {  // [pair][sample u][0: (c_re, c_re), 1: (c_im, c_im)] of the conj(template) of filters 0 and 1
   alignas(16) float t[2][8][2][2];
@@ -266,7 +268,7 @@ cpm_detect_m2l2_kernel(const __grid_constant__ CpmParams p, const __grid_constan
                        const __grid_constant__ CpmPairTaps tp) {
   constexpr int NS = 2 * P2, HP = P2 / 2;
   static_assert(NS <= 64 && NS > 32 && (RING & (RING - 1)) == 0, "40-state layout: one 64-bit decision word per step");
-  __align__(16) __shared__ float4 tile[2][kBfThreads * kBfPitch];
+  __align__(16) __shared__ float4 tile[kBfBufs][kBfThreads * kBfPitch];
   extern __shared__ __align__(16) unsigned char smem_raw[];
   unsigned long long* tb = reinterpret_cast<unsigned long long*>(smem_raw);  // [RING][kBfThreads]
 
@@ -280,7 +282,6 @@ cpm_detect_m2l2_kernel(const __grid_constant__ CpmParams p, const __grid_constan
   int8_t* out = (active && p.dec_syms) ? p.dec_syms + frame * p.n_steps : nullptr;
   const int cmp_lo = (int)p.skip_head, cmp_hi = min(S, n_steps) - (int)p.skip_tail;
   const bool tx_vec = tx != nullptr && ((reinterpret_cast<uintptr_t>(tx) & 3) == 0);
-
   // staging pattern: unit e = lane + 32 r (r < CS) of the warp's 32 rows x 4 CS units -> row e / (4 CS), unit e % (4 CS)
   constexpr int UPR = 4 * kBfCS;              // units per row per chunk
   constexpr int RPS = 32 / UPR;               // rows covered by one 32-lane pass
@@ -342,19 +343,26 @@ cpm_detect_m2l2_kernel(const __grid_constant__ CpmParams p, const __grid_constan
   };
 
   const int n_chunks = (n_steps + kBfCS - 1) / kBfCS;
-  if (n_chunks > 0) stage(0, 0);
+  // kBfBufs - 1 chunks ahead: with one thread per frame a batch is a single wave of ~3.5 warps per scheduler, too
+  // few to hide a DRAM round trip behind one step of arithmetic (long-scoreboard stalls 0.57 cycles per issue with
+  // one chunk ahead); every iteration commits exactly one group (empty past the end) so the wait count is constant
+#pragma unroll
+  for (int k = 0; k < kBfBufs - 1; ++k) {
+    if (k < n_chunks) stage(k, k);
+    else cp_async_commit();
+  }
   float2 carry = make_float2(0.f, 0.f);  // sample 8 i - 1 (zero before the frame)
   int released = 0;
   int next_rel = 2 * D - 1;  // the next step that ends a release block
+  int buf = 0, buf_next = kBfBufs - 1;  // c % kBfBufs and (c + kBfBufs - 1) % kBfBufs
   for (int c = 0; c < n_chunks; ++c) {
-    if (c + 1 < n_chunks) {
-      stage((c + 1) & 1, c + 1);
-      cp_async_wait<1>();
-    } else {
-      cp_async_wait<0>();
-    }
+    if (c + kBfBufs - 1 < n_chunks) stage(buf_next, c + kBfBufs - 1);
+    else cp_async_commit();
+    cp_async_wait<kBfBufs - 1>();
     __syncwarp();
-    const float4* row = &tile[c & 1][tid * kBfPitch];
+    const float4* row = &tile[buf][tid * kBfPitch];
+    buf_next = buf;
+    buf = buf + 1 == kBfBufs ? 0 : buf + 1;
 #pragma unroll
     for (int u = 0; u < kBfCS; ++u) {
       const int i = c * kBfCS + u;
@@ -428,7 +436,7 @@ cpm_detect_m2l2_kernel(const __grid_constant__ CpmParams p, const __grid_constan
         }
       }
     }
-    __syncwarp();  // all lanes are done with tile[c & 1] before chunk c + 2 is staged into it
+    __syncwarp();  // all lanes are done with this buffer before chunk c + kBfBufs is staged into it
   }
   if (p.counters) {
     // binary alphabet: bit errors = symbol errors; one atomic triple per warp when the points agree
@@ -528,7 +536,7 @@ template <int RING, int NORM>
 __global__ void __launch_bounds__(kLfWarps * 32)
 cpm_detect_lanev_kernel(const __grid_constant__ CpmParams p, const __grid_constant__ CpmRot rot,
                         const __grid_constant__ CpmLaneTaps tp) {
-  constexpr int M = 4, NHH = 2, BITS = 2;
+  constexpr int M = 4, NHH = 2;
   __align__(16) __shared__ float2 ring_s[kLfWarps][kLfRingSamples];
   __align__(16) __shared__ float4 zq_s[kLfWarps][2][2][8];    // [buffer][step of the pair][(re_x, re_x+1, im_x, im_x+1) at 2 h_new + x / 2]
   __shared__ uint8_t tb_s[kLfWarps][RING * 32];
