@@ -204,7 +204,9 @@ viterbi_soqpsk_l2_kernel(const __grid_constant__ VitParams<T> p) {
   constexpr int ROWS_PER_STEP = 32 * NPAT / ROWU;     // every NPAT r's, this many rows further on
   constexpr int STEPS = 32 / ROWS_PER_STEP;
   static_assert(ROWU == 12 || ROWU == 8, "chunk must be 12 or 8 units");
-  __align__(16) __shared__ uint4 tile[2][kL2Threads * PITCHU];
+  constexpr int NBUF = 3;  // chunk c + 2 is requested while chunk c is consumed (one wave of ~3.5 warps per scheduler
+                           // cannot hide a DRAM round trip behind one chunk of arithmetic)
+  __align__(16) __shared__ uint4 tile[NBUF][kL2Threads * PITCHU];
 
   const int lane = threadIdx.x & 31, wrow0 = threadIdx.x & ~31;
   const int64_t wframe0 = (int64_t)blockIdx.x * kL2Threads + wrow0;
@@ -273,17 +275,22 @@ viterbi_soqpsk_l2_kernel(const __grid_constant__ VitParams<T> p) {
   };
 
   const int n_chunks = (n_calls + CH - 1) / CH;
-  if (n_chunks > 0) stage(0, 0);
+  // every iteration commits exactly one group (empty past the end), so the wait count is a constant
+#pragma unroll
+  for (int k = 0; k < NBUF - 1; ++k) {
+    if (k < n_chunks) stage(k, k * CH);
+    else cp_async_commit();
+  }
+  int buf = 0, buf_next = NBUF - 1;  // c % NBUF and (c + NBUF - 1) % NBUF
   for (int c = 0; c < n_chunks; ++c) {
     const int c0 = c * CH;
-    if (c + 1 < n_chunks) {
-      stage((c + 1) & 1, c0 + CH);
-      cp_async_wait<1>();
-    } else {
-      cp_async_wait<0>();
-    }
+    if (c + NBUF - 1 < n_chunks) stage(buf_next, c0 + (NBUF - 1) * CH);
+    else cp_async_commit();
+    cp_async_wait<NBUF - 1>();
     __syncwarp();
-    const uint4* row = &tile[c & 1][threadIdx.x * PITCHU];
+    const uint4* row = &tile[buf][threadIdx.x * PITCHU];
+    buf_next = buf;
+    buf = buf + 1 == NBUF ? 0 : buf + 1;
     auto decide = [&](int i, const T* zr, const T* zi, int par) {
       const uint32_t d = par ? detector_call_l2<T, 1, DIFF>(M, zpr, zpi, zr, zi)
                              : detector_call_l2<T, 0, DIFF>(M, zpr, zpi, zr, zi);
@@ -351,7 +358,7 @@ viterbi_soqpsk_l2_kernel(const __grid_constant__ VitParams<T> p) {
       }
     }
     if (((c0 + CH) & 31) == 0) { count_group(c0 + CH - 32); decw = 0; }
-    __syncwarp();  // all lanes are done with tile[c & 1] before chunk c+2 is staged into it
+    __syncwarp();  // all lanes are done with this buffer before chunk c + NBUF is staged into it
   }
   if ((n_chunks * CH) & 31) count_group((n_chunks * CH) & ~31);  // group left open by the last chunk
 
