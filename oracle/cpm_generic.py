@@ -80,9 +80,35 @@ class CpmTrellis:
         bits = max(1, (self.M - 1).bit_length())
         return max(1, min(16, 32 // bits))
 
-    def detect(self, z, depth=None, return_margin=False):
+    def start_parity(self):
+        """Parity of the phase-state index v the detector may start from, or None when every v is reachable.
+
+        Every transition of step i moves v by K_i a with a odd, so it changes the parity of v by K_i mod 2 -- the
+        same for all branches of the step: the trellis is bipartite and at any time only the p phase states of ONE
+        parity class are reachable (the textbook count: p states for even K, 2 p for odd K, of which p at a time).
+        The frame starts with no symbols in the air, i.e. v = 0 once the Lp - 1 phantom symbols of the first steps
+        have left the window; walking those steps backwards gives the parity class at the start."""
+        if all(k % 2 == 0 for k in self.h_num):
+            return None                      # even K only: parity never changes; odd v are the same dead class forever
+        par = 0
+        for i in range(self.Lp - 2, -1, -1):  # steps whose leaving symbol index i - Lp + 1 is negative (phantom)
+            par = (par - self.h_num[(i - self.Lp + 1) % self.n_h]) % 2
+        return par
+
+    def live_parity(self, i):
+        """Parity class of v AFTER step i (start_parity() propagated through steps 0..i)."""
+        par = self.start_parity()
+        if par is None:
+            return None
+        for j in range(i + 1):
+            par = (par + self.h_num[(j - self.Lp + 1) % self.n_h]) % 2
+        return par
+
+    def detect(self, z, depth=None, return_margin=False, reachable=True):
         """Viterbi detection maximising sum Re{e^{-j pi v/p} z}.  z complex[n_steps, n_h*n_filt].
-        Returns symbol INDICES (0..M-1) uint8[n_steps].  All states start equal (unknown start).
+        Returns symbol INDICES (0..M-1) uint8[n_steps].  The history part of the start state is unknown (all equal);
+        the phase part starts in the reachable parity class (``reachable``: states of the other class start at
+        -inf and stay there -- see start_parity; False = all 2 p phase states start equal, the round-1 rule).
 
         Decision rule -- BLOCK RELEASE with survivor memory 2 D (D = ``depth``, default min(16, 32 / log2 M)):
         the add-compare-select of every step stores, per state, which predecessor won; whenever
@@ -101,6 +127,9 @@ class CpmTrellis:
         n_steps = z.shape[0]
         NS, NH = self.n_states, self.n_hist
         pm = np.zeros(NS)
+        sp0 = self.start_parity() if reachable else None
+        if sp0 is not None:
+            pm[(np.arange(NS) // NH) % 2 != sp0] = -np.inf
         rot = np.exp(-1j * np.pi * np.arange(p2) / self.p)
         out = np.zeros(n_steps, dtype=np.uint8)
         marg = np.zeros((n_steps, 2))
@@ -137,7 +166,7 @@ class CpmTrellis:
                 cand = pm[pred] + np.real(rot[vpred] * zi[f])
                 take = cand > best               # strict: the lowest x wins ties
                 second = np.where(take, best, np.maximum(second, cand))
-                amax = max(amax, float(np.max(np.abs(cand))))
+                amax = max(amax, float(np.max(np.abs(cand[np.isfinite(cand)]))) if np.any(np.isfinite(cand)) else 0.0)
                 best = np.where(take, cand, best)
                 arg = np.where(take, pred, arg)
                 argx = np.where(take, x, argx)
@@ -145,8 +174,11 @@ class CpmTrellis:
             sym_of[i] = argx if Lp == 1 else hnew // (NH // M)   # symbol index of step i
             pm = best - best.max()
             if return_margin:
-                top = np.sort(best)
-                marg[i] = (min(float(np.min(best - second)), float(top[-1] - top[-2])), amax)
+                live = np.isfinite(best)
+                top = np.sort(best[live])
+                gaps = best[live] - second[live]          # second = -inf where a live state has one live candidate only
+                gaps = gaps[np.isfinite(gaps)]
+                marg[i] = (min(float(np.min(gaps)) if gaps.size else np.inf, float(top[-1] - top[-2])), amax)
             if (i + 1) % D == 0 and i + 1 >= 2 * D:
                 release(i, i + 1 - D)
                 released = i + 1 - D

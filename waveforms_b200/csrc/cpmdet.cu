@@ -44,6 +44,7 @@ struct CpmParams {
   unsigned long long* counters;
   int64_t B, n_steps, ld_z, S, skip_head, skip_tail, Tn, ld_rx;
   int M, Lp, p, n_h, depth, bits, n_filt, n_hist, n_states, n_cols;
+  int start_parity;  // parity class of the phase-state index v the detector starts from (oracle/cpm_generic.py:start_parity); -1 = every v
   int delta[kCpmMaxH][16];  // (K_h * alphabet[x]) mod 2p
 };
 
@@ -83,7 +84,11 @@ viterbi_cpm_kernel(const __grid_constant__ CpmParams p) {
 
   T* pm[2] = {pm_s[wid][0], pm_s[wid][1]};
   unsigned long long* hs[2] = {hist_s[wid][0], hist_s[wid][1]};
-  for (int s = lane; s < NS; s += 32) { pm[0][s] = (T)0; hs[0][s] = 0ull; }
+  for (int s = lane; s < NS; s += 32) {
+    const bool dead = p.start_parity >= 0 && (((s / NH) & 1) != p.start_parity);
+    pm[0][s] = dead ? (sizeof(T) == 4 ? (T)-3.0e38f : (T)-1e300) : (T)0;  // absorbs every finite increment: stays dead
+    hs[0][s] = 0ull;
+  }
   __syncwarp();
 
   unsigned long long sym_err = 0, bit_err = 0, compared = 0;
@@ -267,10 +272,11 @@ __global__ void __launch_bounds__(kBfThreads)
 cpm_detect_m2l2_kernel(const __grid_constant__ CpmParams p, const __grid_constant__ CpmRot rot,
                        const __grid_constant__ CpmPairTaps tp) {
   constexpr int NS = 2 * P2, HP = P2 / 2;
-  static_assert(NS <= 64 && NS > 32 && (RING & (RING - 1)) == 0, "40-state layout: one 64-bit decision word per step");
+  static_assert(P2 <= 32 && (P2 % 4) == 0 && (D0 & 1) && (D1 & 1) && (RING & (RING - 1)) == 0,
+                "both phase steps odd: the P2 states of one parity class of v are live at a time, one 32-bit decision word per step");
   __align__(16) __shared__ float4 tile[kBfBufs][kBfThreads * kBfPitch];
   extern __shared__ __align__(16) unsigned char smem_raw[];
-  unsigned long long* tb = reinterpret_cast<unsigned long long*>(smem_raw);  // [RING][kBfThreads]
+  uint32_t* tb = reinterpret_cast<uint32_t*>(smem_raw);  // [RING][kBfThreads]: one decision bit per LIVE state (P2 of them) per step
 
   const int tid = threadIdx.x, lane = tid & 31, wrow0 = tid & ~31;
   const int64_t wframe0 = (int64_t)blockIdx.x * kBfThreads + wrow0;
@@ -301,7 +307,8 @@ cpm_detect_m2l2_kernel(const __grid_constant__ CpmParams p, const __grid_constan
 
   float pm[NS];
 #pragma unroll
-  for (int s = 0; s < NS; ++s) pm[s] = 0.f;
+  for (int s = 0; s < NS; ++s) pm[s] = 0.f;  // step 0 reads the start class only; the other half is written before it is read
+  const int start_par = p.start_parity;      // 0 or 1 here (odd phase steps)
   unsigned sym_err = 0, compared = 0;
   const float2* tap2 = reinterpret_cast<const float2*>(tp.t);
 
@@ -309,8 +316,9 @@ cpm_detect_m2l2_kernel(const __grid_constant__ CpmParams p, const __grid_constan
   auto trace_release = [&](int t, int s, int lo, int hi) {
     unsigned long long bitsw = 0ull;  // bit (tau - lo) = decided symbol index of step tau
     for (int tau = t; tau >= lo; --tau) {
-      const unsigned long long w = tb[(tau & (RING - 1)) * kBfThreads + tid];
-      const unsigned b = (unsigned)(w >> (s < 32 ? 31 - s : 71 - s)) & 1u;  // which predecessor won
+      const uint32_t w = tb[(tau & (RING - 1)) * kBfThreads + tid];
+      const int j = ((s >> 2) << 1) | (s & 1);                 // rank of s = 4 m + 2 Q + h among the live states of its step
+      const unsigned b = (w >> (P2 - 1 - j)) & 1u;             // which predecessor won
       if (tau < hi) bitsw |= (unsigned long long)(s & 1) << (tau - lo);
       int vp = (s >> 1) - (b ? D1 : D0);
       vp += vp < 0 ? P2 : 0;
@@ -388,52 +396,60 @@ cpm_detect_m2l2_kernel(const __grid_constant__ CpmParams p, const __grid_constan
           zx[pr] = ac.x - eb.y; zy[pr] = eb.x + ac.y;          // filter pr
           zx[3 - pr] = ac.x + eb.y; zy[3 - pr] = ac.y - eb.x;  // its conjugate partner
         }
-        // ---- Re{e^{-j pi k/p} z_f}, k < p (the other half of the circle is the negative) ---------
-        float r[HP][4];
+        // ---- the step proper, for the parity class Q of the phase states it ENDS in -----------------
+        // Both phase steps are odd, so every branch flips the parity of v: the states of class Q are written
+        // from the states of class 1 - Q, IN PLACE (the two halves of pm[] alternate as source and destination),
+        // and only the P2 / 2 rotations Re{e^{-j pi k/p} z_f} of the predecessor class are formed.
+        auto step = [&](auto qc) {
+          constexpr int Q = decltype(qc)::value;
+          float r[HP][4];
 #pragma unroll
-        for (int k = 0; k < HP; ++k)
+          for (int k = 0; k < HP; ++k)
+            if ((k & 1) != Q) {  // k = vp mod HP has the parity of vp (HP is even): predecessor class 1 - Q
 #pragma unroll
-          for (int f = 0; f < 4; ++f)
-            r[k][f] = k == 0 ? zx[f] : ((2 * k == HP) ? zy[f] : rot.c[k] * zx[f] + rot.s[k] * zy[f]);
-        // ---- add-compare-select: one decision bit per state -------------------------------------
-        float pn[NS];
-        uint32_t w0 = 0, w1 = 0;
-#pragma unroll
-        for (int s = 0; s < NS; ++s) {
-          const int vnew = s >> 1, hnew = s & 1;
-          const int vp0 = (vnew - D0 + 2 * P2) % P2, vp1 = (vnew - D1 + 2 * P2) % P2;
-          const int f0 = hnew * 2, f1 = hnew * 2 + 1;
-          const float c0 = vp0 < HP ? pm[2 * vp0] + r[vp0 % HP][f0] : pm[2 * vp0] - r[vp0 % HP][f0];
-          const float c1 = vp1 < HP ? pm[2 * vp1 + 1] + r[vp1 % HP][f1] : pm[2 * vp1 + 1] - r[vp1 % HP][f1];
-          const float d = c0 - c1;  // negative <=> c1 > c0: strict, so the lower x keeps ties
-          pn[s] = fmaxf(c0, c1);
-          if (s < 32) w0 = funnel_l1(w0, __float_as_uint(d));
-          else w1 = funnel_l1(w1, __float_as_uint(d));
-        }
-        tb[(i & (RING - 1)) * kBfThreads + tid] = (unsigned long long)w0 | ((unsigned long long)w1 << 32);
-        const bool blk = i == next_rel;
-        const bool rel = blk || i == n_steps - 1;
-        if (rel || NORM == 1 || (i & (NORM - 1)) == NORM - 1) {
-          float wmax = pn[0];
-#pragma unroll
-          for (int s = 1; s < NS; ++s) wmax = fmaxf(wmax, pn[s]);
-          if (rel) {
-            int best_s = NS - 1;
-#pragma unroll
-            for (int s = NS - 2; s >= 0; --s) best_s = (pn[s] == wmax) ? s : best_s;  // lowest index wins
-            if (blk) {
-              trace_release(i, best_s, released, i + 1 - D);
-              released = i + 1 - D;
-              next_rel += D;
+              for (int f = 0; f < 4; ++f)
+                r[k][f] = k == 0 ? zx[f] : ((2 * k == HP) ? zy[f] : rot.c[k] * zx[f] + rot.s[k] * zy[f]);
             }
-            if (i == n_steps - 1) trace_release(i, best_s, released, n_steps);
+          uint32_t w = 0;
+          float wmax = -3.0e38f;
+#pragma unroll
+          for (int s = 0; s < NS; ++s) {
+            const int vnew = s >> 1, hnew = s & 1;
+            if ((vnew & 1) == Q) {
+              const int vp0 = (vnew - D0 + 2 * P2) % P2, vp1 = (vnew - D1 + 2 * P2) % P2;
+              const int f0 = hnew * 2, f1 = hnew * 2 + 1;
+              const float c0 = vp0 < HP ? pm[2 * vp0] + r[vp0 % HP][f0] : pm[2 * vp0] - r[vp0 % HP][f0];
+              const float c1 = vp1 < HP ? pm[2 * vp1 + 1] + r[vp1 % HP][f1] : pm[2 * vp1 + 1] - r[vp1 % HP][f1];
+              const float d = c0 - c1;  // negative <=> c1 > c0: strict, so the lower x keeps ties
+              pm[s] = fmaxf(c0, c1);
+              wmax = fmaxf(wmax, pm[s]);
+              w = funnel_l1(w, __float_as_uint(d));  // live states in increasing s: rank j ends at bit P2 - 1 - j
+            }
           }
+          tb[(i & (RING - 1)) * kBfThreads + tid] = w;
+          const bool blk = i == next_rel;
+          const bool rel = blk || i == n_steps - 1;
+          if (rel || NORM == 1 || (i & (NORM - 1)) == NORM - 1) {
+            if (rel) {
+              int best_s = -1;
 #pragma unroll
-          for (int s = 0; s < NS; ++s) pm[s] = pn[s] - wmax;
-        } else {
+              for (int s = NS - 1; s >= 0; --s)
+                if (((s >> 1) & 1) == Q) best_s = (pm[s] == wmax || best_s < 0) ? s : best_s;  // lowest live index wins
+              if (blk) {
+                trace_release(i, best_s, released, i + 1 - D);
+                released = i + 1 - D;
+                next_rel += D;
+              }
+              if (i == n_steps - 1) trace_release(i, best_s, released, n_steps);
+            }
 #pragma unroll
-          for (int s = 0; s < NS; ++s) pm[s] = pn[s];
-        }
+            for (int s = 0; s < NS; ++s)
+              if (((s >> 1) & 1) == Q) pm[s] -= wmax;
+          }
+        };
+        // class after step i: the start class flipped i + 1 times
+        if ((start_par + i + 1) & 1) step(std::integral_constant<int, 1>{});
+        else step(std::integral_constant<int, 0>{});
       }
     }
     __syncwarp();  // all lanes are done with this buffer before chunk c + kBfBufs is staged into it
@@ -599,7 +615,7 @@ cpm_detect_lanev_kernel(const __grid_constant__ CpmParams p, const __grid_consta
 
   float pm[M];
 #pragma unroll
-  for (int h = 0; h < M; ++h) pm[h] = 0.f;
+  for (int h = 0; h < M; ++h) pm[h] = (p.start_parity >= 0 && ((lane & 1) != p.start_parity)) ? -3.0e38f : 0.f;
   unsigned sym_err = 0, bit_err = 0, compared = 0;  // per lane, reduced at the end
 
   // chunk c = samples [64 c - 8, 64 c + 56) -> ring slots (64 c + j) & 255; lane l moves unit l
@@ -763,6 +779,22 @@ static int fill_cpm_params(CpmParams& q, int M, int Lp, int p, const int32_t* h_
       if (d < 0) d += 2 * p;
       q.delta[h][x] = d;
     }
+  // Every branch of a step moves v by K a with a odd, i.e. flips the parity of v iff K is odd: the trellis is
+  // bipartite and only one parity class of phase states is reachable at a time.  The frame starts with no symbol in
+  // the air (v = 0 once the Lp - 1 phantom symbols have left the window); walking those steps backwards gives the
+  // class at the start.  States of the other class start at -BIG and never recover (oracle/cpm_generic.py).
+  bool any_odd = false;
+  for (int h = 0; h < n_h; ++h) any_odd |= (h_num[h] & 1) != 0;
+  q.start_parity = -1;
+  if (any_odd) {
+    int par = 0;
+    for (int i = Lp - 2; i >= 0; --i) {
+      int idx = (i - Lp + 1) % n_h;
+      if (idx < 0) idx += n_h;
+      par = (par + (h_num[idx] & 1)) & 1;  // minus = plus, mod 2
+    }
+    q.start_parity = par;
+  }
   return WF_OK;
 }
 
@@ -871,7 +903,7 @@ extern "C" int wf_cpm_detect(const void* d_rx, int dtype, int64_t B, int64_t T, 
     const unsigned g = (unsigned)((B + kBfThreads - 1) / kBfThreads);
 #define WF_BF_LAUNCH(RING_, NORM_)                                                                            \
   do {                                                                                                        \
-    const size_t sm = (size_t)RING_ * kBfThreads * sizeof(unsigned long long);                                \
+    const size_t sm = (size_t)RING_ * kBfThreads * sizeof(uint32_t);                                          \
     auto kfn = cpm_detect_m2l2_kernel<20, 13, 7, RING_, NORM_>;                                               \
     cudaError_t e = cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm);          \
     if (e != cudaSuccess) return cuda_fail(e, "cudaFuncSetAttribute(cpm_detect_m2l2_kernel)");                \
