@@ -514,8 +514,10 @@ static __device__ __noinline__ uint3 lanev_trace_release(const uint8_t* tb, uint
   unsigned long long w0 = 0ull, w1 = 0ull;  // 2 bits per released symbol, symbol lo in the lowest bits of w0
   int hn2 = 2 * hn;
   auto back = [&](int tau) {
-    const unsigned b = tb[((tau & (RING - 1)) << 5) + v];
-    const unsigned x = (b >> hn2) & 3u;
+    // the byte of lane 2 m + (hn >> 1), m = (v - class) / 2, class = live parity after step tau = (tau & 3) >> 1
+    const int li = ((v - ((tau & 3) >> 1)) & 30) | (hn2 >> 2);
+    const unsigned b = tb[((tau & (RING - 1)) << 5) + li];
+    const unsigned x = (b >> (hn2 & 2)) & 3u;
     const uint32_t dl = (tau & 1) ? dl0 : dl1;  // transition parity (tau - Lp + 1) % 2 = (tau + 1) & 1
 #ifdef WF_HOSTEMU
     const uint32_t dv = (dl >> (8 * x)) & 0xFFu;
@@ -569,33 +571,27 @@ cpm_detect_lanev_kernel(const __grid_constant__ CpmParams p, const __grid_consta
   float2* ring = ring_s[wid];
   uint8_t* tb = tb_s[wid];
 
-  // per-lane transition tables for each modulation-index parity, as register PAIRS (x, x + 1)
-  int src[NHH][M];
-  float2 rc2[NHH][M / 2], rs2[NHH][M / 2];
+  // Reachable states only.  h = {even, odd} / p: the parity class of the phase-state index v flips on the
+  // odd-K transitions, i.e. after step i the live class is LA(i) = (i & 3) >> 1 (start class 1), 16 phase states x 4
+  // histories = 64 of the 128 states.  Lane = 2 m + hh owns v = 2 m + LA and the two histories h_new = 2 hh, 2 hh + 1.
+  // The predecessor of (v, h_new) through oldest symbol x is (v - delta[lp][x], x), held by lane
+  //   (lane & ~1) + (LA - LB) - delta[lp][x] + (x >> 1)   (mod 32; LB = class before the step)
+  // in its register pm[x & 1]: four shuffles per step, sources = one lane-constant plus uniform integers.
+  // The rotation e^{-j pi v_pred / p} splits into a lane part e^{-j pi 2 m / p} (cm, sm below) and a uniform part
+  // e^{-j pi (LA - delta[lp][x]) / p} that the BANK lanes fold into z before they hand it over.
+  const int base_lane = lane & ~1, hh = lane & 1;
+  const float cm = rot.c[base_lane], sm = rot.s[base_lane];     // cos / sin(pi 2 m / p)
+  float2 cm2 = make_float2(cm, cm), sm2 = make_float2(sm, sm);
+  int nd[NHH][M];                                               // -delta[lp][x] + (x >> 1), uniform
 #pragma unroll
   for (int h = 0; h < NHH; ++h)
 #pragma unroll
-    for (int x = 0; x < M; ++x) {
-      src[h][x] = lane - p.delta[h][x];  // SHFL.IDX uses the source lane modulo 32: no mask needed
-      const float c = rot.c[src[h][x] & 31], s = rot.s[src[h][x] & 31];
-      if (x & 1) { rc2[h][x / 2].y = c; rs2[h][x / 2].y = s; }
-      else { rc2[h][x / 2].x = c; rs2[h][x / 2].x = s; }
-    }
+    for (int x = 0; x < M; ++x) nd[h][x] = (x >> 1) - p.delta[h][x];
   // phase steps of both parities packed one per byte: the traceback picks byte x with one PRMT
   const uint32_t dl0 = (uint32_t)p.delta[0][0] | ((uint32_t)p.delta[0][1] << 8) | ((uint32_t)p.delta[0][2] << 16) | ((uint32_t)p.delta[0][3] << 24);
   const uint32_t dl1 = (uint32_t)p.delta[1][0] | ((uint32_t)p.delta[1][1] << 8) | ((uint32_t)p.delta[1][2] << 16) | ((uint32_t)p.delta[1][3] << 24);
 #ifndef WF_HOSTEMU
-  // pin the values in registers: left alone, the compiler re-reads rot.c[src] in the loop, a
-  // lane-divergent constant-bank access that serialises 32 ways
-#pragma unroll
-  for (int h = 0; h < NHH; ++h)
-#pragma unroll
-    for (int j = 0; j < M / 2; ++j)
-      asm volatile("" : "+f"(rc2[h][j].x), "+f"(rc2[h][j].y), "+f"(rs2[h][j].x), "+f"(rs2[h][j].y));
-#pragma unroll
-  for (int h = 0; h < NHH; ++h)
-#pragma unroll
-    for (int x = 0; x < M; ++x) asm volatile("" : "+r"(src[h][x]));
+  asm volatile("" : "+f"(cm2.x), "+f"(cm2.y), "+f"(sm2.x), "+f"(sm2.y));  // keep them in registers (see CpmRot)
 #endif
   // bank role of this lane: it serves the step of ITS parity (steps come in pairs (even, odd)), filter pair q,
   // and accumulates either (A, C) (which = 0, taps c_re) or (E, B) (which = 1, taps c_im) over all 8 samples
@@ -612,10 +608,20 @@ cpm_detect_lanev_kernel(const __grid_constant__ CpmParams p, const __grid_consta
 #endif
   const int bf = bwhich ? 15 - bq : bq;              // the filter this lane finishes
   const int zword = 32 * bstep + 4 * (bf >> 1) + (bf & 1);  // its re slot inside a buffer (floats); im is two words further on
-
-  float pm[M];
+  // uniform part of the rotation for the filter this lane finishes (oldest symbol x = bf & 3) at its steps
+  // u = 2 up + bstep: transition parity lp = (bstep + 1) & 1, class after the step LA = up & 1
+  float zrc[2], zrs[2];
 #pragma unroll
-  for (int h = 0; h < M; ++h) pm[h] = (p.start_parity >= 0 && ((lane & 1) != p.start_parity)) ? -3.0e38f : 0.f;
+  for (int a = 0; a < 2; ++a) {
+    const int n = (a - p.delta[(bstep + 1) & 1][bf & 3]) & 31;
+    zrc[a] = rot.c[n];
+    zrs[a] = -rot.s[n];  // e^{-j pi n / p} = cos - j sin
+  }
+#ifndef WF_HOSTEMU
+  asm volatile("" : "+f"(zrc[0]), "+f"(zrc[1]), "+f"(zrs[0]), "+f"(zrs[1]));
+#endif
+
+  float pm[2] = {0.f, 0.f};  // histories 2 hh, 2 hh + 1 of this lane's live phase state (every live state starts equal)
   unsigned sym_err = 0, bit_err = 0, compared = 0;  // per lane, reduced at the end
 
   // chunk c = samples [64 c - 8, 64 c + 56) -> ring slots (64 c + j) & 255; lane l moves unit l
@@ -671,8 +677,10 @@ cpm_detect_lanev_kernel(const __grid_constant__ CpmParams p, const __grid_consta
         const float2 acc = fadd2(a0, a1);
         const float ox = __shfl_xor_sync(0xFFFFFFFFu, acc.x, 1), oy = __shfl_xor_sync(0xFFFFFFFFu, acc.y, 1);
         // which = 0: own (A, C), other (E, B) -> z_q = (A - B, E + C);  which = 1: own (E, B), other (A, C) -> z_{15-q} = (A + B, C - E)
-        const float zr = bwhich ? ox + acc.y : acc.x - oy;
-        const float zi = bwhich ? oy - acc.x : ox + acc.y;
+        const float zr0 = bwhich ? ox + acc.y : acc.x - oy;
+        const float zi0 = bwhich ? oy - acc.x : ox + acc.y;
+        const float zr = fmaf(-zi0, zrs[up & 1], zr0 * zrc[up & 1]);   // z e^{-j pi (LA - delta) / p}
+        const float zi = fmaf(zi0, zrc[up & 1], zr0 * zrs[up & 1]);
         float* zs = reinterpret_cast<float*>(zq_s[wid][up & 1]);  // double buffered: the readers of this buffer are two pairs back
         zs[zword] = zr;
         zs[zword + 2] = zi;
@@ -685,23 +693,24 @@ cpm_detect_lanev_kernel(const __grid_constant__ CpmParams p, const __grid_consta
         if (i >= n_steps) break;
         const int lp = (us + 1) & 1;      // transition parity (i - 1) % 2  (i0 is a multiple of 8: i % 2 = us)
         const float4* zq = zq_s[wid][up & 1][us];
-        // ---- add-compare-select ----------------------------------------------------------------------
+        // ---- add-compare-select over the live class --------------------------------------------------
+        const int LA = (u & 3) >> 1, LB = ((u + 3) & 3) >> 1;  // class after / before step i (i0 is a multiple of 8; folded by the unroll)
         float2 pmx2[M / 2];
 #pragma unroll
         for (int j = 0; j < M / 2; ++j) {
-          pmx2[j].x = __shfl_sync(0xFFFFFFFFu, pm[2 * j], src[lp][2 * j]);
-          pmx2[j].y = __shfl_sync(0xFFFFFFFFu, pm[2 * j + 1], src[lp][2 * j + 1]);
+          pmx2[j].x = __shfl_sync(0xFFFFFFFFu, pm[0], base_lane + nd[lp][2 * j] + (LA - LB));
+          pmx2[j].y = __shfl_sync(0xFFFFFFFFu, pm[1], base_lane + nd[lp][2 * j + 1] + (LA - LB));
         }
         unsigned dec = 0;
         float lmax = -3.0e38f;
 #pragma unroll
-        for (int hn = 0; hn < M; ++hn) {
+        for (int k = 0; k < 2; ++k) {  // h_new = 2 hh + k
           float2 c2[M / 2];
 #pragma unroll
           for (int j = 0; j < M / 2; ++j) {
-            const float4 q = zq[2 * hn + j];
-            float2 t2 = fmul2(rc2[lp][j], make_float2(q.x, q.y));
-            t2 = ffma2(rs2[lp][j], make_float2(q.z, q.w), t2);
+            const float4 q = zq[4 * hh + 2 * k + j];
+            float2 t2 = fmul2(cm2, make_float2(q.x, q.y));
+            t2 = ffma2(sm2, make_float2(q.z, q.w), t2);
             c2[j] = fadd2(pmx2[j], t2);
           }
           // strict '>' tournament: the lowest x keeps ties
@@ -710,8 +719,8 @@ cpm_detect_lanev_kernel(const __grid_constant__ CpmParams p, const __grid_consta
           const bool bf2 = m23 > m01;
           const float best = fmaxf(m01, m23);
           const unsigned idx = bf2 ? (2u | (b23 ? 1u : 0u)) : (b01 ? 1u : 0u);
-          dec |= idx << (2 * hn);
-          pm[hn] = best;
+          dec |= idx << (2 * k);
+          pm[k] = best;
           lmax = fmaxf(lmax, best);
         }
         tb[((i & (RING - 1)) << 5) + lane] = (uint8_t)dec;
@@ -722,8 +731,8 @@ cpm_detect_lanev_kernel(const __grid_constant__ CpmParams p, const __grid_consta
           if (rel) {
             int best_s = 0x7FFFFFFF;  // lowest state index v M + h with the maximum metric
 #pragma unroll
-            for (int hn = M - 1; hn >= 0; --hn)
-              if (pm[hn] == wmax) best_s = lane * M + hn;
+            for (int k = 1; k >= 0; --k)
+              if (pm[k] == wmax) best_s = (base_lane + LA) * M + 2 * hh + k;
             const int wbest = warp_min_s32(best_s);
             __syncwarp();  // this step's decision bytes are visible to the whole warp
             if (blk) {
@@ -733,8 +742,8 @@ cpm_detect_lanev_kernel(const __grid_constant__ CpmParams p, const __grid_consta
             }
             if (i == n_steps - 1) trace_release(i, wbest >> 2, wbest & 3, released, n_steps);
           }
-#pragma unroll
-          for (int hn = 0; hn < M; ++hn) pm[hn] -= wmax;
+          pm[0] -= wmax;
+          pm[1] -= wmax;
         }
       }
     }
@@ -823,7 +832,10 @@ static int fused_kind(int dtype, int64_t Tn, int64_t ld_rx, const double* tre, c
   if (q.M == 2 && q.n_h == 1 && q.p == 10 && q.delta[0][0] == 13 && q.delta[0][1] == 7 && q.depth <= 32 &&
       8 * n_steps <= Tn && 8 * ((n_steps + kBfCS - 1) / kBfCS) * kBfCS <= ld_rx)  // whole chunks are staged
     return 1;
-  if (q.M == 4 && q.n_h == 2 && q.p == 16 && q.depth <= 32) return 2;
+  // the lane layout is built on the class pattern of h = {even, odd} / 16 (ARTM: 4/16, 5/16): start class 1, flips on even steps
+  if (q.M == 4 && q.n_h == 2 && q.p == 16 && q.depth <= 32 && (q.delta[0][0] & 1) == 0 && (q.delta[1][0] & 1) == 1 &&
+      q.start_parity == 1)
+    return 2;
   return 0;
 }
 
