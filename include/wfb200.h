@@ -236,7 +236,9 @@ WF_API int wf_bert(const uint8_t* d_dec_bits, const int8_t* d_dec_syms, int64_t 
  *      float64 statement in oracle/cpm_generic.py.  Parity unpinned. ---------------------- */
 /* d_z complex[B][ld_z][n_h * M^Lp]: per detection step the bank outputs for every symbol
  * hypothesis (newest symbol most significant), one block of M^Lp per step parity i % n_h.
- * h = h_num[k % n_h] / p.  State count 2p * M^(Lp-1) <= 256.  Decision rule (oracle/cpm_generic.py):
+ * h = h_num[k % n_h] / p.  State count 2p * M^(Lp-1) <= 256.  Start: every history equal; of the 2p phase states only
+ * the parity class reachable from an empty channel (v = 0 after the Lp - 1 phantom symbols; every step changes the
+ * parity of v by K mod 2 for all its branches) -- the other class starts at -inf.  Decision rule (oracle/cpm_generic.py):
  * BLOCK RELEASE with survivor memory 2 D, D = `depth` (0 -> min(16, 32 / log2 M)): whenever t + 1 is a
  * multiple of D and t + 1 >= 2 D the survivor of the best state at step t releases the symbols of
  * steps [t - 2D + 1, t - D]; the best final survivor releases the rest.  This entry point keeps
