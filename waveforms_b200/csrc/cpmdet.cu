@@ -411,7 +411,6 @@ cpm_detect_m2l2_kernel(const __grid_constant__ CpmParams p, const __grid_constan
                 r[k][f] = k == 0 ? zx[f] : ((2 * k == HP) ? zy[f] : rot.c[k] * zx[f] + rot.s[k] * zy[f]);
             }
           uint32_t w = 0;
-          float wmax = -3.0e38f;
 #pragma unroll
           for (int s = 0; s < NS; ++s) {
             const int vnew = s >> 1, hnew = s & 1;
@@ -422,7 +421,6 @@ cpm_detect_m2l2_kernel(const __grid_constant__ CpmParams p, const __grid_constan
               const float c1 = vp1 < HP ? pm[2 * vp1 + 1] + r[vp1 % HP][f1] : pm[2 * vp1 + 1] - r[vp1 % HP][f1];
               const float d = c0 - c1;  // negative <=> c1 > c0: strict, so the lower x keeps ties
               pm[s] = fmaxf(c0, c1);
-              wmax = fmaxf(wmax, pm[s]);
               w = funnel_l1(w, __float_as_uint(d));  // live states in increasing s: rank j ends at bit P2 - 1 - j
             }
           }
@@ -430,6 +428,10 @@ cpm_detect_m2l2_kernel(const __grid_constant__ CpmParams p, const __grid_constan
           const bool blk = i == next_rel;
           const bool rel = blk || i == n_steps - 1;
           if (rel || NORM == 1 || (i & (NORM - 1)) == NORM - 1) {
+            float wmax = -3.0e38f;  // only the steps that normalise or release need the maximum
+#pragma unroll
+            for (int s = 0; s < NS; ++s)
+              if (((s >> 1) & 1) == Q) wmax = fmaxf(wmax, pm[s]);
             if (rel) {
               int best_s = -1;
 #pragma unroll
