@@ -4,7 +4,7 @@ One replicate of oracle/make_ber_table.py -- the reference itself, pure Python -
 cores.  The oracle chain (oracle/cpm_link.py) reproduces the reference's error count of every frame exactly when it is
 fed the same PN frame and the same PCG64 seed (tests/test_oracle_golden.py::
 test_oracle_link_reproduces_reference_ber_table_frames; this script's --check reproduces whole replicates of G10 cell by
-cell), and with its detector vectorised over frames one replicate takes a few minutes.  This script therefore runs the
+cell: done for salts 0 and 1e6), and with its detector vectorised over frames one replicate takes a few minutes.  This script therefore runs the
 SAME experiment (frames 0..1023 x 13 points, PCG64(1000 * EbN0 + frame + salt), PT / PAM at offset 0 and PT at offset
 -1 on the same received frame) for further salts and writes tests/golden/g10b_ber_table_oracle.npz: per replicate and
 pooled error counts, flagged source = "oracle".

@@ -336,3 +336,35 @@ def test_oracle_link_reproduces_reference_ber_table_frames():
                 assert be == int(ebf[rep, ebn0, frame, col]), (salt, ebn0, frame, det, off, be, int(ebf[rep, ebn0, frame, col]))
                 checked += 1
     assert checked == 18 * len(salts)
+
+
+def test_reference_equivalent_ber_replicates_are_consistent():
+    """G10b (oracle/make_ber_table_oracle.py): replicates of the BER-table experiment run through the oracle chain for
+    salts the reference was not run on.  The file must say where it comes from, must have been checked against whole
+    reference replicates, its salts must be disjoint from G10's, its sums must add up, and every one of its
+    replicates must be statistically compatible with the reference's own replicates (same experiment, other noise):
+    |replicate - pooled reference| below 5 standard errors of a replicate (design effect 2) in every cell, and the
+    mean over replicates within 4 standard errors of the reference's pooled estimate."""
+    import os
+
+    from tests.conftest import GOLDEN
+    if not os.path.exists(os.path.join(GOLDEN, "g10b_ber_table_oracle.npz")):
+        pytest.skip("no reference-equivalent replicates in this tree")
+    g, gb = golden("g10_ber_table.npz"), golden("g10b_ber_table_oracle.npz")
+    assert str(gb["source"]) == "oracle" and int(gb["frames"]) == int(g["frames"]) == 1024
+    assert len(gb["checked_against_g10_salts"]) >= 1 and set(map(int, gb["checked_against_g10_salts"])) <= set(map(int, g["salts"]))
+    assert not set(map(int, gb["salts"])) & set(map(int, g["salts"]))
+    reps = gb["errors_by_replicate"]                      # [salt][point][PT, PAM, PT@-1]
+    assert reps.shape == (gb["salts"].size, 13, 3)
+    for c, key in enumerate(("pt_errors", "pam_errors", "pt_m1_errors")):
+        assert np.array_equal(reps[:, :, c].sum(axis=0), gb[key])
+    n1 = 1024 * 4093
+    assert np.all(gb["compared_by_replicate"] == n1) and np.all(gb["compared"] == reps.shape[0] * n1)
+    n_ref = int(g["replicates"])
+    for c, key in enumerate(("pt_errors", "pam_errors", "pt_m1_errors")):
+        p_ref = g[key] / (n_ref * n1)
+        se1 = np.sqrt(2.0 * p_ref * (1 - p_ref) / n1)     # one replicate, design effect 2
+        dev = (reps[:, :, c] / n1 - p_ref) / np.sqrt(se1 ** 2 * (1 + 1 / n_ref))
+        assert np.max(np.abs(dev)) < 5.0, (key, float(np.max(np.abs(dev))))
+        zmean = (reps[:, :, c].mean(axis=0) / n1 - p_ref) / np.sqrt(se1 ** 2 * (1 / reps.shape[0] + 1 / n_ref))
+        assert np.max(np.abs(zmean)) < 4.0, (key, np.round(zmean, 2).tolist())
